@@ -1,0 +1,128 @@
+/* ofx.h -- C ABI of libofx.so: the B200 (sm_100a) replacement for the native entry points of
+ * OcclusionFusion's non-rigid fusion hot path.
+ *
+ * What it replaces in the reference (paths relative to the reference root):
+ *   - the PyCUDA `SourceModule(...).get_function("integrate")` launch
+ *         fusion_with_occlusion/tsdf.py:192-288 (kernel), :290 (binding), :405-441 (launch)
+ *   - the numba.cuda launch `deform_lbs_cuda[grid, block](...)`
+ *         fusion_with_occlusion/warpfield.py:234-266, 288-294, 607-630
+ *   - the torch warp `Registration.deform_ED`      NonRigidICP/model/registration_fusion.py:157-184
+ *   - the pykdtree query + numpy weights in `WarpField.skin`   fusion_with_occlusion/warpfield.py:83-129
+ *   - the numpy/numba CPU branch of `TSDFVolume.integrate`     fusion_with_occlusion/tsdf.py:442-494
+ *     (this branch defines the arithmetic: see DESIGN.md "contract arithmetic")
+ *
+ * Conventions
+ *   - plain C: opaque handle, raw pointers, sizes; no C++ or torch types; no exceptions.
+ *   - every function returns 0 on success, non-zero on failure; ofx_last_error() returns the
+ *     message of the calling thread's last failure.
+ *   - pointers are DEVICE pointers owned by the caller (torch tensors on the Python side)
+ *     unless the parameter name ends in `_host`.
+ *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it, nothing
+ *     synchronises except where stated.
+ *   - one handle per GPU (per volume shard); the handle's device must be current.
+ *   - there is no CPU fallback: without a CUDA device every call that would launch fails.
+ *
+ * Volume layout (tsdf.py:133-141, 294-304): three float32 arrays of shape (nx_local, Dy, Dz),
+ * C order, linear index (lx*Dy + iy)*Dz + iz, iz fastest.  A shard owns the x-planes
+ *     gx = (lx / x_block) * x_block * n_shards + shard * x_block + lx % x_block
+ * (x_block = Dx / n_shards gives contiguous slabs; smaller blocks deal planes round-robin).
+ */
+#ifndef OFX_H
+#define OFX_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OFX_ABI_VERSION 1
+#define OFX_MAX_K 8
+
+typedef struct ofx_volume ofx_volume; /* opaque */
+
+typedef struct ofx_volume_desc {
+    int32_t dims[3];      /* global Dx, Dy, Dz                                   tsdf.py:95-118 */
+    int32_t n_shards;     /* 1 = whole volume on this GPU                                        */
+    int32_t shard;        /* this GPU's shard index in [0, n_shards)                             */
+    int32_t x_block;      /* planes per dealt block; Dx % (x_block*n_shards) == 0               */
+    float origin[3];      /* _vol_origin (float32)                               tsdf.py:129    */
+    double voxel_size;    /* _voxel_size (float64 in the reference)              tsdf.py:106    */
+    double trunc_margin;  /* _trunc_margin                                       tsdf.py:127    */
+    float *tsdf;          /* (nx_local, Dy, Dz) device arrays, caller-owned       tsdf.py:133-141 */
+    float *weight;
+    float *colour;
+} ofx_volume_desc;
+
+/* counters written by ofx_integrate (device array of OFX_N_STATS uint64) */
+enum {
+    OFX_STAT_UPDATED = 0,    /* voxels whose tsdf/weight/colour were written                  */
+    OFX_STAT_SKIN_VALID = 1, /* voxels with K anchors inside 4*coverage that were visited     */
+    OFX_STAT_BRICKS = 2,     /* bricks visited                                                */
+    OFX_STAT_WEIGHT_SUM = 3, /* sum of the new weights of updated voxels (integer-valued)     */
+    OFX_N_STATS = 4
+};
+
+int ofx_abi_version(void);
+const char *ofx_last_error(void);
+
+/* ---- volume handle ------------------------------------------------------------------------ */
+int ofx_volume_create(ofx_volume **out, const ofx_volume_desc *desc);
+int ofx_volume_destroy(ofx_volume *v);
+/* fills tsdf=1, weight=0, colour=0                                         tsdf.py:133-141 */
+int ofx_volume_reset(ofx_volume *v, void *stream);
+int64_t ofx_volume_num_voxels(const ofx_volume *v); /* local voxels: nx_local*Dy*Dz */
+
+/* Graph nodes (canonical positions g, EDGraph.nodes) -- call again after node insertion
+ * (WarpField.update_graph, warpfield.py:487-582 -> :532-533 rebuild tree + re-skin).
+ * Rebuilds the per-voxel anchor cache (the device form of WarpField.skin_tsdf's cache,
+ * warpfield.py:131-141).  K = graph_neighbours (warpfield.py:60), 1..OFX_MAX_K, K <= M. */
+int ofx_set_graph(ofx_volume *v, const float *nodes, int32_t M, double node_coverage, int32_t K,
+                  void *stream);
+/* Node transforms in origin form: rotations (M,3,3) row-major, translations T = -R g + g + t
+ * (WarpField.update_transformations, warpfield.py:389-420). */
+int ofx_set_transforms(ofx_volume *v, const float *rotations, const float *translations,
+                       void *stream);
+
+/* One frame of TSDFVolume.integrate (tsdf.py:378-494): warp every voxel (unless
+ * identity_warp != 0: the source frame, tsdf.py:395-398), project, test, update in place.
+ * depth / colour_packed are the (H,W) images TSDFVolume.update produces (tsdf.py:545-572);
+ * intr_host = {fx, fy, cx, cy} already cast to float32 (tsdf.py:357); camera pose is I (:392).
+ * stats (may be NULL) receives OFX_N_STATS counters, overwritten. */
+int ofx_integrate(ofx_volume *v, const float *depth, const float *colour_packed, int32_t H,
+                  int32_t W, const float *intr_host, double obs_weight, int32_t identity_warp,
+                  uint64_t *stats, void *stream);
+
+/* Materialise what the reference keeps on the host, on request only (vis / tests):
+ *   world_pts (n,3)                                   tsdf.py:307
+ *   world_anchors (n,K) i32, world_weights (n,K) f32, world_valid_pts (n,) u8   warpfield.py:131-141
+ *   deform_tsdf(): warped (n,3) f32 + valid (n,) u8   warpfield.py:369-380
+ * Any output pointer may be NULL. n = ofx_volume_num_voxels. */
+int ofx_volume_world_points(ofx_volume *v, float *out_pts, void *stream);
+int ofx_volume_skin(ofx_volume *v, int32_t *anchors, float *weights, uint8_t *valid, void *stream);
+int ofx_volume_deform(ofx_volume *v, float *out_pts, uint8_t *valid, void *stream);
+
+/* ---- free-standing point-set operators ------------------------------------------------------ */
+/* TSDFVolume.update (tsdf.py:545-572): im (C,H,W) f32, C >= 4 -> packed colour (H,W) from
+ * channels 0..2 (RGB in [0,1]) and depth (H,W) = last channel (im[-1], tsdf.py:554).  The
+ * reference frame has C = 6 (RGB + XYZ); the host may upload only RGB + Z (C = 4). */
+int ofx_pack_frame(const float *im, int32_t C, int32_t H, int32_t W, float *colour_packed,
+                   float *depth, void *stream);
+/* WarpField.skin (warpfield.py:83-129): anchors (n,K) i32 (-1 beyond 4*coverage), weights (n,K)
+ * f32, valid (n,) u8. */
+int ofx_skin(const float *points, int64_t n, const float *nodes, int32_t M, double node_coverage,
+             int32_t K, int32_t *anchors, float *weights, uint8_t *valid, void *stream);
+/* WarpField.deform (warpfield.py:270-305): out = sum_k w_k (R_k p + T_k) for valid points,
+ * p itself otherwise. */
+int ofx_warp_points(const float *points, int64_t n, const int32_t *anchors, const float *weights,
+                    const uint8_t *valid, int32_t K, const float *rotations,
+                    const float *translations, float *out, void *stream);
+/* TSDFVolume.check_visibility (tsdf.py:599-612): valid (n,) u8, depth_diff (n,) f64. */
+int ofx_check_visibility(const float *points, int64_t n, const float *depth, int32_t H, int32_t W,
+                         const float *intr_host, double trunc_margin, uint8_t *valid,
+                         double *depth_diff, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OFX_H */

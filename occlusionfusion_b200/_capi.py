@@ -1,0 +1,111 @@
+"""ctypes binding of libofx.so (include/ofx.h).  Thin on purpose: torch tensors in, raw device
+pointers + sizes + the current CUDA stream out.  There is no CPU fallback: if the library is
+missing or no CUDA device is present, every entry point raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+import torch
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "lib", "libofx.so")
+
+OFX_MAX_K = 8
+OFX_N_STATS = 4
+STAT_UPDATED, STAT_SKIN_VALID, STAT_BRICKS, STAT_WEIGHT_SUM = range(4)
+
+# every symbol include/ofx.h declares (tests check the .so exports all of them)
+SYMBOLS = [
+    "ofx_abi_version", "ofx_last_error", "ofx_volume_create", "ofx_volume_destroy", "ofx_volume_reset",
+    "ofx_volume_num_voxels", "ofx_set_graph", "ofx_set_transforms", "ofx_integrate",
+    "ofx_volume_world_points", "ofx_volume_skin", "ofx_volume_deform", "ofx_pack_frame", "ofx_skin",
+    "ofx_warp_points", "ofx_check_visibility",
+]
+
+
+class OfxError(RuntimeError):
+    pass
+
+
+class VolumeDesc(C.Structure):
+    _fields_ = [
+        ("dims", C.c_int32 * 3), ("n_shards", C.c_int32), ("shard", C.c_int32), ("x_block", C.c_int32),
+        ("origin", C.c_float * 3), ("voxel_size", C.c_double), ("trunc_margin", C.c_double),
+        ("tsdf", C.c_void_p), ("weight", C.c_void_p), ("colour", C.c_void_p),
+    ]
+
+
+_lib = None
+
+
+def load():
+    """Loads libofx.so; raises OfxError when it has not been built (no fallback path)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise OfxError(f"{LIB_PATH} not found: build it with `python -m occlusionfusion_b200.build` "
+                       "(there is no CPU or PyTorch fallback for this path)")
+    lib = C.CDLL(LIB_PATH)
+    vp, i32, i64, f64 = C.c_void_p, C.c_int32, C.c_int64, C.c_double
+    lib.ofx_abi_version.restype = C.c_int
+    lib.ofx_last_error.restype = C.c_char_p
+    lib.ofx_volume_create.argtypes = [C.POINTER(vp), C.POINTER(VolumeDesc)]
+    lib.ofx_volume_destroy.argtypes = [vp]
+    lib.ofx_volume_reset.argtypes = [vp, vp]
+    lib.ofx_volume_num_voxels.argtypes = [vp]
+    lib.ofx_volume_num_voxels.restype = i64
+    lib.ofx_set_graph.argtypes = [vp, vp, i32, f64, i32, vp]
+    lib.ofx_set_transforms.argtypes = [vp, vp, vp, vp]
+    lib.ofx_integrate.argtypes = [vp, vp, vp, i32, i32, C.POINTER(C.c_float), f64, i32, vp, vp]
+    lib.ofx_volume_world_points.argtypes = [vp, vp, vp]
+    lib.ofx_volume_skin.argtypes = [vp, vp, vp, vp, vp]
+    lib.ofx_volume_deform.argtypes = [vp, vp, vp, vp]
+    lib.ofx_pack_frame.argtypes = [vp, i32, i32, i32, vp, vp, vp]
+    lib.ofx_skin.argtypes = [vp, i64, vp, i32, f64, i32, vp, vp, vp, vp]
+    lib.ofx_warp_points.argtypes = [vp, i64, vp, vp, vp, i32, vp, vp, vp, vp]
+    lib.ofx_check_visibility.argtypes = [vp, i64, vp, i32, i32, C.POINTER(C.c_float), f64, vp, vp, vp]
+    for name in SYMBOLS:
+        getattr(lib, name)      # AttributeError here = the .so is older than include/ofx.h
+    _lib = lib
+    return lib
+
+
+def check(rc):
+    if rc != 0:
+        raise OfxError(load().ofx_last_error().decode("utf-8", "replace"))
+
+
+def require_cuda():
+    if not torch.cuda.is_available():
+        raise OfxError("no CUDA device: occlusionfusion_b200 runs its hot path only on the GPU "
+                       "(no CPU fallback by design)")
+
+
+def stream_ptr(device=None):
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def ptr(t):
+    """Device pointer of a contiguous CUDA tensor (None -> NULL)."""
+    if t is None:
+        return C.c_void_p(0)
+    assert t.is_cuda and t.is_contiguous(), "expected a contiguous CUDA tensor"
+    return C.c_void_p(t.data_ptr())
+
+
+def intr4(cam_intr):
+    """{fx, fy, cx, cy} cast to float32 as cam2pix does (tsdf.py:357-359)."""
+    k = np.asarray(cam_intr, dtype=np.float64)
+    if k.shape == (3, 3):
+        k = np.array([k[0, 0], k[1, 1], k[0, 2], k[1, 2]])
+    k32 = k.astype(np.float32)
+    return (C.c_float * 4)(*[float(x) for x in k32])
+
+
+def to_device(a, dtype, device):
+    """numpy / tensor -> contiguous CUDA tensor of `dtype` (no copy when already there)."""
+    if isinstance(a, torch.Tensor):
+        return a.to(device=device, dtype=dtype).contiguous()
+    return torch.from_numpy(np.ascontiguousarray(a)).to(device=device, dtype=dtype).contiguous()

@@ -1,0 +1,189 @@
+// ofx_math.cuh -- the contract arithmetic of the fusion hot path as device functions.
+//
+// Compiled with --fmad=false: every fused multiply-add below is an explicit __fmaf_rn, every
+// other float/double operation is a single IEEE round-to-nearest op (nvcc defaults
+// -prec-div=true -prec-sqrt=true -ftz=false), so results are bit-identical to the reference
+// op order restated in DESIGN.md ("contract arithmetic").  Reference lines are relative to
+// /root/reference/fusion_with_occlusion/.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#define OFX_MAX_K 8
+
+namespace ofx {
+
+// float32 exp with a fixed op sequence: Cody-Waite reduction by ln2 (hi/lo), degree-5 Cephes
+// polynomial, exact scale by 2^n.  Stands in for numpy's float32 exp in warpfield.py:114
+// (neither numpy's nor CUDA's expf is correctly rounded, so the contract fixes its own).
+__device__ __forceinline__ float expf_det(float x)
+{
+    if (!(x > -87.0f)) return 0.0f;
+    const float n = rintf(x * 1.44269504088896341f);
+    float r = __fmaf_rn(n, -0.693145751953125f, x);
+    r = __fmaf_rn(n, -1.42860682030941723e-06f, r);
+    float p = 1.9875691500e-4f;
+    p = __fmaf_rn(p, r, 1.3981999507e-3f);
+    p = __fmaf_rn(p, r, 8.3334519073e-3f);
+    p = __fmaf_rn(p, r, 4.1665795894e-2f);
+    p = __fmaf_rn(p, r, 1.6666665459e-1f);
+    p = __fmaf_rn(p, r, 5.0000001201e-1f);
+    const float y = __fmaf_rn(p, r * r, r) + 1.0f;
+    return y * __int_as_float(((int)n + 127) << 23);
+}
+
+// pykdtree's float32 squared distance: ((dx*dx)+(dy*dy))+(dz*dz)   (warpfield.py:104)
+__device__ __forceinline__ float dist2(float px, float py, float pz, float gx, float gy, float gz)
+{
+    const float dx = px - gx, dy = py - gy, dz = pz - gz;
+    return ((dx * dx) + (dy * dy)) + (dz * dz);
+}
+
+// Sorted top-K insertion, ascending by (d2, arrival order).  Candidates must arrive in
+// ascending node index so that ties keep the lower index first (strict <).
+template <int K>
+__device__ __forceinline__ void topk_insert(float d2, int j, float (&bd)[K], int (&bi)[K])
+{
+    if (d2 < bd[K - 1]) {
+        bd[K - 1] = d2;
+        bi[K - 1] = j;
+#pragma unroll
+        for (int k = K - 1; k > 0; --k) {
+            if (bd[k] < bd[k - 1]) {
+                const float td = bd[k]; bd[k] = bd[k - 1]; bd[k - 1] = td;
+                const int ti = bi[k]; bi[k] = bi[k - 1]; bi[k - 1] = ti;
+            }
+        }
+    }
+}
+
+// np.sum(weights, axis=-1) order (warpfield.py:121): sequential for K < 8, numpy's 8-lane
+// pairwise tree for K == 8.
+template <int K>
+__device__ __forceinline__ float sum_k(const float (&w)[K])
+{
+    if constexpr (K < 8) {
+        float s = w[0];
+#pragma unroll
+        for (int k = 1; k < K; ++k) s = s + w[k];
+        return s;
+    } else {
+        return ((w[0] + w[1]) + (w[2] + w[3])) + ((w[4] + w[5]) + (w[6] + w[7]));
+    }
+}
+
+// Skinning weights from the K sorted squared distances (warpfield.py:104-121).
+// Returns true when all K anchors lie within cutoff = float32(4*coverage).
+template <int K>
+__device__ __forceinline__ bool skin_weights(const float (&bd)[K], float cutoff, float denom,
+                                             float (&w)[K], bool (&in_range)[K])
+{
+    bool ok = true;
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        const float d = sqrtf(bd[k]);
+        in_range[k] = !(d > cutoff);
+        ok = ok && in_range[k];
+        w[k] = in_range[k] ? expf_det(-(d * d) / denom) : 0.0f;
+    }
+    const float s = sum_k<K>(w) + 1e-6f;
+#pragma unroll
+    for (int k = 0; k < K; ++k) w[k] = w[k] / s;
+    return ok;
+}
+
+// One anchor's contribution to the blend: acc += w * (R p + T)   (warpfield.py:225-226).
+// rec = {R00..R22 row-major, T0, T1, T2}.
+__device__ __forceinline__ void lbs_accumulate(const float *__restrict__ rec, float w, float px,
+                                               float py, float pz, float &ax, float &ay, float &az)
+{
+    const float qx = __fmaf_rn(rec[2], pz, __fmaf_rn(rec[1], py, __fmaf_rn(rec[0], px, rec[9])));
+    const float qy = __fmaf_rn(rec[5], pz, __fmaf_rn(rec[4], py, __fmaf_rn(rec[3], px, rec[10])));
+    const float qz = __fmaf_rn(rec[8], pz, __fmaf_rn(rec[7], py, __fmaf_rn(rec[6], px, rec[11])));
+    ax = __fmaf_rn(w, qx, ax);
+    ay = __fmaf_rn(w, qy, ay);
+    az = __fmaf_rn(w, qz, az);
+}
+
+struct Camera {
+    float fx, fy, cx, cy;   // already float32 (tsdf.py:357-359)
+    int H, W;
+};
+
+// cam2pix + frustum test (tsdf.py:351-364, 589-593): float64, multiply before divide,
+// round half to even.  false when z <= 0 or the pixel falls outside the image.
+__device__ __forceinline__ bool project(float qx, float qy, float qz, const Camera &cam, int &u, int &v)
+{
+    if (!(qz > 0.0f)) return false;
+    const double z = (double)qz;
+    const double fu = rint((double)qx * (double)cam.fx / z + (double)cam.cx);
+    const double fv = rint((double)qy * (double)cam.fy / z + (double)cam.cy);
+    if (!(fu >= 0.0 && fu < (double)cam.W && fv >= 0.0 && fv < (double)cam.H)) return false;
+    u = (int)fu;
+    v = (int)fv;
+    return true;
+}
+
+// Running-average update of one voxel (tsdf.py:466, 373-375, 479-493).
+// diff = depth - z (float64), already known to satisfy depth > 0 && diff >= -trunc.
+__device__ __forceinline__ void fuse_voxel(float &tsdf, float &weight, float &colour, double diff,
+                                           float new_colour, double trunc, double obs, float obsf)
+{
+    const double dist = fmin(1.0, diff / trunc);
+    const float w_old = weight;
+    const float w_new = (float)((double)w_old + obs);
+    const float prod = w_old * tsdf;
+    tsdf = (float)(((double)prod + obs * dist) / (double)w_new);
+    weight = w_new;
+
+    const float oc = colour, nc = new_colour;
+    const float ob = floorf(oc / 65536.0f);
+    const float og = floorf((oc - ob * 65536.0f) / 256.0f);
+    const float orr = oc - ob * 65536.0f - og * 256.0f;
+    const float nb = floorf(nc / 65536.0f);
+    const float ng = floorf((nc - nb * 65536.0f) / 256.0f);
+    const float nr = nc - nb * 65536.0f - ng * 256.0f;
+    const float b = fminf(255.0f, rintf((w_old * ob + obsf * nb) / w_new));
+    const float g = fminf(255.0f, rintf((w_old * og + obsf * ng) / w_new));
+    const float r = fminf(255.0f, rintf((w_old * orr + obsf * nr) / w_new));
+    colour = b * 65536.0f + g * 256.0f + r;
+}
+
+// ---- TMA (1-D bulk copy) + mbarrier helpers ------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// global -> shared bulk copy through the TMA unit (SASS: UBLKCP); bytes % 16 == 0, both
+// addresses 16-byte aligned; completion is signalled on `bar` as transaction bytes.
+__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+}  // namespace ofx

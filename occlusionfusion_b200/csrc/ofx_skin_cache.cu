@@ -1,0 +1,385 @@
+// ofx_skin_cache.cu -- ofx_set_graph: builds the per-voxel anchor cache, the device form of
+// WarpField.skin_tsdf (warpfield.py:131-141), which the reference recomputes only when the graph
+// changes (node insertion, warpfield.py:493,532-533).
+//
+// The reference caches 33 B/voxel (anchors i32 x4, weights f32 x4, valid).  Here the cache is
+// K bytes per voxel (padded to 4 or 8): brick-local anchor ids into a per-brick list of the
+// nodes its voxels actually use; weights are recomputed from the node positions (same float
+// ops, so bit-identical) in the fused kernel.  Bricks without a single skin-valid voxel never
+// enter the work list, so the 4*coverage cutoff (warpfield.py:109) culls whole bricks exactly.
+//
+// Pipeline (all on `stream`; ends with one small device->host read, i.e. it synchronises):
+//   1 brick_bound_kernel   per brick: K-th nearest node distance D_K from the brick centre;
+//                          exact candidate radius R = min(D_K + 2h, cutoff + h) (h = half
+//                          diagonal); bricks with D_K - h > cutoff are dead
+//   2 scan                 offsets of the candidate lists
+//   3 brick_fill_kernel    candidate node ids, ascending
+//   4 skin_brick_kernel    per voxel exact top-K over the brick's candidates (registers),
+//                          used-node marking, compaction, byte ids -> anchor cache
+//   5 scan                 work list of active bricks
+#include <vector>
+
+#include "ofx_volume.cuh"
+
+int ofx_upload_nodes(ofx_volume *v, const float *nodes, int M, cudaStream_t s);
+
+namespace ofx {
+
+constexpr int BOUND_NODE_TILE = 1024;
+constexpr float RADIUS_SLACK_REL = 1.0002f;   // covers float32 rounding of centre/voxel distances
+constexpr float RADIUS_SLACK_ABS = 1e-5f;
+
+struct BrickBox {
+    float cx, cy, cz, h;
+};
+
+__device__ __forceinline__ BrickBox brick_box(const VolumeGeom &g, int b)
+{
+    const BrickCoord c = brick_coord(g, b);
+    const int lx1 = min(c.lx0 + BX, g.nx) - 1, iy1 = min(c.iy0 + BY, g.Dy) - 1, iz1 = min(c.iz0 + BZ, g.Dz) - 1;
+    // planes of one brick may be non-contiguous in world x when shards are dealt round-robin
+    float x_lo = g.px[c.lx0], x_hi = x_lo;
+    for (int lx = c.lx0 + 1; lx <= lx1; ++lx) { x_lo = fminf(x_lo, g.px[lx]); x_hi = fmaxf(x_hi, g.px[lx]); }
+    const float y_lo = g.py[c.iy0], y_hi = g.py[iy1], z_lo = g.pz[c.iz0], z_hi = g.pz[iz1];
+    BrickBox bb;
+    bb.cx = 0.5f * (x_lo + x_hi); bb.cy = 0.5f * (y_lo + y_hi); bb.cz = 0.5f * (z_lo + z_hi);
+    const float hx = 0.5f * (x_hi - x_lo), hy = 0.5f * (y_hi - y_lo), hz = 0.5f * (z_hi - z_lo);
+    bb.h = sqrtf(hx * hx + hy * hy + hz * hz) * RADIUS_SLACK_REL + RADIUS_SLACK_ABS;
+    return bb;
+}
+
+// Pass 1+2 (count) when cand == nullptr, pass 3 (fill) otherwise.
+__global__ void __launch_bounds__(128) brick_bound_kernel(VolumeGeom g, int n_bricks, const float *__restrict__ node_rec,
+                                                          int M, int K, float cutoff, float *__restrict__ radius,
+                                                          int *__restrict__ cnt, const int *__restrict__ off,
+                                                          int *__restrict__ cand)
+{
+    __shared__ float s_n[BOUND_NODE_TILE * 3];
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = b < n_bricks;
+    BrickBox bb{0.f, 0.f, 0.f, 0.f};
+    if (live) bb = brick_box(g, b);
+    const bool fill = cand != nullptr;
+    float R = 0.f;
+    int w = 0;
+    if (fill && live) { R = radius[b]; w = off[b]; }
+
+    if (!fill) {
+        float bd[OFX_MAX_K];
+        for (int k = 0; k < OFX_MAX_K; ++k) bd[k] = __int_as_float(0x7f800000);
+        for (int base = 0; base < M; base += BOUND_NODE_TILE) {
+            const int n = min(BOUND_NODE_TILE, M - base);
+            __syncthreads();
+            for (int t = threadIdx.x; t < n; t += blockDim.x) {
+                const float *r = node_rec + (int64_t)(base + t) * NODE_REC_FLOATS;
+                s_n[3 * t] = r[0]; s_n[3 * t + 1] = r[1]; s_n[3 * t + 2] = r[2];
+            }
+            __syncthreads();
+            if (live)
+                for (int j = 0; j < n; ++j) {
+                    const float d2 = dist2(bb.cx, bb.cy, bb.cz, s_n[3 * j], s_n[3 * j + 1], s_n[3 * j + 2]);
+                    if (d2 < bd[K - 1]) {
+                        int k = K - 1;
+                        while (k > 0 && d2 < bd[k - 1]) { bd[k] = bd[k - 1]; --k; }
+                        bd[k] = d2;
+                    }
+                }
+        }
+        if (live) {
+            const float dk = sqrtf(bd[K - 1]) * RADIUS_SLACK_REL + RADIUS_SLACK_ABS;
+            const float cut = cutoff * RADIUS_SLACK_REL + RADIUS_SLACK_ABS;
+            // dead brick: even the nearest corner is farther than the cutoff from its K-th node
+            R = (sqrtf(bd[K - 1]) - bb.h > cut) ? -1.0f : fminf(dk + 2.0f * bb.h, cut + bb.h);
+            radius[b] = R;
+        }
+    }
+    int count = 0;
+    for (int base = 0; base < M; base += BOUND_NODE_TILE) {
+        const int n = min(BOUND_NODE_TILE, M - base);
+        __syncthreads();
+        for (int t = threadIdx.x; t < n; t += blockDim.x) {
+            const float *r = node_rec + (int64_t)(base + t) * NODE_REC_FLOATS;
+            s_n[3 * t] = r[0]; s_n[3 * t + 1] = r[1]; s_n[3 * t + 2] = r[2];
+        }
+        __syncthreads();
+        if (live && R >= 0.f)
+            for (int j = 0; j < n; ++j) {
+                const float d2 = dist2(bb.cx, bb.cy, bb.cz, s_n[3 * j], s_n[3 * j + 1], s_n[3 * j + 2]);
+                if (d2 <= R * R) {
+                    if (fill) cand[w + count] = base + j;
+                    ++count;
+                }
+            }
+    }
+    if (live && !fill) cnt[b] = count;
+}
+
+// Single-CTA exclusive scan of n ints (n up to a few million; runs only when the graph changes).
+// flag_mode: scan (in[i] > 0) instead of in[i] and scatter i into `compact` at its rank.
+__global__ void __launch_bounds__(1024) scan_kernel(const int *__restrict__ in, int n, int *__restrict__ out,
+                                                    int *__restrict__ compact, int *__restrict__ total_max)
+{
+    __shared__ int s_warp[32];
+    __shared__ int s_carry;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_carry = 0;
+    int vmax = 0;
+    __syncthreads();
+    for (int base = 0; base < n; base += 1024) {
+        const int i = base + threadIdx.x;
+        int x = i < n ? in[i] : 0;
+        vmax = max(vmax, x);
+        if (compact) x = x > 0 ? 1 : 0;
+        int incl = x;
+        for (int o = 1; o < 32; o <<= 1) {
+            const int y = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += y;
+        }
+        if (lane == 31) s_warp[wid] = incl;
+        __syncthreads();
+        if (wid == 0) {
+            int t = s_warp[lane];
+            for (int o = 1; o < 32; o <<= 1) {
+                const int y = __shfl_up_sync(0xffffffffu, t, o);
+                if (lane >= o) t += y;
+            }
+            s_warp[lane] = t;
+        }
+        __syncthreads();
+        const int excl = s_carry + (wid ? s_warp[wid - 1] : 0) + incl - x;
+        if (i < n) {
+            if (out) out[i] = excl;
+            if (compact && x) compact[excl] = i;
+        }
+        __syncthreads();
+        if (threadIdx.x == 1023) s_carry = excl + x;
+        __syncthreads();
+    }
+    // block max
+    for (int o = 16; o > 0; o >>= 1) vmax = max(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+    if (lane == 0) s_warp[wid] = vmax;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int m = 0;
+        for (int k = 0; k < 32; ++k) m = max(m, s_warp[k]);
+        total_max[0] = s_carry;
+        total_max[1] = m;
+    }
+}
+
+// Pass 4.  One CTA per brick; dynamic shared memory:
+//   s_pos  [3 * CAND_TILE] floats   candidate positions of the current tile
+//   s_rank [max_cnt] uint16         used flag, then rank among used
+constexpr int CAND_TILE = 512;
+
+template <int K>
+__global__ void __launch_bounds__(BRICK_THREADS) skin_brick_kernel(VolumeGeom g, const float *__restrict__ node_rec,
+                                                                   float cutoff, const int *__restrict__ off,
+                                                                   int *__restrict__ cnt, const int *__restrict__ cand,
+                                                                   int *__restrict__ brick_nodes,
+                                                                   uint8_t *__restrict__ cache, int cache_bpv,
+                                                                   int *__restrict__ error_flag)
+{
+    extern __shared__ __align__(16) unsigned char s_raw[];
+    float *s_pos = reinterpret_cast<float *>(s_raw);
+    unsigned short *s_rank = reinterpret_cast<unsigned short *>(s_raw + 3 * CAND_TILE * sizeof(float));
+    __shared__ int s_warp[BRICK_THREADS / 32];
+    __shared__ int s_carry;
+
+    const int b = blockIdx.x;
+    const int n_cand = cnt[b], base_off = off[b];
+    if (n_cand == 0) return;   // dead brick: never enters the work list, its cache bytes are never read
+    const BrickCoord bc = brick_coord(g, b);
+    const int tz = threadIdx.x & 7, ty = (threadIdx.x >> 3) & 7, tx = threadIdx.x >> 6;
+    const int lx = bc.lx0 + tx, iy = bc.iy0 + ty, iz0 = bc.iz0 + tz * VOX_PER_THREAD;
+    const bool row_live = lx < g.nx && iy < g.Dy;
+    const int64_t vox0 = ((int64_t)lx * g.Dy + iy) * g.Dz + iz0;
+
+    bool any_valid = false;
+    int bi[VOX_PER_THREAD][K];
+    bool ok[VOX_PER_THREAD];
+    if (n_cand > 0) {
+        float bd[VOX_PER_THREAD][K];
+#pragma unroll
+        for (int e = 0; e < VOX_PER_THREAD; ++e)
+#pragma unroll
+            for (int k = 0; k < K; ++k) { bd[e][k] = __int_as_float(0x7f800000); bi[e][k] = -1; }
+        float px = 0.f, py = 0.f, pz[VOX_PER_THREAD] = {0.f, 0.f, 0.f, 0.f};
+        if (row_live) {
+            px = g.px[lx]; py = g.py[iy];
+#pragma unroll
+            for (int e = 0; e < VOX_PER_THREAD; ++e) pz[e] = (iz0 + e < g.Dz) ? g.pz[iz0 + e] : 0.f;
+        }
+        for (int t = threadIdx.x; t < n_cand; t += blockDim.x) s_rank[t] = 0;
+        for (int base = 0; base < n_cand; base += CAND_TILE) {
+            const int n = min(CAND_TILE, n_cand - base);
+            __syncthreads();
+            for (int t = threadIdx.x; t < n; t += blockDim.x) {
+                const float *r = node_rec + (int64_t)cand[base_off + base + t] * NODE_REC_FLOATS;
+                s_pos[3 * t] = r[0]; s_pos[3 * t + 1] = r[1]; s_pos[3 * t + 2] = r[2];
+            }
+            __syncthreads();
+            if (row_live)
+                for (int j = 0; j < n; ++j) {
+                    const float gx = s_pos[3 * j], gy = s_pos[3 * j + 1], gz = s_pos[3 * j + 2];
+                    const float dx = px - gx, dy = py - gy;
+                    const float dxy = (dx * dx) + (dy * dy);          // shared by the 4 voxels of the thread
+#pragma unroll
+                    for (int e = 0; e < VOX_PER_THREAD; ++e) {
+                        const float dz = pz[e] - gz;
+                        topk_insert<K>(dxy + (dz * dz), base + j, bd[e], bi[e]);
+                    }
+                }
+        }
+#pragma unroll
+        for (int e = 0; e < VOX_PER_THREAD; ++e) {
+            // all K within the cutoff <=> the K-th is (distances ascending)   warpfield.py:109-120
+            ok[e] = row_live && (iz0 + e < g.Dz) && !(sqrtf(bd[e][K - 1]) > cutoff);
+            any_valid |= ok[e];
+            if (ok[e])
+#pragma unroll
+                for (int k = 0; k < K; ++k) s_rank[bi[e][k]] = 1;
+        }
+    } else {
+#pragma unroll
+        for (int e = 0; e < VOX_PER_THREAD; ++e) ok[e] = false;
+    }
+    __syncthreads();
+
+    // rank the used candidates (exclusive scan over the flags), emit the brick's node list
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    for (int base = 0; base < n_cand; base += BRICK_THREADS) {
+        const int i = base + threadIdx.x;
+        const int x = i < n_cand ? s_rank[i] : 0;
+        int incl = x;
+        for (int o = 1; o < 32; o <<= 1) {
+            const int y = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += y;
+        }
+        if (lane == 31) s_warp[wid] = incl;
+        __syncthreads();
+        int wpre = 0;
+        for (int k = 0; k < wid; ++k) wpre += s_warp[k];
+        const int excl = s_carry + wpre + incl - x;
+        if (i < n_cand) {
+            s_rank[i] = (unsigned short)excl;
+            if (x) brick_nodes[base_off + excl] = cand[base_off + i];
+        }
+        __syncthreads();
+        if (threadIdx.x == BRICK_THREADS - 1) s_carry = excl + x;
+        __syncthreads();
+    }
+    const int n_used = s_carry;
+    if (threadIdx.x == 0) {
+        cnt[b] = n_used;
+        if (n_used > MAX_BRICK_NODES) atomicExch(error_flag, n_used);
+    }
+
+    // byte ids -> cache (0xFF = no anchor)
+    if (row_live) {
+#pragma unroll
+        for (int e = 0; e < VOX_PER_THREAD; ++e) {
+            if (iz0 + e >= g.Dz) continue;
+            uint8_t *c = cache + (vox0 + e) * cache_bpv;
+            for (int k = 0; k < cache_bpv; ++k) {
+                uint8_t id = 0xFF;
+                if (k < K && ok[e]) id = (uint8_t)min((int)s_rank[bi[e][k]], 254);
+                c[k] = id;
+            }
+        }
+    }
+    (void)any_valid;
+}
+
+}  // namespace ofx
+
+using namespace ofx;
+
+template <int K>
+static int launch_skin_brick(ofx_volume *v, int max_cnt, cudaStream_t s)
+{
+    const size_t smem = 3 * CAND_TILE * sizeof(float) + (size_t)max_cnt * sizeof(unsigned short) + 16;
+    OFX_REQUIRE(smem <= 200 * 1024, "ofx_set_graph: a brick has %d candidate nodes; unsupported", max_cnt);
+    OFX_CUDA(cudaFuncSetAttribute(skin_brick_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    skin_brick_kernel<K><<<v->n_bricks, BRICK_THREADS, smem, s>>>(v->geom, v->node_rec, v->cutoff, v->brick_off,
+                                                                  v->brick_cnt, v->cand, v->brick_nodes,
+                                                                  v->anchor_cache, v->cache_bytes_per_voxel,
+                                                                  v->scratch + 2);
+    OFX_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int ofx_set_graph(ofx_volume *v, const float *nodes, int32_t M, double node_coverage, int32_t K,
+                             void *stream)
+{
+    OFX_REQUIRE(v && nodes, "ofx_set_graph: null argument");
+    OFX_REQUIRE(K >= 1 && K <= OFX_MAX_K && M >= K, "ofx_set_graph: need 1 <= K <= %d and K <= M (K=%d, M=%d)",
+                OFX_MAX_K, K, M);
+    OFX_REQUIRE(node_coverage > 0, "ofx_set_graph: node_coverage must be positive");
+    cudaStream_t s = (cudaStream_t)stream;
+    v->graph_ready = false;
+    v->transforms_ready = false;
+    if (int rc = ofx_upload_nodes(v, nodes, M, s)) return rc;
+    v->M = M; v->K = K; v->coverage = node_coverage;
+    v->cutoff = (float)(4.0 * node_coverage);                        // warpfield.py:109
+    v->denom = (float)(2.0 * (node_coverage * node_coverage));       // warpfield.py:114
+
+    const int bpv = K <= 4 ? 4 : 8;
+    if (!v->anchor_cache || bpv != v->cache_bytes_per_voxel) {
+        if (v->anchor_cache) OFX_CUDA(cudaFree(v->anchor_cache));
+        v->anchor_cache = nullptr;
+        OFX_CUDA(cudaMalloc(&v->anchor_cache, (size_t)v->n_voxels * bpv));
+        v->cache_bytes_per_voxel = bpv;
+    }
+
+    const int nb = v->n_bricks;
+    OFX_CUDA(cudaMemsetAsync(v->scratch, 0, 16 * sizeof(int), s));
+    brick_bound_kernel<<<(nb + 127) / 128, 128, 0, s>>>(v->geom, nb, v->node_rec, M, K, v->cutoff, v->brick_radius,
+                                                        v->brick_cnt, nullptr, nullptr);
+    OFX_LAUNCH_CHECK();
+    scan_kernel<<<1, 1024, 0, s>>>(v->brick_cnt, nb, v->brick_off, nullptr, v->scratch);
+    OFX_LAUNCH_CHECK();
+    int tm[2] = {0, 0};
+    OFX_CUDA(cudaMemcpyAsync(tm, v->scratch, sizeof(tm), cudaMemcpyDeviceToHost, s));
+    OFX_CUDA(cudaStreamSynchronize(s));
+    const int64_t total = tm[0];
+    const int max_cnt = tm[1];
+    if (total > v->list_capacity) {
+        if (v->cand) OFX_CUDA(cudaFree(v->cand));
+        if (v->brick_nodes) OFX_CUDA(cudaFree(v->brick_nodes));
+        v->cand = v->brick_nodes = nullptr;
+        const int64_t cap = total + total / 4 + 1024;
+        OFX_CUDA(cudaMalloc(&v->cand, cap * sizeof(int)));
+        OFX_CUDA(cudaMalloc(&v->brick_nodes, cap * sizeof(int)));
+        v->list_capacity = cap;
+    }
+    if (total > 0) {
+        brick_bound_kernel<<<(nb + 127) / 128, 128, 0, s>>>(v->geom, nb, v->node_rec, M, K, v->cutoff,
+                                                            v->brick_radius, v->brick_cnt, v->brick_off, v->cand);
+        OFX_LAUNCH_CHECK();
+    }
+    int rc = 0;
+    switch (K) {
+    case 1: rc = launch_skin_brick<1>(v, max_cnt, s); break;
+    case 2: rc = launch_skin_brick<2>(v, max_cnt, s); break;
+    case 3: rc = launch_skin_brick<3>(v, max_cnt, s); break;
+    case 4: rc = launch_skin_brick<4>(v, max_cnt, s); break;
+    case 5: rc = launch_skin_brick<5>(v, max_cnt, s); break;
+    case 6: rc = launch_skin_brick<6>(v, max_cnt, s); break;
+    case 7: rc = launch_skin_brick<7>(v, max_cnt, s); break;
+    default: rc = launch_skin_brick<8>(v, max_cnt, s); break;
+    }
+    if (rc) return rc;
+    scan_kernel<<<1, 1024, 0, s>>>(v->brick_cnt, nb, nullptr, v->active, v->scratch + 4);
+    OFX_LAUNCH_CHECK();
+    int res[6] = {0};
+    OFX_CUDA(cudaMemcpyAsync(res, v->scratch, sizeof(res), cudaMemcpyDeviceToHost, s));
+    OFX_CUDA(cudaStreamSynchronize(s));
+    OFX_REQUIRE(res[2] == 0, "ofx_set_graph: a brick of %dx%dx%d voxels uses %d distinct anchor nodes (limit %d); "
+                "nodes are far denser than the voxel grid", BX, BY, BZ, res[2], MAX_BRICK_NODES);
+    v->n_active = res[4];
+    v->graph_ready = true;
+    return 0;
+}

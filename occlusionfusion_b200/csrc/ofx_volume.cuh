@@ -1,0 +1,71 @@
+// ofx_volume.cuh -- the device-side state behind an ofx_volume handle, shared by the
+// translation units that build the anchor cache (ofx_skin_cache.cu) and run the fused
+// warp + integrate kernel (ofx_integrate.cu).
+#pragma once
+#include "../../include/ofx.h"
+#include "ofx_common.h"
+#include "ofx_math.cuh"
+
+namespace ofx {
+
+// A brick is the unit of work of one CTA: BX x BY x BZ voxels, 256 threads, each thread owns
+// VOX_PER_THREAD consecutive voxels along z (the contiguous axis) = one float4 of each volume.
+constexpr int BX = 4, BY = 8, BZ = 32;
+constexpr int VOX_PER_THREAD = 4;
+constexpr int BRICK_THREADS = BX * BY * (BZ / VOX_PER_THREAD);   // 256
+constexpr int BRICK_VOXELS = BX * BY * BZ;                       // 1024
+constexpr int NODE_REC_FLOATS = 16;   // {gx,gy,gz,0, R00..R22, T0,T1,T2} = 64 B, one TMA bulk copy
+constexpr int MAX_BRICK_NODES = 255;  // local anchor ids are bytes, 0xFF = "no anchor"
+
+struct VolumeGeom {
+    int nx, Dy, Dz;          // local extent (nx = planes owned by this shard)
+    int nbx, nby, nbz;       // bricks per axis
+    const float *px;         // world x of local plane lx   (nx entries)   tsdf.py:348
+    const float *py;         // world y of iy               (Dy entries)
+    const float *pz;         // world z of iz               (Dz entries)
+};
+
+struct BrickCoord {
+    int lx0, iy0, iz0;
+};
+
+__device__ __forceinline__ BrickCoord brick_coord(const VolumeGeom &g, int b)
+{
+    const int bz = b % g.nbz;
+    const int by = (b / g.nbz) % g.nby;
+    const int bx = b / (g.nbz * g.nby);
+    return BrickCoord{bx * BX, by * BY, bz * BZ};
+}
+
+}  // namespace ofx
+
+struct ofx_volume {
+    ofx_volume_desc desc;
+    int device;
+    ofx::VolumeGeom geom;
+    int64_t n_voxels;
+    int n_bricks;
+    float *tables;            // px | py | pz
+
+    // graph
+    int M, K;
+    double coverage;
+    float cutoff, denom;
+    float *node_rec;          // M x NODE_REC_FLOATS
+    int node_rec_capacity;
+
+    // anchor cache (device form of WarpField.skin_tsdf's cache, warpfield.py:131-141)
+    int cache_bytes_per_voxel;   // 4 (K<=4) or 8
+    uint8_t *anchor_cache;       // n_voxels * cache_bytes_per_voxel
+    int *brick_cnt;              // n_bricks: candidate count, later used-node count
+    int *brick_off;              // n_bricks: offset into brick_nodes / cand
+    float *brick_radius;         // n_bricks
+    int *cand;                   // conservative candidate lists
+    int *brick_nodes;            // used-node lists (ascending node index)
+    int64_t list_capacity;
+    int *active;                 // bricks with at least one skin-valid voxel
+    int n_active;
+    int *scratch;                // small device scratch: [0]=total [1]=max [2]=error
+    uint64_t *stats_scratch;     // OFX_N_STATS counters when the caller passes NULL
+    bool graph_ready, transforms_ready;
+};

@@ -1,0 +1,257 @@
+"""TSDFVolume -- drop-in for the reference class of the same name
+(/root/reference/fusion_with_occlusion/tsdf.py:37-875) on the non-rigid fusion hot path.
+
+Same constructor and method signatures; the three volumes live in HBM as torch tensors and
+every per-voxel computation runs in libofx.so (include/ofx.h).  What the reference keeps as
+full-volume host arrays (`world_pts`, `vox_coords`, cached anchors/weights) is never
+materialised on the per-frame path; `world_pts` is produced on request.
+
+Not rebuilt here (SURVEY.md section 8f "next" rows): marching-cubes mesh extraction
+(tsdf.py:704-809) and everything that needs a visualiser.
+"""
+import logging
+import os
+import pickle
+
+import numpy as np
+import torch
+
+from . import _capi
+
+
+class TSDFVolume:
+    """Volumetric TSDF fusion of RGB-D frames under a non-rigid warp field (tsdf.py:37)."""
+
+    def __init__(self, bbox, max_depth, cam_intr, fopt, visualizer=None, *, device=None,
+                 shard=0, n_shards=1, x_block=None):
+        """
+        Args (as tsdf.py:41-49):
+            bbox: (w_min, h_min, w_max, h_max) of the captured region in pixels
+            max_depth: maximum depth in the sequence (metres)
+            cam_intr: (fx, fy, cx, cy)
+            fopt: options namespace; reads voxel_dim or voxel_size, source_frame, skip_rate and,
+                  when present, datadir (results folders as tsdf.py:314-319)
+            visualizer: kept for signature parity; unused (headless)
+        Extra keyword-only arguments (multi-GPU): this process owns shard `shard` of `n_shards`;
+        x-planes are dealt in blocks of `x_block` (default Dx/n_shards = contiguous slabs).
+        """
+        _capi.require_cuda()
+        self._lib = _capi.load()
+        self.fopt = fopt
+        self.vis = visualizer
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+
+        self.cam_intr = np.eye(3)                                            # tsdf.py:55-59
+        self.cam_intr[0, 0], self.cam_intr[1, 1] = cam_intr[0], cam_intr[1]
+        self.cam_intr[0, 2], self.cam_intr[1, 2] = cam_intr[2], cam_intr[3]
+
+        self._vol_bnds, self._vol_dim, self._voxel_size = self.volume_geometry(bbox, max_depth, self.cam_intr, fopt)
+        self._color_const = 256 * 256
+        self._trunc_margin = 0.04                                            # tsdf.py:127
+        self._vol_bnds[:, 1] = self._vol_bnds[:, 0] + self._vol_dim * self._voxel_size
+        self._vol_origin = self._vol_bnds[:, 0].copy(order="C").astype(np.float32)   # tsdf.py:129
+
+        Dx, Dy, Dz = (int(d) for d in self._vol_dim)
+        self.n_shards, self.shard = int(n_shards), int(shard)
+        if Dx % self.n_shards:
+            raise ValueError(f"voxel_dim[0]={Dx} is not divisible by n_shards={n_shards}")
+        self.x_block = Dx // self.n_shards if x_block is None else int(x_block)
+        self._nx_local = Dx // self.n_shards
+        self._local_dim = (self._nx_local, Dy, Dz)
+
+        with torch.cuda.device(self.device):
+            self._tsdf_vol = torch.empty(self._local_dim, dtype=torch.float32, device=self.device)
+            self._weight_vol = torch.empty_like(self._tsdf_vol)
+            self._color_vol = torch.empty_like(self._tsdf_vol)
+            desc = _capi.VolumeDesc()
+            desc.dims[:] = [Dx, Dy, Dz]
+            desc.n_shards, desc.shard, desc.x_block = self.n_shards, self.shard, self.x_block
+            desc.origin[:] = [float(x) for x in self._vol_origin]
+            desc.voxel_size, desc.trunc_margin = float(self._voxel_size), float(self._trunc_margin)
+            desc.tsdf, desc.weight, desc.colour = (self._tsdf_vol.data_ptr(), self._weight_vol.data_ptr(),
+                                                   self._color_vol.data_ptr())
+            h = _capi.C.c_void_p()
+            _capi.check(self._lib.ofx_volume_create(_capi.C.byref(h), _capi.C.byref(desc)))
+            self._h = h
+            _capi.check(self._lib.ofx_volume_reset(self._h, _capi.stream_ptr(self.device)))  # tsdf=1, w=0, c=0
+            self._stats = torch.zeros(_capi.OFX_N_STATS, dtype=torch.int64, device=self.device)
+        self._intr4 = _capi.intr4(self.cam_intr)
+        self._frame_host = None      # pinned staging buffer for the (6,H,W) frame
+        self._frame_dev = None
+        self._h2d_done = None
+        self._color_im_dev = self._depth_im_dev = None
+        self._world_pts = None
+
+        if hasattr(fopt, "datadir") and fopt.datadir is not None:            # tsdf.py:314-319
+            self.savepath = os.path.join(fopt.datadir, "results")
+            for sub in ("", "tsdf", "visible_nodes", "canonical_model"):
+                os.makedirs(os.path.join(self.savepath, sub), exist_ok=True)
+        else:
+            self.savepath = None
+        self.log = logging.getLogger(__name__)
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h is not None and getattr(self, "_lib", None) is not None:
+            self._lib.ofx_volume_destroy(h)
+            self._h = None
+
+    # ------------------------------------------------------------------ geometry (host, O(1))
+    @staticmethod
+    def volume_geometry(bbox, max_depth, cam_intr3x3, fopt):
+        """Volume bounds, dims and voxel size exactly as tsdf.py:75-118 derives them."""
+        w_min, h_min, w_max, h_max = bbox
+        K = cam_intr3x3
+        zs = np.array([0, max_depth, max_depth, max_depth, max_depth])
+        view_frust_pts = np.array([
+            (np.array([0, w_min, w_min, w_max, w_max]) - K[0, 2]) * zs / K[0, 0],
+            (np.array([0, h_min, h_max, h_min, h_max]) - K[1, 2]) * zs / K[1, 1],
+            zs,
+        ])
+        vol_bnds = np.asarray([np.min(view_frust_pts, axis=1), np.max(view_frust_pts, axis=1)]).T
+        assert vol_bnds.shape == (3, 2), "[!] `vol_bnds` should be of shape (3, 2)."
+        if hasattr(fopt, "voxel_dim"):                                       # tsdf.py:95-107
+            voxel_dim = fopt.voxel_dim
+            if type(voxel_dim) == int:
+                vol_dim = np.array([voxel_dim, voxel_dim, voxel_dim])
+            elif type(voxel_dim) == list:
+                assert len(voxel_dim) == 3, f"Voxel dimension should have length = 3 found {voxel_dim}"
+                vol_dim = np.array(voxel_dim)
+            else:
+                voxel_dim = np.asarray(voxel_dim)
+                assert voxel_dim.shape[0] == 3, f"Voxel dimension should have length = 3 found {voxel_dim}"
+                vol_dim = voxel_dim
+            voxel_size = ((vol_bnds[:, 1] - vol_bnds[:, 0]) / vol_dim).max()
+        elif hasattr(fopt, "voxel_size"):                                    # tsdf.py:110-118
+            voxel_size = float(fopt.voxel_size)
+            vol_dim = np.ceil((vol_bnds[:, 1] - vol_bnds[:, 0]) / voxel_size).copy(order="C").astype(int)
+        else:
+            raise AttributeError("fopt needs voxel_dim or voxel_size")
+        return vol_bnds, vol_dim, voxel_size
+
+    @property
+    def world_pts(self):
+        """(N,3) float32 voxel positions (tsdf.py:307), materialised on first access only."""
+        if self._world_pts is None:
+            n = int(self._lib.ofx_volume_num_voxels(self._h))
+            out = torch.empty((n, 3), dtype=torch.float32, device=self.device)
+            _capi.check(self._lib.ofx_volume_world_points(self._h, _capi.ptr(out), _capi.stream_ptr(self.device)))
+            self._world_pts = out.cpu().numpy()
+        return self._world_pts
+
+    # ------------------------------------------------------------------ per-frame path
+    def update(self, im, frame_id):
+        """Update RGB-D frame info (tsdf.py:545-572): (6,H,W) float32, RGB in [0,1] + XYZ.
+
+        The frame is staged through pinned memory, uploaded once, and folded into the packed
+        colour image and the depth image on the device (same float32 op order)."""
+        im_t = im if isinstance(im, torch.Tensor) else None
+        shape = tuple(im.shape)
+        assert len(shape) == 3 and shape[0] >= 4, \
+            f"Input not correct\nDepth:{shape[1:]} should be (H,W)\nColor:{shape} should be (H,W,3)"
+        if shape[0] != 6:
+            raise ValueError("expected a (6,H,W) RGB+XYZ frame")
+        H, W = shape[1:]
+        # only RGB (im[:3]) and Z (im[-1]) are read by the path: upload 4 of the 6 channels
+        if self._frame_dev is None or tuple(self._frame_dev.shape[1:]) != (H, W):
+            self._frame_host = torch.empty((4, H, W), dtype=torch.float32, pin_memory=True)
+            self._frame_dev = torch.empty((4, H, W), dtype=torch.float32, device=self.device)
+            self._color_im_dev = torch.empty((H, W), dtype=torch.float32, device=self.device)
+            self._depth_im_dev = torch.empty((H, W), dtype=torch.float32, device=self.device)
+        if im_t is not None and im_t.is_cuda:
+            self._frame_dev[:3].copy_(im_t[:3])
+            self._frame_dev[3].copy_(im_t[-1])
+        else:
+            src = im_t if im_t is not None else torch.from_numpy(np.asarray(im, dtype=np.float32))
+            if self._h2d_done is not None:
+                self._h2d_done.synchronize()     # the previous frame's DMA must have left the staging buffer
+            self._frame_host[:3].copy_(src[:3])
+            self._frame_host[3].copy_(src[-1])
+            self._frame_dev.copy_(self._frame_host, non_blocking=True)
+            if self._h2d_done is None:
+                self._h2d_done = torch.cuda.Event()
+            self._h2d_done.record(torch.cuda.current_stream(self.device))
+        self.h2d_bytes_last_frame = self._frame_dev.numel() * 4
+        _capi.check(self._lib.ofx_pack_frame(_capi.ptr(self._frame_dev), 4, H, W, _capi.ptr(self._color_im_dev),
+                                             _capi.ptr(self._depth_im_dev), _capi.stream_ptr(self.device)))
+        self.im = im
+        if hasattr(self, "frame_id"):                                        # tsdf.py:569-570
+            assert self.frame_id + self.fopt.skip_rate == frame_id, \
+                f"Updating image data failed. Previous frame:{self.frame_id}, current frame:{frame_id} not integrated."
+        self.frame_id = frame_id
+
+    @property
+    def color_im(self):
+        return self._color_im_dev.cpu().numpy()
+
+    @property
+    def depth_im(self):
+        return self._depth_im_dev.cpu().numpy()
+
+    def integrate(self, image_data, obs_weight=1.):
+        """Integrate an RGB-D frame into the TSDF volume (tsdf.py:378-494).
+
+        image_data: {"im": (6,H,W) float32, "id": int}.  Source frame -> identity warp
+        (tsdf.py:395-398); any other frame is warped by self.warpfield (tsdf.py:401)."""
+        with torch.cuda.device(self.device):
+            self.update(image_data["im"], image_data["id"])
+            identity = self.frame_id == self.fopt.source_frame
+            if not identity:
+                wf = self.warpfield
+                assert wf.frame_id == self.frame_id, \
+                    f"Warpfield maps to:{wf.frame_id}th frame but TSDF maps to:{self.frame_id}th frame"  # warpfield.py:374
+                wf._sync_device()
+            H, W = self._depth_im_dev.shape
+            _capi.check(self._lib.ofx_integrate(self._h, _capi.ptr(self._depth_im_dev), _capi.ptr(self._color_im_dev),
+                                                H, W, self._intr4, float(obs_weight), int(identity),
+                                                _capi.ptr(self._stats), _capi.stream_ptr(self.device)))
+
+    def last_stats(self):
+        """Counters of the last integrate(): dict(updated, skin_valid, bricks, weight_sum). Synchronises."""
+        s = self._stats.cpu().tolist()
+        return dict(updated=s[_capi.STAT_UPDATED], skin_valid=s[_capi.STAT_SKIN_VALID],
+                    bricks=s[_capi.STAT_BRICKS], weight_sum=s[_capi.STAT_WEIGHT_SUM])
+
+    # ------------------------------------------------------------------ callers either side
+    def check_visibility(self, points):
+        """For each point check that it is not behind the image depth (tsdf.py:599-612).
+        Returns (valid (n,) bool, depth_diff (n,) float64)."""
+        pts = _capi.to_device(points, torch.float32, self.device).reshape(-1, 3)
+        n = pts.shape[0]
+        valid = torch.empty(n, dtype=torch.uint8, device=self.device)
+        diff = torch.empty(n, dtype=torch.float64, device=self.device)
+        H, W = self._depth_im_dev.shape
+        with torch.cuda.device(self.device):
+            _capi.check(self._lib.ofx_check_visibility(_capi.ptr(pts), n, _capi.ptr(self._depth_im_dev), H, W,
+                                                       self._intr4, float(self._trunc_margin), _capi.ptr(valid),
+                                                       _capi.ptr(diff), _capi.stream_ptr(self.device)))
+        return valid.cpu().numpy().astype(bool), diff.cpu().numpy()
+
+    def get_visible_nodes(self):
+        """Visibility of the deformed graph nodes in the current frame (tsdf.py:614-638)."""
+        assert self.warpfield.frame_id == self.frame_id
+        deformed_nodes = self.warpfield.get_deformed_nodes()
+        visible_nodes, _ = self.check_visibility(deformed_nodes)
+        if self.savepath is not None:
+            np.save(os.path.join(self.savepath, "visible_nodes", f"{self.frame_id}.npy"), visible_nodes)
+        return visible_nodes
+
+    def get_volume(self):
+        """(tsdf, colour, weight) as host float32 arrays of this shard (tsdf.py:673-680)."""
+        return self._tsdf_vol.cpu().numpy(), self._color_vol.cpu().numpy(), self._weight_vol.cpu().numpy()
+
+    def save_volume(self, datapath):                                         # tsdf.py:682-687
+        data = [np.expand_dims(d, axis=0) for d in self.get_volume()]
+        with open(datapath, "wb") as f:
+            pickle.dump(np.concatenate(data, axis=0), f)
+
+    def load_volume(self, datapath):                                         # tsdf.py:689-702
+        with open(datapath, "rb") as f:
+            data = pickle.load(f)
+        self._tsdf_vol.copy_(torch.from_numpy(np.ascontiguousarray(data[0], dtype=np.float32)))
+        self._color_vol.copy_(torch.from_numpy(np.ascontiguousarray(data[1], dtype=np.float32)))
+        self._weight_vol.copy_(torch.from_numpy(np.ascontiguousarray(data[2], dtype=np.float32)))
+
+    def get_canonical_model(self):
+        raise NotImplementedError("surface extraction (tsdf.py:704-809) is a 'next' row (SURVEY.md 8 f3); "
+                                  "pass canonical vertices to WarpField.update_graph explicitly")

@@ -36,7 +36,7 @@ def _load():
     lib = C.CDLL(_LIB_PATH)
     lib.ofx_oracle_expf.restype = C.c_float
     lib.ofx_oracle_expf.argtypes = [C.c_float]
-    lib.ofx_oracle_vox2world.argtypes = [_f32p, C.c_double, C.c_int, C.c_int, C.c_int, _f32p]
+    lib.ofx_oracle_vox2world.argtypes = [_f32p, C.c_double, C.c_int, C.c_int, C.c_int, C.c_int, _f32p]
     lib.ofx_oracle_pack_frame.argtypes = [_f32p, C.c_int, C.c_int, _f32p, _f32p]
     lib.ofx_oracle_skin.restype = C.c_int
     lib.ofx_oracle_skin.argtypes = [_f32p, C.c_int64, _f32p, C.c_int, C.c_int, C.c_double,
@@ -68,10 +68,11 @@ def expf(x):
     return np.array([lib().ofx_oracle_expf(float(v)) for v in np.ravel(x)], np.float32).reshape(np.shape(x))
 
 
-def vox2world(origin, voxel_size, dims):
+def vox2world(origin, voxel_size, dims, x0=0):
+    """dims = (Dx, Dy, Dz) of the slab starting at global x-plane x0."""
     Dx, Dy, Dz = (int(d) for d in dims)
     out = np.empty((Dx * Dy * Dz, 3), np.float32)
-    lib().ofx_oracle_vox2world(_c(origin, np.float32), float(voxel_size), Dx, Dy, Dz, out)
+    lib().ofx_oracle_vox2world(_c(origin, np.float32), float(voxel_size), int(x0), Dx, Dy, Dz, out)
     return out
 
 
@@ -136,7 +137,7 @@ def origin_translations(R, t, nodes):
 class OracleVolume:
     """The reference sequence TSDFVolume + WarpField on the CPU, via the oracle stages."""
 
-    def __init__(self, dims, origin, voxel_size, intr4, trunc=0.04):
+    def __init__(self, dims, origin, voxel_size, intr4, trunc=0.04, x0=0):
         self.dims = tuple(int(d) for d in dims)
         self.origin = np.asarray(origin, np.float32)
         self.voxel_size = float(voxel_size)
@@ -145,7 +146,7 @@ class OracleVolume:
         self.tsdf = np.ones(self.dims, np.float32)        # tsdf.py:133
         self.weight = np.zeros(self.dims, np.float32)     # tsdf.py:138
         self.colour = np.zeros(self.dims, np.float32)     # tsdf.py:141
-        self.world_pts = vox2world(self.origin, self.voxel_size, self.dims)
+        self.world_pts = vox2world(self.origin, self.voxel_size, self.dims, x0)
         self._skin = None
 
     def set_graph(self, nodes, coverage, K=None):

@@ -1,0 +1,276 @@
+"""GPU parity: the CUDA path (through the drop-in classes, i.e. through the C ABI of libofx.so)
+against (1) the golden vectors produced by the reference's own Python and (2) the C oracle on
+seeded synthetic inputs.  Bars (BASELINE.json north_star): anchors and integer weight counts
+bit-exact; TSDF, skinning weights and colours within 1e-5 absolute.  Against the oracle the CUDA
+path is expected to be bit-identical throughout (same op order), which the tests assert."""
+import types
+
+import numpy as np
+import pytest
+
+from conftest import load_golden
+
+pytestmark = pytest.mark.gpu
+
+
+def _mk_volume(g_or_w, dims=None, **kw):
+    from occlusionfusion_b200 import TSDFVolume
+    if isinstance(g_or_w, dict) or hasattr(g_or_w, "files"):
+        g = g_or_w
+        fopt = types.SimpleNamespace(voxel_dim=[int(d) for d in g["voxel_dim"]], source_frame=0, skip_rate=1)
+        return TSDFVolume(tuple(g["bbox"]), float(g["max_depth"]), g["intr"], fopt, None, **kw)
+    w = g_or_w
+    return TSDFVolume(w.bbox, w.max_depth, w.intr, w.fopt, None, **kw)
+
+
+def _graph(nodes, coverage):
+    from occlusionfusion_b200 import EDGraph
+    return EDGraph(nodes=nodes, graph_generation_parameters={"node_coverage": float(coverage)})
+
+
+@pytest.mark.parametrize("name", ["ref_k4", "ref_k8", "ref_m3"])
+def test_golden_sequence(name, oracle):
+    """The reference's own run, frame by frame: geometry, frame packing, warp, volumes."""
+    from occlusionfusion_b200 import WarpField
+    g = load_golden(name)
+    vol = _mk_volume(g)
+    assert np.array_equal(vol._vol_dim, g["voxel_dim"])
+    assert vol._voxel_size == float(g["voxel_size"])
+    assert np.array_equal(vol._vol_origin, g["vol_origin"])
+    assert np.array_equal(vol.world_pts, g["world_pts"])
+
+    K = min(int(g["K"]), len(g["nodes"]))
+    ov = oracle.OracleVolume(g["voxel_dim"], g["vol_origin"], g["voxel_size"], g["intr"], g["trunc"])
+    ov.set_graph(g["nodes"], float(g["coverage"]), K)
+
+    vol.integrate({"im": g["frames"][0], "id": 0})
+    ov.integrate(g["frames"][0], True)
+    assert np.array_equal(vol.color_im, g["color_im_0"]) and np.array_equal(vol.depth_im, g["depth_im_0"])
+    t, c, w = vol.get_volume()
+    assert np.array_equal(w, g["weight_0"]) and np.array_equal(c, g["color_0"])
+    assert np.array_equal(t, g["tsdf_0"])          # identity warp: no float32 warp in the way -> exact
+    assert vol.last_stats()["updated"] == int((g["weight_0"] != 0).sum())
+
+    wf = WarpField(_graph(g["nodes"], g["coverage"]), vol, None)
+    wf.graph_neighbours = K
+    vol.warpfield = wf
+    for f in range(1, len(g["frames"])):
+        est = dict(node_rotations=g[f"R_{f}"], node_translations=g[f"t_{f}"],
+                   deformed_nodes_to_target=g["nodes"] + g[f"t_{f}"], target_frame_id=f)
+        wf.update_transformations(est)
+        assert np.array_equal(wf.translations, g[f"T_{f}"])
+        vol.integrate({"im": g["frames"][f], "id": f})
+        ov.set_transforms(g[f"R_{f}"], g[f"T_{f}"])
+        n_upd = ov.integrate(g["frames"][f], False)
+        t, c, w = vol.get_volume()
+        # against the reference's run
+        assert np.array_equal(w, g[f"weight_{f}"]), "integer weight counts must be bit-exact"
+        assert np.array_equal(c, g[f"color_{f}"])
+        assert np.abs(t - g[f"tsdf_{f}"]).max() <= 1e-5
+        # against the oracle: bit-identical
+        assert np.array_equal(t, ov.tsdf) and np.array_equal(w, ov.weight) and np.array_equal(c, ov.colour)
+        st = vol.last_stats()
+        assert st["updated"] == n_upd
+        assert st["weight_sum"] == int(ov.weight[ov.weight != (g[f"weight_{f-1}"])].sum())
+        warped, valid = wf.deform_tsdf()
+        assert np.array_equal(valid, g[f"valid_{f}"])
+        assert np.abs(warped - g[f"warped_{f}"]).max() <= 1e-6
+        ow, _ = ov.deform_tsdf()
+        assert np.array_equal(warped, ow)
+    a, wts, v = wf.skin_tsdf()
+    oa, owt, ovl = ov.skin_tsdf()
+    assert np.array_equal(a, oa) and np.array_equal(wts, owt) and np.array_equal(v, ovl)
+    assert np.array_equal(v, g["skin_valid"])
+    assert np.abs(wts - g["weights"]).max() <= 1e-6 or name == "ref_k8"
+
+
+@pytest.mark.parametrize("name", ["ref_k4", "ref_k8", "ref_m3"])
+def test_point_operators_golden(name, oracle):
+    """skin / deform / check_visibility on free point sets (mesh vertices, graph nodes)."""
+    from occlusionfusion_b200 import WarpField
+    g = load_golden(name)
+    vol = _mk_volume(g)
+    last = len(g["frames"]) - 1
+    vol.update(g["frames"][last], 0)
+    wf = WarpField(_graph(g["nodes"], g["coverage"]), vol, None)
+    K = min(int(g["K"]), len(g["nodes"]))
+    wf.graph_neighbours = K
+    sub = g["nodes"][: max(int(g["K"]), len(g["nodes"]) // 2)]
+    a, w, v = wf.skin(g["skin_q"], nodes=sub)
+    assert a.dtype == np.int32 and w.dtype == np.float32 and v.dtype == bool
+    assert np.array_equal(a, g["skin_q_anchors"]) and np.array_equal(v, g["skin_q_valid"])
+    assert np.abs(w - g["skin_q_weights"]).max() <= 1e-6
+    oa, ow, ovl = oracle.skin(g["skin_q"], sub, K, float(g["coverage"]))
+    assert np.array_equal(a, oa) and np.array_equal(w, ow) and np.array_equal(v, ovl)
+    vis, diff = vol.check_visibility(g["skin_q"])
+    assert np.array_equal(vis, g["vis_valid"]) and np.array_equal(diff, g["vis_diff"])
+    # deform(): anchors index the sub-table
+    R, T = g[f"R_{last}"][: len(sub)], g[f"T_{last}"][: len(sub)]
+    wf.rotations, wf.translations = R, T
+    out = wf.deform(g["skin_q"], a, w, None, v)
+    assert np.array_equal(out, oracle.warp(g["skin_q"], a, w, v, R, T))
+    assert np.array_equal(out[~v], g["skin_q"][~v])               # invalid points pass through
+
+
+def _run_pair(w, oracle, n_frames=3, vol_kw=None, obs_weight=1.0):
+    """Drives the CUDA classes and the oracle over the same synthetic sequence."""
+    from occlusionfusion_b200 import WarpField
+    vol = _mk_volume(w, **(vol_kw or {}))
+    ov = oracle.OracleVolume(w.dims, w.origin, w.voxel_size, w.intr, w.trunc)
+    ov.set_graph(w.nodes, w.coverage, w.K)
+    wf = WarpField(w.graph(), vol, None)
+    wf.graph_neighbours = w.K
+    vol.warpfield = wf
+    stats = []
+    for f in range(n_frames):
+        im = w.frame(f)
+        if f > 0:
+            est = w.estimate(f)
+            wf.update_transformations(est)
+            ov.set_transforms(est["node_rotations"], wf.translations)
+        vol.integrate({"im": im, "id": f}, obs_weight)
+        n = ov.integrate(im, f == 0, obs_weight)
+        stats.append((vol.last_stats(), n))
+    return vol, ov, wf, stats
+
+
+def _assert_bit_equal(vol, ov, sl=slice(None)):
+    t, c, w = vol.get_volume()
+    assert np.array_equal(w, ov.weight[sl]), "weights differ"
+    assert np.array_equal(c, ov.colour[sl]), "colours differ"
+    assert np.array_equal(t, ov.tsdf[sl]), f"tsdf differs, max {np.abs(t - ov.tsdf[sl]).max()}"
+
+
+def test_synthetic_tiny_bit_exact(oracle):
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload("tiny")
+    vol, ov, wf, stats = _run_pair(w, oracle, n_frames=4)
+    _assert_bit_equal(vol, ov)
+    for st, n in stats:
+        assert st["updated"] == n
+    assert stats[1][1] > 1000, "workload too thin to mean anything"
+    a, wt, v = wf.skin_tsdf()
+    oa, owt, ovl = ov.skin_tsdf()
+    assert np.array_equal(a, oa) and np.array_equal(wt, owt) and np.array_equal(v, ovl)
+    assert stats[1][0]["skin_valid"] == int(ovl.sum())
+
+
+def test_synthetic_dense_and_obs_weight(oracle):
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload("c1-dense", dim=[48, 40, 64], voxel=0.02, n_nodes=64, H=120, W=160)
+    vol, ov, wf, stats = _run_pair(w, oracle, n_frames=3, obs_weight=2.0)
+    _assert_bit_equal(vol, ov)
+    assert stats[1][0]["skin_valid"] == w.dims[0] * w.dims[1] * w.dims[2]     # every voxel has K anchors
+
+
+@pytest.mark.parametrize("dims", [[13, 17, 19], [8, 8, 33], [5, 3, 4]])
+def test_ragged_dims_scalar_path(dims, oracle):
+    """Dz not a multiple of 4 -> unaligned rows -> scalar load/store path; bricks partly empty."""
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload("tiny", dim=dims, voxel=0.06, n_nodes=30, H=60, W=80)
+    vol, ov, wf, stats = _run_pair(w, oracle, n_frames=3)
+    _assert_bit_equal(vol, ov)
+
+
+@pytest.mark.parametrize("K", [1, 2, 3, 5, 8])
+def test_other_k(K, oracle):
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload("tiny", K=K, dim=[24, 24, 32], voxel=0.04)
+    vol, ov, wf, stats = _run_pair(w, oracle, n_frames=2)
+    _assert_bit_equal(vol, ov)
+    assert stats[1][1] > 0
+
+
+@pytest.mark.parametrize("x_block", [None, 4])
+def test_sharded_equals_whole(x_block, oracle):
+    """Two shards (contiguous slabs, and 4-plane blocks dealt round-robin) reproduce the whole volume."""
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload("tiny")
+    ov = None
+    parts = []
+    for r in range(2):
+        vol, ov, wf, stats = _run_pair(w, oracle, n_frames=3, vol_kw=dict(shard=r, n_shards=2, x_block=x_block))
+        parts.append(vol)
+    xb = w.dims[0] // 2 if x_block is None else x_block
+    for r, vol in enumerate(parts):
+        gx = np.array([(lx // xb) * xb * 2 + r * xb + lx % xb for lx in range(w.dims[0] // 2)])
+        _assert_bit_equal(vol, ov, gx)
+
+
+def test_idempotent_weight_count(oracle):
+    """Integrating the same warped frame n times: weight == n exactly on every touched voxel and
+    tsdf unchanged to 1 ulp (SURVEY.md 8c known-answer 4)."""
+    from occlusionfusion_b200 import WarpField
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload("tiny")
+    vol = _mk_volume(w)
+    wf = WarpField(w.graph(), vol, None)
+    vol.warpfield = wf
+    vol.fopt.source_frame = -1                       # every frame is a warped frame
+    wf.frame_id = -1
+    vol.frame_id = -1
+    im = w.frame(1)
+    est = w.estimate(1)
+    first = None
+    for f in range(5):
+        est["target_frame_id"] = f
+        wf.update_transformations(est)
+        vol.integrate({"im": im, "id": f})
+        t, c, wt = vol.get_volume()
+        if first is None:
+            first = (t.copy(), c.copy(), wt.copy())
+    touched = first[2] > 0
+    assert touched.sum() > 1000
+    assert np.array_equal(wt[touched], np.full(touched.sum(), 5.0, np.float32))
+    assert np.array_equal(wt[~touched], np.zeros((~touched).sum(), np.float32))
+    assert np.abs(t - first[0]).max() <= 2.4e-7
+    assert np.array_equal(c, first[1])
+
+
+def test_empty_inputs_and_errors():
+    from occlusionfusion_b200 import WarpField, _capi
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload("tiny")
+    vol = _mk_volume(w)
+    wf = WarpField(w.graph(), vol, None)
+    a, wt, v = wf.skin(np.zeros((0, 3), np.float32))
+    assert a.shape == (0, 4) and wt.shape == (0, 4) and v.shape == (0,)
+    vol.update(w.frame(0), 0)
+    vis, diff = vol.check_visibility(np.zeros((0, 3), np.float32))
+    assert vis.shape == (0,) and diff.shape == (0,)
+    # warped frame without a warp field / K > M -> loud errors, no silent fallback
+    wf.graph_neighbours = 500
+    with pytest.raises(_capi.OfxError):
+        wf.skin(np.zeros((4, 3), np.float32))
+    with pytest.raises(AssertionError):
+        vol.update(w.frame(1), 5)                    # frame id must advance by skip_rate (tsdf.py:569)
+
+
+def test_full_size_256_properties():
+    """BASELINE config c1 (256^3, 1 cm, ~1k nodes): size-independent properties at full size."""
+    from occlusionfusion_b200 import WarpField
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload("c1")
+    vol = _mk_volume(w)
+    wf = WarpField(w.graph(), vol, None)
+    vol.warpfield = wf
+    vol.integrate({"im": w.frame(0), "id": 0})
+    s0 = vol.last_stats()
+    t, c, wt = vol.get_volume()
+    assert int(wt.sum()) == s0["updated"] == s0["weight_sum"]
+    assert set(np.unique(wt)) <= {0.0, 1.0}
+    assert t.min() >= -1.0 and t.max() <= 1.0
+    # identity transforms on a warped frame == plain integrate restricted to skin-valid voxels
+    est = w.estimate(1)
+    est["node_rotations"] = np.tile(np.eye(3, dtype=np.float32), (w.M, 1, 1))
+    est["node_translations"] = np.zeros((w.M, 3), np.float32)
+    wf.update_transformations(est)
+    vol.integrate({"im": w.frame(0), "id": 1})
+    s1 = vol.last_stats()
+    t1, c1, wt1 = vol.get_volume()
+    assert 0 < s1["updated"] <= s1["skin_valid"] < wt.size
+    assert int(wt1.sum()) == s0["updated"] + s1["updated"]
+    # the warp only ever touches skin-valid voxels, and each at most once per frame
+    assert set(np.unique(wt1)) <= {0.0, 1.0, 2.0}
+    assert t1.min() >= -1.0 and t1.max() <= 1.0
+    assert np.all(c1 < 2 ** 24) and np.array_equal(c1, np.floor(c1))

@@ -1,0 +1,78 @@
+"""CPU: the C oracle against golden vectors produced by running the reference's own Python
+(oracle/make_golden.py).  Tolerances follow BASELINE.json north_star: anchors and weight counts
+bit-exact, tsdf / skinning weights / colours within 1e-5 (colours and counts are exact here)."""
+import numpy as np
+
+
+def _K(g):
+    return min(int(g["K"]), len(g["nodes"]))
+
+
+def test_vox2world_exact(oracle, golden):
+    _, g = golden
+    wp = oracle.vox2world(g["vol_origin"], g["voxel_size"], g["voxel_dim"])
+    assert np.array_equal(wp, g["world_pts"])
+
+
+def test_pack_frame_exact(oracle, golden):
+    _, g = golden
+    for f in range(len(g["frames"])):
+        c, d = oracle.pack_frame(g["frames"][f])
+        assert np.array_equal(c, g[f"color_im_{f}"])
+        assert np.array_equal(d, g[f"depth_im_{f}"])
+
+
+def test_skin_matches_reference(oracle, golden):
+    name, g = golden
+    a, w, v = oracle.skin(g["world_pts"], g["nodes"], _K(g), float(g["coverage"]))
+    assert np.array_equal(v, g["skin_valid"])
+    bad = np.nonzero((a != g["anchors"]).any(axis=1))[0]
+    # The golden run uses scipy's float64 cKDTree in place of pykdtree's float32 tree
+    # (oracle/ref_shims.py); two neighbours whose float32 distances tie or swap may come back in
+    # the other order.  Such rows must hold the same anchor SET, and there are at most a handful.
+    assert len(bad) <= 4, f"{name}: {len(bad)} anchor rows differ"
+    for i in bad:
+        assert sorted(a[i]) == sorted(g["anchors"][i])
+    ok = np.setdiff1d(np.arange(len(a)), bad)
+    assert np.abs(w[ok] - g["weights"][ok]).max() <= 1e-6
+    # free-standing skin() against an explicit node subset (warpfield.py:99-104)
+    sub = g["nodes"][: max(int(g["K"]), len(g["nodes"]) // 2)]
+    a2, w2, v2 = oracle.skin(g["skin_q"], sub, _K(g), float(g["coverage"]))
+    assert np.array_equal(a2, g["skin_q_anchors"]) and np.array_equal(v2, g["skin_q_valid"])
+    assert np.abs(w2 - g["skin_q_weights"]).max() <= 1e-6
+
+
+def test_check_visibility_exact(oracle, golden):
+    _, g = golden
+    last = len(g["frames"]) - 1
+    v, d = oracle.check_visibility(g["skin_q"], g[f"depth_im_{last}"], g["intr"], g["trunc"])
+    assert np.array_equal(v, g["vis_valid"])
+    assert np.array_equal(d, g["vis_diff"])
+
+
+def test_sequence_matches_reference(oracle, golden):
+    """source-frame integrate, then warped frames: warp <= 1e-6, tsdf <= 1e-5, weight and colour exact."""
+    name, g = golden
+    ov = oracle.OracleVolume(g["voxel_dim"], g["vol_origin"], g["voxel_size"], g["intr"], g["trunc"])
+    ov.set_graph(g["nodes"], float(g["coverage"]), _K(g))
+    for f in range(len(g["frames"])):
+        if f > 0:
+            T = oracle.origin_translations(g[f"R_{f}"], g[f"t_{f}"], g["nodes"])
+            assert np.array_equal(T, g[f"T_{f}"])
+            ov.set_transforms(g[f"R_{f}"], T)
+            warped, valid = ov.deform_tsdf()
+            assert np.array_equal(valid, g[f"valid_{f}"])
+            assert np.abs(warped - g[f"warped_{f}"]).max() <= 1e-6
+            assert np.abs(warped - g[f"warped_ed64_{f}"]).max() <= 1e-6      # ED form, float64
+        n_upd = ov.integrate(g["frames"][f], identity_warp=(f == 0))
+        assert n_upd == int((g[f"weight_{f}"] != (g[f"weight_{f-1}"] if f else 0)).sum())
+        assert np.array_equal(ov.weight, g[f"weight_{f}"]), f"{name} frame {f}: weight counts differ"
+        assert np.array_equal(ov.colour, g[f"color_{f}"]), f"{name} frame {f}: colours differ"
+        assert np.abs(ov.tsdf - g[f"tsdf_{f}"]).max() <= 1e-5
+
+
+def test_expf_close_to_libm(oracle):
+    x = np.linspace(-8.0, 0.0, 20001).astype(np.float32)
+    y = oracle.expf(x)
+    ref = np.exp(x.astype(np.float64))
+    assert np.max(np.abs(y - ref) / ref) < 3e-7
