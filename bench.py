@@ -1,0 +1,416 @@
+#!/usr/bin/env python
+"""bench.py -- warped-TSDF integration throughput (BASELINE.json metric) on N B200s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2-dense] [--impl reference]
+
+A step = one frame: node-transform upload + fused warp/integrate of the whole volume.
+  value      updated voxels / s, inputs resident in HBM, CUDA-event time, max over ranks
+  e2e        the same through the public classes (WarpField.update_transformations +
+             TSDFVolume.integrate on HOST numpy buffers, + reading the counters back)
+  roofline   the fused kernel against the measured HBM copy bandwidth (MEASURED_PEAKS.json)
+  cpu_baseline  the CPU oracle (C/OpenMP port of the reference CPU path) on a bounded slab
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "warped_tsdf_voxel_updates_per_sec"
+UNIT = "voxel-updates/s"
+FALLBACK_HBM_GBS = 6650.0     # /opt/skills/guides/B200_PROFILING.md fallback
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--workload", default="c2-dense")
+    ap.add_argument("--impl", default="ofx", choices=["ofx", "reference"])
+    ap.add_argument("--also", default="c2,c1", help="extra workloads reported under 'also' (N=1 only); '' = none")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-planes", type=int, default=0, help="x-planes in the CPU sample (0 = auto)")
+    return ap.parse_args()
+
+
+def hbm_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except Exception:
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+def cpu_baseline(w, n_steps, n_planes=0, n_frames=4):
+    """The CPU oracle (port of the reference CPU path: cached skin -> deform -> integrate CPU
+    branch) on a bounded sample: a centred slab of x-planes of the SAME volume, steady state
+    (skin cached, as WarpField.skin_tsdf does), all host cores via OpenMP."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle as O
+    O.build()
+    cores = os.cpu_count() or 1
+    Dx, Dy, Dz = w.dims
+    if n_planes <= 0:
+        n_planes = max(1, min(Dx, int(6e6 // (Dy * Dz)) or 1))      # ~6 M voxels: seconds of CPU work
+    x0 = (Dx - n_planes) // 2
+    ov = O.OracleVolume((n_planes, Dy, Dz), w.origin, w.voxel_size, w.intr, w.trunc, x0=x0)
+    ov.set_graph(w.nodes, w.coverage, w.K)
+    ov.integrate(w.frame(0), True)
+    t0 = time.perf_counter()
+    ov.skin_tsdf()
+    t_skin = time.perf_counter() - t0
+    frames = [w.frame(1 + i) for i in range(n_frames)]
+    ests = [w.estimate(1 + i) for i in range(n_frames)]
+    Ts = [O.origin_translations(e["node_rotations"], e["node_translations"], w.nodes) for e in ests]
+    def one(i):
+        t0 = time.perf_counter()
+        ov.set_transforms(ests[i]["node_rotations"], Ts[i])
+        n = ov.integrate(frames[i], False)
+        return time.perf_counter() - t0, n
+
+    # pick the thread count that is fastest on this host (more threads is not always faster:
+    # cgroup-limited containers and memory-bound loops), then time n_steps frames with it
+    avail = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else cores
+    cands = sorted({1, 2, 4, 8, 16, 32, avail // 2, avail} & set(range(1, avail + 1)))
+    trial = {}
+    one(0)
+    for nt in cands:
+        O.set_threads(nt)
+        one(0)
+        trial[nt] = min(one(1)[0], one(2)[0])
+    best = min(trial, key=trial.get)
+    O.set_threads(best)
+    cores = best
+    times, upd = [], []
+    for s in range(n_steps):
+        dt, n = one(s % n_frames)
+        times.append(dt); upd.append(n)
+    t = float(np.mean(times))
+    n_upd = float(np.mean(upd))
+    return {"value": n_upd / t, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"oracle (C/OpenMP port of tsdf.py:442-494 + warpfield.py deform, cached skin) on x-planes "
+                      f"[{x0},{x0 + n_planes}) of {w.name} {Dx}x{Dy}x{Dz} = {n_planes * Dy * Dz} voxels, "
+                      f"{n_steps} frames, {n_upd:.0f} updates/frame, {t * 1e3:.1f} ms/frame "
+                      f"(one-off KNN skin of the slab: {t_skin:.1f} s, not in value); OpenMP threads tried "
+                      f"{ {k: round(v * 1e3, 1) for k, v in trial.items()} } ms -> {best} used of {avail} available",
+            "ms_per_frame_sample": t * 1e3, "voxels_visited_per_s": n_planes * Dy * Dz / t}
+
+
+# ------------------------------------------------------------------------------------------------
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path (here the oracle port:
+    the reference is Python and /root/reference does not exist on the GPU box), all host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload(args.workload)
+    cb = cpu_baseline(w, max(1, args.steps), args.cpu_planes)
+    ms = cb["ms_per_frame_sample"]
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32 (f64 projection/TSDF average)", "data": "synthetic",
+            "config": workload_config(w, args.gpus), "cpu_baseline": cb,
+            "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(w, n_gpus):
+    return {"workload": f"{w.name}: {w.dims[0]}x{w.dims[1]}x{w.dims[2]} voxels @ {w.voxel_size * 1e3:.2f} mm, "
+                        f"{w.W}x{w.H} synthetic depth+colour, {w.M} nodes, K={w.K}, scene={w.scene}, warped frames, "
+                        f"steady state (graph unchanged)",
+            "sharding": f"x-plane blocks of 4 dealt round-robin over {n_gpus} GPU(s)" if n_gpus > 1 else "single GPU",
+            "l2": "volume state > L2 and a 256 MiB buffer is written between timed steps"}
+
+
+# ------------------------------------------------------------------------------------------------
+def bench_workload(name, args, rank, world, device, with_e2e=True):
+    """Returns a dict of measurements for one workload on this rank's shard (max over ranks applied)."""
+    import torch
+    import torch.distributed as dist
+    from occlusionfusion_b200 import TSDFVolume, WarpField, _capi
+    from occlusionfusion_b200.sharded import CudaShard, ShardedFusion, default_x_block
+    from occlusionfusion_b200.synthetic import Workload
+
+    w = Workload(name)
+    xb = default_x_block(w.dims[0], world)
+    vol = TSDFVolume(w.bbox, w.max_depth, w.intr, w.fopt, None, device=device, shard=rank, n_shards=world, x_block=xb)
+    wf = WarpField(w.graph(), vol, None)
+    vol.warpfield = wf
+    sf = ShardedFusion(CudaShard(vol), w.dims, rank, world, xb, device)
+    n_frames = 4
+    frames = [w.frame(i) for i in range(n_frames + 1)] if rank == 0 else [None] * (n_frames + 1)
+    ests = [w.estimate(i) for i in range(1, n_frames + 1)]
+    H, W = w.H, w.W
+
+    # source frame + graph
+    if rank == 0:
+        sf._ensure_packet(H, W)
+    sf.set_graph(w.nodes if rank == 0 else None, w.coverage, w.K)
+    if rank == 0:
+        sf.fill_packet(frames[0], np.tile(np.eye(3, dtype=np.float32), (w.M, 1, 1)), np.zeros((w.M, 3), np.float32))
+    sf.step(H, W, identity_warp=True)
+    wf._graph_key = (id(wf.graph.nodes), w.M, w.K, float(w.coverage))      # graph already on the device
+    n_active = None
+
+    # device-resident frame packets (inputs in HBM before the timed region)
+    packets = []
+    for i in range(n_frames):
+        if rank == 0:
+            wf.rotations = ests[i]["node_rotations"]
+            T = -np.einsum("nij,nj->ni", ests[i]["node_rotations"], w.nodes) + w.nodes + ests[i]["node_translations"]
+            sf.fill_packet(frames[i + 1], ests[i]["node_rotations"], T)
+        torch.cuda.synchronize(device)
+        packets.append(sf.buf.clone())
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)
+    stream = torch.cuda.current_stream(device)
+
+    def one_step(i, ev0, ev1, kev0=None, kev1=None):
+        flush.fill_(i & 0xFF)                                  # evict the volume lines from L2
+        sf.buf.copy_(packets[i % n_frames])                    # rank 0's packet for this frame (device copy, untimed)
+        ev0.record(stream)
+        if world > 1:
+            dist.broadcast(sf.buf, src=0)
+        v = sf.views
+        sf.be.set_transforms(v["R"], v["T"])
+        if kev0 is not None:
+            kev0.record(stream)
+        st = sf.be.integrate(v["depth"], v["colour"], False, 1.0)
+        if kev1 is not None:
+            kev1.record(stream)
+        if world > 1:
+            out = torch.empty((world, 4), dtype=torch.int64, device=device)
+            dist.all_gather_into_tensor(out, st)
+        ev1.record(stream)
+        return st
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(device)
+
+    mk = lambda: torch.cuda.Event(enable_timing=True)
+    for i in range(max(3, args.warmup)):
+        one_step(i, mk(), mk())
+    barrier()
+    K = args.steps
+    evs = [(mk(), mk(), mk(), mk()) for _ in range(K)]
+    upd_total = 0
+    sampler = ClockSampler(device.index or 0)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    t_wall0 = time.perf_counter()
+    stats_acc = torch.zeros(4, dtype=torch.int64, device=device)
+    for i in range(K):
+        st = one_step(i, *evs[i])
+        stats_acc += st
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    clocks = sampler.stop() if rank == 0 else None
+    step_ms = sum(a.elapsed_time(b) for a, b, _, _ in evs)
+    kern_ms = sum(c.elapsed_time(d) for _, _, c, d in evs)
+    tot = torch.tensor([step_ms, kern_ms], dtype=torch.float64, device=device)
+    cnt = stats_acc.clone()
+    if world > 1:
+        dist.all_reduce(tot, op=dist.ReduceOp.MAX)
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+    step_ms, kern_ms = float(tot[0]) / K, float(tot[1]) / K
+    upd = float(cnt[_capi.STAT_UPDATED]) / K
+    valid = float(cnt[_capi.STAT_SKIN_VALID]) / K
+    bricks = float(cnt[_capi.STAT_BRICKS]) / K
+    local_upd = float(stats_acc[_capi.STAT_UPDATED]) / K
+    res = dict(workload=w, ms_per_step=step_ms, kernel_ms=kern_ms, updated=upd, skin_valid=valid, bricks=bricks,
+               value=upd / (step_ms * 1e-3), wall_ms_per_step=t_wall * 1e3 / K, clocks=clocks,
+               local_updated=local_upd, launches_per_step=2)
+    # roofline of the fused kernel on this rank's shard (rank 0 reports its own shard)
+    alg_bytes = 24.0 * local_upd + 8.0 * H * W + 60.0 * w.M
+    res["alg_bytes"] = alg_bytes
+    res["achieved_gbs"] = alg_bytes / (float(kern_ms_local(evs, K)) * 1e-3) / 1e9
+    res["kernel_ms_local"] = kern_ms_local(evs, K)
+
+    # ---- e2e: public API, host buffers, H2D + D2H inside the timed region ------------------------
+    if with_e2e:
+        res["e2e"] = bench_e2e(w, vol, wf, sf, frames, ests, args, rank, world, device)
+    del vol, wf, sf, packets, flush
+    torch.cuda.empty_cache()
+    return res
+
+
+def kern_ms_local(evs, K):
+    return sum(c.elapsed_time(d) for _, _, c, d in evs) / K
+
+
+def bench_e2e(w, vol, wf, sf, frames, ests, args, rank, world, device):
+    """Per step, through the public classes: rank 0 takes the HOST frame + the estimator dict,
+    WarpField.update_transformations (host numpy), H2D of RGB+Z (pinned staging) and of R,T;
+    [N>1: one NCCL broadcast]; fused kernel; counters read back to the host."""
+    import torch
+    import torch.distributed as dist
+    n_frames = len(ests)
+    K, Wm = args.steps, max(3, args.warmup)
+    H, W = w.H, w.W
+    fid = [vol.frame_id]
+    wf.frame_id = vol.frame_id           # the warp field follows the volume's frame counter (warpfield.py:399)
+
+    def step(i):
+        est = dict(ests[i % n_frames])
+        fid[0] += 1
+        est["target_frame_id"] = fid[0]
+        if world == 1:
+            wf.update_transformations(est)
+            vol.integrate({"im": frames[1 + i % n_frames], "id": fid[0]})
+            return vol.last_stats()["updated"]
+        if rank == 0:
+            wf.frame_id = vol.frame_id
+            wf.update_transformations(est)
+            sf.fill_packet(frames[1 + i % n_frames], wf.rotations, wf.translations)
+        else:
+            vol.frame_id = fid[0]
+        out = sf.step(H, W, identity_warp=False)
+        return int(out[:, 0].sum().item())
+
+    for i in range(Wm):
+        step(i)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(device)
+    t0 = time.perf_counter()
+    upd = 0
+    for i in range(K):
+        upd += step(i)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(device)
+    dt = time.perf_counter() - t0
+    tmax = torch.tensor([dt], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    dt = float(tmax[0])
+    h2d = 4 * 4 * H * W + 48 * w.M
+    return {"value": upd / dt, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 32 * world,
+            "ms_per_step": dt * 1e3 / K, "timing": "host wall clock around K steps (includes host numpy + sync per step)"}
+
+
+# ------------------------------------------------------------------------------------------------
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return run_reference(args)
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the hot path has no CPU fallback (use --impl reference for the CPU arm)")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    device = torch.device("cuda", local)
+    torch.cuda.set_device(device)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+    from occlusionfusion_b200.synthetic import Workload
+
+    main_res = bench_workload(args.workload, args, rank, world, device)
+    also = {}
+    if world == 1 and args.also:
+        for name in [n for n in args.also.split(",") if n and n != args.workload]:
+            r = bench_workload(name, args, rank, world, device, with_e2e=True)
+            also[name] = {"value": r["value"], "unit": UNIT, "ms_per_step": r["ms_per_step"],
+                          "kernel_ms": r["kernel_ms_local"], "updated_per_frame": r["updated"],
+                          "skin_valid_per_frame": r["skin_valid"], "bricks_per_frame": r["bricks"],
+                          "voxels": int(np.prod(r["workload"].dims)),
+                          "achieved_gbs": r["achieved_gbs"], "e2e": r["e2e"],
+                          "config": workload_config(r["workload"], world)}
+    cb = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cb = cpu_baseline(Workload(args.workload), 6, args.cpu_planes)
+    if rank == 0:
+        w = main_res["workload"]
+        peak, peak_src = hbm_peak()
+        line = {
+            "metric": METRIC, "value": main_res["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": main_res["ms_per_step"], "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32 (f64 projection/TSDF average)", "data": "synthetic",
+            "config": workload_config(w, world),
+            "voxels": int(np.prod(w.dims)), "updated_per_frame": main_res["updated"],
+            "skin_valid_per_frame": main_res["skin_valid"], "bricks_per_frame": main_res["bricks"],
+            "voxels_visited_per_s": float(np.prod(w.dims)) / (main_res["ms_per_step"] * 1e-3),
+            "wall_ms_per_step": main_res["wall_ms_per_step"],
+            "e2e": main_res["e2e"], "gpu_launches": main_res["launches_per_step"] * args.steps,
+            "clocks": main_res["clocks"],
+            "roofline": {"bound": "hbm", "achieved": main_res["achieved_gbs"], "peak": peak, "unit": "GB/s",
+                         "frac": main_res["achieved_gbs"] / peak, "traffic": None, "peak_source": peak_src,
+                         "kernel": "fused_brick_kernel<K,VEC,WARPED>", "kernel_ms": main_res["kernel_ms_local"],
+                         "algorithmic_bytes_per_launch": main_res["alg_bytes"],
+                         "bytes_formula": "24*N_updated(this GPU) + 8*W*H + 60*M"},
+            "cpu_baseline": cb, "also": also,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,188 @@
+"""Multi-GPU fusion: the volume is split into x-plane shards, one process per GPU
+(`torch.distributed`, NCCL over NVLink/NVSwitch).  Voxels are independent given the frame
+(SURVEY.md section 8e): no halo, no data-path collective.  Per frame there is exactly
+
+    1 broadcast   of the frame packet  [R (M,9) | T (M,3) | packed colour (H,W) | depth (H,W)]
+                  = 48*M + 8*H*W bytes, from rank 0 (the rank that receives the camera frame and
+                  the estimator's node transforms)
+    1 all-gather  of OFX_N_STATS int64 counters per shard ("slab statistics")
+
+and, only when the graph changes (node insertion), one more broadcast of the node table.
+
+Shards are blocks of `x_block` planes dealt round-robin (default 4 = one brick): the view
+frustum is a pyramid inside its bounding box, so contiguous slabs would leave the outer GPUs
+nearly idle; dealt blocks give every GPU the same share of in-frustum bricks.
+
+The reference has no multi-device path at all; this module is new.
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+N_STATS = 4
+
+
+def plane_map(Dx, n_shards, shard, x_block):
+    """Global x index of each local plane of `shard` (same formula as include/ofx.h)."""
+    assert Dx % (x_block * n_shards) == 0, "Dx must be a multiple of x_block * n_shards"
+    lx = np.arange(Dx // n_shards)
+    return (lx // x_block) * x_block * n_shards + shard * x_block + lx % x_block
+
+
+def default_x_block(Dx, n_shards, brick_x=4):
+    """Smallest brick-aligned block that divides the volume evenly; falls back to contiguous slabs."""
+    if Dx % (brick_x * n_shards) == 0:
+        return brick_x
+    return Dx // n_shards
+
+
+class FramePacket:
+    """Layout of the one buffer broadcast per frame (float32 words)."""
+
+    def __init__(self, M, H, W):
+        self.M, self.H, self.W = int(M), int(H), int(W)
+        self.o_R = 0
+        self.o_T = self.o_R + 9 * self.M
+        self.o_colour = -(-(self.o_T + 3 * self.M) // 4) * 4          # 16-byte aligned images
+        self.o_depth = self.o_colour + self.H * self.W
+        self.numel = self.o_depth + self.H * self.W
+
+    @property
+    def nbytes(self):
+        return 4 * self.numel
+
+    def alloc(self, device):
+        return torch.zeros(self.numel, dtype=torch.float32, device=device)
+
+    def views(self, buf):
+        M, H, W = self.M, self.H, self.W
+        return dict(R=buf[self.o_R:self.o_R + 9 * M].view(M, 3, 3), T=buf[self.o_T:self.o_T + 3 * M].view(M, 3),
+                    colour=buf[self.o_colour:self.o_colour + H * W].view(H, W),
+                    depth=buf[self.o_depth:self.o_depth + H * W].view(H, W))
+
+
+class ShardedFusion:
+    """Drives one shard per rank.  `shard_backend` owns the shard's volume and implements
+        set_graph(nodes (M,3) tensor, coverage, K), set_transforms(R, T tensors),
+        integrate(depth, colour tensors, identity_warp, obs_weight) -> stats tensor int64[N_STATS],
+        pack_frame(im) -> (colour, depth) tensors            [rank 0 only]
+        get_volume() -> (tsdf, colour, weight) numpy arrays of the local planes
+    The CUDA backend is `CudaShard` below; CPU tests inject an oracle-backed stand-in."""
+
+    def __init__(self, shard_backend, dims, rank, world, x_block, device, group=None):
+        self.be, self.dims = shard_backend, tuple(int(d) for d in dims)
+        self.rank, self.world, self.x_block = int(rank), int(world), int(x_block)
+        self.device, self.group = device, group
+        self.planes = plane_map(self.dims[0], self.world, self.rank, self.x_block)
+        self.packet = self.buf = None
+        self.M = 0
+
+    # -- graph (rare) ----------------------------------------------------------------------------
+    def set_graph(self, nodes, coverage, K):
+        """rank 0 passes the node table (others may pass None); every rank ends up with it."""
+        meta = torch.zeros(3, dtype=torch.float64, device=self.device)
+        if self.rank == 0:
+            meta[0], meta[1], meta[2] = len(nodes), float(coverage), int(K)
+        if self.world > 1:
+            dist.broadcast(meta, src=0, group=self.group)
+        M, coverage, K = int(meta[0].item()), float(meta[1].item()), int(meta[2].item())
+        nd = torch.empty((M, 3), dtype=torch.float32, device=self.device)
+        if self.rank == 0:
+            nd.copy_(torch.as_tensor(np.ascontiguousarray(nodes, dtype=np.float32)))
+        if self.world > 1:
+            dist.broadcast(nd, src=0, group=self.group)
+        self.M, self.coverage, self.K = M, coverage, K
+        self.be.set_graph(nd, coverage, K)
+        self.packet = None
+        return nd
+
+    # -- per frame -------------------------------------------------------------------------------
+    def _ensure_packet(self, H, W):
+        if self.packet is None or (self.packet.H, self.packet.W, self.packet.M) != (H, W, self.M):
+            self.packet = FramePacket(self.M, H, W)
+            self.buf = self.packet.alloc(self.device)
+            self.views = self.packet.views(self.buf)
+
+    def fill_packet(self, im, R, T):
+        """rank 0: stage the frame (packed on the device) and the node transforms into the packet."""
+        H, W = im.shape[-2:]
+        self._ensure_packet(H, W)
+        colour, depth = self.be.pack_frame(im)
+        self.views["colour"].copy_(colour)
+        self.views["depth"].copy_(depth)
+        self.views["R"].copy_(torch.as_tensor(np.ascontiguousarray(R, dtype=np.float32)), non_blocking=True)
+        self.views["T"].copy_(torch.as_tensor(np.ascontiguousarray(T, dtype=np.float32)), non_blocking=True)
+
+    def step(self, H, W, identity_warp=False, obs_weight=1.0, gather_stats=True):
+        """Broadcast the packet rank 0 filled, integrate the local shard, all-gather the counters.
+        Returns an int64 tensor (world, N_STATS) (or the local (N_STATS,) when gather_stats=False)."""
+        self._ensure_packet(H, W)
+        if self.world > 1:
+            dist.broadcast(self.buf, src=0, group=self.group)
+        v = self.views
+        if not identity_warp:
+            self.be.set_transforms(v["R"], v["T"])
+        stats = self.be.integrate(v["depth"], v["colour"], identity_warp, obs_weight)
+        if not gather_stats:
+            return stats
+        if self.world == 1:
+            return stats.view(1, N_STATS)
+        out = torch.empty((self.world, N_STATS), dtype=torch.int64, device=self.device)
+        dist.all_gather_into_tensor(out, stats.contiguous(), group=self.group)
+        return out
+
+    # -- output (not per frame) ------------------------------------------------------------------
+    def gather_volume(self):
+        """Full (Dx,Dy,Dz) volumes on rank 0 (None elsewhere): undoes the dealt-block plane mapping."""
+        local = [np.ascontiguousarray(a) for a in self.be.get_volume()]
+        if self.world == 1:
+            full = []
+            for a in local:
+                f = np.empty(self.dims, np.float32)
+                f[self.planes] = a
+                full.append(f)
+            return tuple(full)
+        gathered = [None] * self.world if self.rank == 0 else None
+        dist.gather_object((self.planes, local), gathered, dst=0, group=self.group)
+        if self.rank != 0:
+            return None
+        full = [np.empty(self.dims, np.float32) for _ in range(3)]
+        for planes, arrs in gathered:
+            for f, a in zip(full, arrs):
+                f[planes] = a
+        return tuple(full)
+
+
+class CudaShard:
+    """shard backend over a TSDFVolume handle: raw C-ABI calls on device tensors (no host hops)."""
+
+    def __init__(self, tsdf_volume):
+        from . import _capi
+        self._capi, self.vol = _capi, tsdf_volume
+        self.lib, self.dev = _capi.load(), tsdf_volume.device
+        self.stats = torch.zeros(N_STATS, dtype=torch.int64, device=self.dev)
+
+    def _s(self):
+        return self._capi.stream_ptr(self.dev)
+
+    def set_graph(self, nodes, coverage, K):
+        c = self._capi
+        c.check(self.lib.ofx_set_graph(self.vol._h, c.ptr(nodes.contiguous()), nodes.shape[0], float(coverage), int(K), self._s()))
+
+    def set_transforms(self, R, T):
+        c = self._capi
+        c.check(self.lib.ofx_set_transforms(self.vol._h, c.ptr(R), c.ptr(T), self._s()))
+
+    def pack_frame(self, im):
+        self.vol.update(im, getattr(self.vol, "frame_id", -self.vol.fopt.skip_rate) + self.vol.fopt.skip_rate)
+        return self.vol._color_im_dev, self.vol._depth_im_dev
+
+    def integrate(self, depth, colour, identity_warp, obs_weight):
+        c = self._capi
+        H, W = depth.shape
+        c.check(self.lib.ofx_integrate(self.vol._h, c.ptr(depth), c.ptr(colour), H, W, self.vol._intr4, float(obs_weight),
+                                       int(identity_warp), c.ptr(self.stats), self._s()))
+        return self.stats
+
+    def get_volume(self):
+        return self.vol.get_volume()

@@ -44,6 +44,8 @@ def _load():
     lib.ofx_oracle_warp.argtypes = [_f32p, C.c_int64, _i32p, _f32p, _u8p, C.c_int, _f32p, _f32p, _f32p]
     lib.ofx_oracle_check_visibility.argtypes = [_f32p, C.c_int64, _f32p, C.c_int, C.c_int, _f64p,
                                                 C.c_double, _u8p, _f64p]
+    lib.ofx_oracle_set_threads.argtypes = [C.c_int]
+    lib.ofx_oracle_max_threads.restype = C.c_int
     lib.ofx_oracle_integrate.restype = C.c_int64
     lib.ofx_oracle_integrate.argtypes = [_f32p, _f32p, _f32p, C.c_int64, _f32p, _u8p, _f32p, _f32p,
                                          C.c_int, C.c_int, _f64p, C.c_double, C.c_double]
@@ -58,6 +60,14 @@ def lib():
     if _lib is None:
         _lib = _load()
     return _lib
+
+
+def set_threads(n):
+    lib().ofx_oracle_set_threads(int(n))
+
+
+def max_threads():
+    return int(lib().ofx_oracle_max_threads())
 
 
 def _c(a, dt):
