@@ -1,0 +1,249 @@
+// ofx_brick.cuh -- device code shared by the brick kernels of ofx_integrate.cu: argument structs,
+// the per-voxel warp (cached anchors -> weights -> linear blend), brick-level frustum culling and
+// the per-thread body (4 consecutive z voxels: warp, project, test, fuse, store).
+#pragma once
+#include "ofx_volume.cuh"
+
+namespace ofx {
+
+enum Mode { MODE_WARPED = 0, MODE_IDENTITY = 1, MODE_DEFORM = 2 };
+
+struct FrameArgs {
+    const float *depth;
+    const float *colour_im;
+    Camera cam;
+    double trunc, rtrunc, obs;   // rtrunc = RN(1/trunc)
+    float obsf;
+};
+
+struct GraphArgs {
+    const float *node_rec;
+    const int *active;       // work list (MODE_WARPED) or nullptr (all bricks)
+    const int *off;
+    const int *cnt;
+    const int *brick_nodes;
+    const uint8_t *cache;
+    float cutoff, denom;
+};
+
+// Node records sit in shared memory at a stride of 20 floats (80 B): consecutive records start
+// 20 banks apart, so the eight float4 loads of a quarter-warp hit eight distinct 4-bank groups.
+constexpr int REC_STRIDE = 20;
+
+template <int K>
+__device__ __forceinline__ void warp_voxel(const uint32_t (&ids)[2], const float *__restrict__ s_rec, float denom,
+                                           float rdenom, float px, float py, float pz, float &qx, float &qy, float &qz)
+{
+    const float *rec[K];
+    float bd[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        const uint32_t id = (ids[k >> 2] >> (8 * (k & 3))) & 0xFFu;
+        rec[k] = s_rec + id * REC_STRIDE;
+        const float4 g4 = *reinterpret_cast<const float4 *>(rec[k]);
+        bd[k] = dist2(px, py, pz, g4.x, g4.y, g4.z);
+    }
+    float w[K];
+    skin_weights_valid<K>(bd, denom, rdenom, w);       // cached voxel: all K anchors are inside the cutoff
+    float ax = 0.f, ay = 0.f, az = 0.f;
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        if (w[k] == 0.0f) continue;                                  // warpfield.py:219
+        float r12[12];
+        const float4 a = *reinterpret_cast<const float4 *>(rec[k] + 4);
+        const float4 b = *reinterpret_cast<const float4 *>(rec[k] + 8);
+        const float4 c = *reinterpret_cast<const float4 *>(rec[k] + 12);
+        r12[0] = a.x; r12[1] = a.y; r12[2] = a.z; r12[3] = a.w; r12[4] = b.x; r12[5] = b.y; r12[6] = b.z; r12[7] = b.w;
+        r12[8] = c.x; r12[9] = c.y; r12[10] = c.z; r12[11] = c.w;
+        lbs_accumulate(r12, w[k], px, py, pz, ax, ay, az);
+    }
+    qx = ax; qy = ay; qz = az;
+}
+
+// ---- brick-level frustum culling -------------------------------------------------------------------
+// Every voxel p of a brick lies within h of the brick centre c, rotations preserve distances,
+// and the blend weights are non-negative with sum sigma in (0, 1]: the warped voxel is
+// sigma * (a point of the convex hull of the balls B(R_k c + T_k, h) over the brick's nodes).
+// Perspective projection is invariant under the positive scale sigma and maps convex sets in
+// z > 0 to convex sets, so the pixel bounding box of those balls bounds every voxel's pixel.
+// A brick whose box misses the image (1 px margin) cannot update anything and is skipped
+// before it reads a byte.  Returns the bounds of ONE ball; the caller reduces over the nodes.
+struct PixBox {
+    float u_lo, u_hi, v_lo, v_hi, z_lo;
+    int unbounded;
+};
+
+__device__ __forceinline__ PixBox ball_pixbox(float bx, float by, float bz, float h, const Camera &cam)
+{
+    PixBox b;
+    const float z_lo = bz - h, z_hi = bz + h;
+    b.z_lo = z_lo;
+    b.unbounded = !(z_lo > 1e-4f);
+    const float xl = bx - h, xh = bx + h, yl = by - h, yh = by + h;
+    const float zl = b.unbounded ? 1.f : z_lo;
+    b.u_lo = cam.fx * (xl / (xl >= 0.f ? z_hi : zl)) + cam.cx;
+    b.u_hi = cam.fx * (xh / (xh >= 0.f ? zl : z_hi)) + cam.cx;
+    b.v_lo = cam.fy * (yl / (yl >= 0.f ? z_hi : zl)) + cam.cy;
+    b.v_hi = cam.fy * (yh / (yh >= 0.f ? zl : z_hi)) + cam.cy;
+    return b;
+}
+
+__device__ __forceinline__ void brick_centre(const VolumeGeom &g, const BrickCoord &bc, float &cx, float &cy, float &cz,
+                                             float &h)
+{
+    const int lx1 = min(bc.lx0 + BX, g.nx) - 1, iy1 = min(bc.iy0 + BY, g.Dy) - 1, iz1 = min(bc.iz0 + BZ, g.Dz) - 1;
+    float x_lo = __ldg(g.px + bc.lx0), x_hi = x_lo;
+    for (int lx = bc.lx0 + 1; lx <= lx1; ++lx) { const float x = __ldg(g.px + lx); x_lo = fminf(x_lo, x); x_hi = fmaxf(x_hi, x); }
+    const float y_lo = __ldg(g.py + bc.iy0), y_hi = __ldg(g.py + iy1), z_lo = __ldg(g.pz + bc.iz0), z_hi = __ldg(g.pz + iz1);
+    cx = 0.5f * (x_lo + x_hi); cy = 0.5f * (y_lo + y_hi); cz = 0.5f * (z_lo + z_hi);
+    const float hx = 0.5f * (x_hi - x_lo), hy = 0.5f * (y_hi - y_lo), hz = 0.5f * (z_hi - z_lo);
+    h = sqrtf(hx * hx + hy * hy + hz * hz) * 1.001f + 1e-5f;
+}
+
+// warp 0 only: true when no voxel of the brick can project into the image
+__device__ __forceinline__ bool brick_outside_frustum(const VolumeGeom &g, const BrickCoord &bc, const float *s_rec,
+                                                      int n_used, bool identity, const Camera &cam)
+{
+    float cx, cy, cz, h;
+    brick_centre(g, bc, cx, cy, cz, h);
+    const int lane = threadIdx.x & 31;
+    float u_lo = 3.0e38f, u_hi = -3.0e38f, v_lo = 3.0e38f, v_hi = -3.0e38f;
+    int unbounded = 0;
+    const int n = identity ? 1 : n_used;
+    for (int i = lane; i < n; i += 32) {
+        float bx = cx, by = cy, bz = cz;
+        if (!identity) {
+            const float *r = s_rec + i * REC_STRIDE + 4;
+            bx = r[0] * cx + r[1] * cy + r[2] * cz + r[9];
+            by = r[3] * cx + r[4] * cy + r[5] * cz + r[10];
+            bz = r[6] * cx + r[7] * cy + r[8] * cz + r[11];
+        }
+        const PixBox b = ball_pixbox(bx, by, bz, h, cam);
+        unbounded |= b.unbounded;
+        u_lo = fminf(u_lo, b.u_lo); u_hi = fmaxf(u_hi, b.u_hi);
+        v_lo = fminf(v_lo, b.v_lo); v_hi = fmaxf(v_hi, b.v_hi);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        unbounded |= __shfl_xor_sync(0xffffffffu, unbounded, o);
+        u_lo = fminf(u_lo, __shfl_xor_sync(0xffffffffu, u_lo, o));
+        u_hi = fmaxf(u_hi, __shfl_xor_sync(0xffffffffu, u_hi, o));
+        v_lo = fminf(v_lo, __shfl_xor_sync(0xffffffffu, v_lo, o));
+        v_hi = fmaxf(v_hi, __shfl_xor_sync(0xffffffffu, v_hi, o));
+    }
+    if (unbounded) return false;
+    // pixel u is accepted when rint(u) in [0, W): u in [-0.5, W-0.5); keep a 1 px margin
+    return u_hi < -1.5f || u_lo > (float)cam.W + 0.5f || v_hi < -1.5f || v_lo > (float)cam.H + 0.5f;
+}
+
+
+// ---- per-thread body ---------------------------------------------------------------------------------
+// Thread t of a brick owns voxels (lx0 + t/64, iy0 + (t/8)%8, iz0 + 4*(t%8) .. +3).  Counters are
+// accumulated into c_upd / c_valid / c_wsum (the caller reduces them).
+template <int K, bool VEC, int MODE>
+__device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__restrict__ tsdf,
+                                                  float *__restrict__ weight, float *__restrict__ colour,
+                                                  const GraphArgs &ga, const FrameArgs &fa,
+                                                  const float *__restrict__ s_rec, const BrickCoord &bc, int n_used,
+                                                  float rdenom, int t, float *__restrict__ out_pts,
+                                                  uint8_t *__restrict__ out_valid, unsigned &c_upd, unsigned &c_valid,
+                                                  unsigned &c_wsum)
+{
+    const int tz = t & 7, ty = (t >> 3) & 7, tx = t >> 6;
+    const int lx = bc.lx0 + tx, iy = bc.iy0 + ty, iz0 = bc.iz0 + tz * VOX_PER_THREAD;
+    const bool row_live = lx < g.nx && iy < g.Dy && iz0 < g.Dz;
+    if (!row_live) return;
+    const int64_t vox0 = ((int64_t)lx * g.Dy + iy) * g.Dz + iz0;
+    const int n_vox = min(VOX_PER_THREAD, g.Dz - iz0);
+
+    // anchor-cache words of this thread's voxels
+    uint32_t ids[VOX_PER_THREAD][2];
+#pragma unroll
+    for (int e = 0; e < VOX_PER_THREAD; ++e) ids[e][0] = ids[e][1] = 0xFFFFFFFFu;
+    if constexpr (MODE != MODE_IDENTITY) {
+        if (n_used > 0) {
+            if constexpr (K <= 4) {
+                const uint32_t *c = reinterpret_cast<const uint32_t *>(ga.cache) + vox0;
+                if (VEC) {
+                    const uint4 q = __ldg(reinterpret_cast<const uint4 *>(c));
+                    ids[0][0] = q.x; ids[1][0] = q.y; ids[2][0] = q.z; ids[3][0] = q.w;
+                } else {
+                    for (int e = 0; e < n_vox; ++e) ids[e][0] = __ldg(c + e);
+                }
+            } else {
+                const uint2 *c = reinterpret_cast<const uint2 *>(ga.cache) + vox0;
+                for (int e = 0; e < n_vox; ++e) {
+                    const uint2 q = __ldg(c + e);
+                    ids[e][0] = q.x; ids[e][1] = q.y;
+                }
+            }
+        }
+    }
+    const float px = __ldg(g.px + lx), py = __ldg(g.py + iy);
+
+    unsigned upd = 0;
+    double diff[VOX_PER_THREAD];
+    float ncol[VOX_PER_THREAD];
+#pragma unroll
+    for (int e = 0; e < VOX_PER_THREAD; ++e) {
+        if (e >= n_vox) continue;
+        const float pz = __ldg(g.pz + iz0 + e);
+        float qx = px, qy = py, qz = pz;
+        bool skin_ok = true;                                          // source frame: all valid, tsdf.py:395-398
+        if constexpr (MODE != MODE_IDENTITY) {
+            skin_ok = (ids[e][0] & 0xFFu) != 0xFFu;
+            if (skin_ok) warp_voxel<K>(ids[e], s_rec, ga.denom, rdenom, px, py, pz, qx, qy, qz);
+        }
+        if constexpr (MODE == MODE_DEFORM) {
+            if (out_pts) { out_pts[3 * (vox0 + e)] = qx; out_pts[3 * (vox0 + e) + 1] = qy; out_pts[3 * (vox0 + e) + 2] = qz; }
+            if (out_valid) out_valid[vox0 + e] = skin_ok ? 1 : 0;
+        } else {
+            if (!skin_ok) continue;                                   // tsdf.py:464
+            ++c_valid;
+            int u, v;
+            if (!project(qx, qy, qz, fa.cam, u, v)) continue;         // tsdf.py:589-593
+            const int64_t pix = (int64_t)v * fa.cam.W + u;
+            const double d = (double)__ldg(fa.depth + pix);
+            const double df = d - (double)qz;                         // tsdf.py:608
+            if (!(d > 0.0 && df >= -fa.trunc)) continue;              // tsdf.py:609
+            diff[e] = df;
+            ncol[e] = __ldg(fa.colour_im + pix);
+            upd |= 1u << e;
+        }
+    }
+
+    if constexpr (MODE != MODE_DEFORM) {
+        if (!upd) return;
+        float tt[VOX_PER_THREAD], ww[VOX_PER_THREAD], cc[VOX_PER_THREAD];
+        if (VEC) {
+            const float4 t4 = *reinterpret_cast<const float4 *>(tsdf + vox0);
+            const float4 w4 = *reinterpret_cast<const float4 *>(weight + vox0);
+            const float4 c4 = *reinterpret_cast<const float4 *>(colour + vox0);
+            tt[0] = t4.x; tt[1] = t4.y; tt[2] = t4.z; tt[3] = t4.w;
+            ww[0] = w4.x; ww[1] = w4.y; ww[2] = w4.z; ww[3] = w4.w;
+            cc[0] = c4.x; cc[1] = c4.y; cc[2] = c4.z; cc[3] = c4.w;
+        } else {
+#pragma unroll
+            for (int e = 0; e < VOX_PER_THREAD; ++e)
+                if (upd & (1u << e)) { tt[e] = tsdf[vox0 + e]; ww[e] = weight[vox0 + e]; cc[e] = colour[vox0 + e]; }
+        }
+#pragma unroll
+        for (int e = 0; e < VOX_PER_THREAD; ++e)
+            if (upd & (1u << e)) {
+                fuse_voxel(tt[e], ww[e], cc[e], diff[e], ncol[e], fa.trunc, fa.rtrunc, fa.obs, fa.obsf);
+                c_wsum += (unsigned)ww[e];
+            }
+        if (VEC) {
+            *reinterpret_cast<float4 *>(tsdf + vox0) = make_float4(tt[0], tt[1], tt[2], tt[3]);
+            *reinterpret_cast<float4 *>(weight + vox0) = make_float4(ww[0], ww[1], ww[2], ww[3]);
+            *reinterpret_cast<float4 *>(colour + vox0) = make_float4(cc[0], cc[1], cc[2], cc[3]);
+        } else {
+#pragma unroll
+            for (int e = 0; e < VOX_PER_THREAD; ++e)
+                if (upd & (1u << e)) { tsdf[vox0 + e] = tt[e]; weight[vox0 + e] = ww[e]; colour[vox0 + e] = cc[e]; }
+        }
+        c_upd += __popc(upd);
+    }
+}
+
+}  // namespace ofx

@@ -24,7 +24,7 @@ struct FrameArgs {
     const float *depth;
     const float *colour_im;
     Camera cam;
-    double trunc, obs;
+    double trunc, rtrunc, obs;   // rtrunc = RN(1/trunc)
     float obsf;
 };
 
@@ -38,22 +38,25 @@ struct GraphArgs {
     float cutoff, denom;
 };
 
+// Node records sit in shared memory at a stride of 20 floats (80 B): consecutive records start
+// 20 banks apart, so the eight float4 loads of a quarter-warp hit eight distinct 4-bank groups.
+constexpr int REC_STRIDE = 20;
+
 template <int K>
-__device__ __forceinline__ void warp_voxel(const uint32_t (&ids)[2], const float *__restrict__ s_rec, float cutoff,
-                                           float denom, float px, float py, float pz, float &qx, float &qy, float &qz)
+__device__ __forceinline__ void warp_voxel(const uint32_t (&ids)[2], const float *__restrict__ s_rec, float denom,
+                                           float rdenom, float px, float py, float pz, float &qx, float &qy, float &qz)
 {
     const float *rec[K];
     float bd[K];
 #pragma unroll
     for (int k = 0; k < K; ++k) {
         const uint32_t id = (ids[k >> 2] >> (8 * (k & 3))) & 0xFFu;
-        rec[k] = s_rec + id * NODE_REC_FLOATS;
+        rec[k] = s_rec + id * REC_STRIDE;
         const float4 g4 = *reinterpret_cast<const float4 *>(rec[k]);
         bd[k] = dist2(px, py, pz, g4.x, g4.y, g4.z);
     }
     float w[K];
-    bool in_range[K];
-    skin_weights<K>(bd, cutoff, denom, w, in_range);
+    skin_weights_valid<K>(bd, denom, rdenom, w);       // cached voxel: all K anchors are inside the cutoff
     float ax = 0.f, ay = 0.f, az = 0.f;
 #pragma unroll
     for (int k = 0; k < K; ++k) {
@@ -69,15 +72,92 @@ __device__ __forceinline__ void warp_voxel(const uint32_t (&ids)[2], const float
     qx = ax; qy = ay; qz = az;
 }
 
+// ---- brick-level frustum culling -------------------------------------------------------------------
+// Every voxel p of a brick lies within h of the brick centre c, rotations preserve distances,
+// and the blend weights are non-negative with sum sigma in (0, 1]: the warped voxel is
+// sigma * (a point of the convex hull of the balls B(R_k c + T_k, h) over the brick's nodes).
+// Perspective projection is invariant under the positive scale sigma and maps convex sets in
+// z > 0 to convex sets, so the pixel bounding box of those balls bounds every voxel's pixel.
+// A brick whose box misses the image (1 px margin) cannot update anything and is skipped
+// before it reads a byte.  Returns the bounds of ONE ball; the caller reduces over the nodes.
+struct PixBox {
+    float u_lo, u_hi, v_lo, v_hi, z_lo;
+    int unbounded;
+};
+
+__device__ __forceinline__ PixBox ball_pixbox(float bx, float by, float bz, float h, const Camera &cam)
+{
+    PixBox b;
+    const float z_lo = bz - h, z_hi = bz + h;
+    b.z_lo = z_lo;
+    b.unbounded = !(z_lo > 1e-4f);
+    const float xl = bx - h, xh = bx + h, yl = by - h, yh = by + h;
+    const float zl = b.unbounded ? 1.f : z_lo;
+    b.u_lo = cam.fx * (xl / (xl >= 0.f ? z_hi : zl)) + cam.cx;
+    b.u_hi = cam.fx * (xh / (xh >= 0.f ? zl : z_hi)) + cam.cx;
+    b.v_lo = cam.fy * (yl / (yl >= 0.f ? z_hi : zl)) + cam.cy;
+    b.v_hi = cam.fy * (yh / (yh >= 0.f ? zl : z_hi)) + cam.cy;
+    return b;
+}
+
+__device__ __forceinline__ void brick_centre(const VolumeGeom &g, const BrickCoord &bc, float &cx, float &cy, float &cz,
+                                             float &h)
+{
+    const int lx1 = min(bc.lx0 + BX, g.nx) - 1, iy1 = min(bc.iy0 + BY, g.Dy) - 1, iz1 = min(bc.iz0 + BZ, g.Dz) - 1;
+    float x_lo = __ldg(g.px + bc.lx0), x_hi = x_lo;
+    for (int lx = bc.lx0 + 1; lx <= lx1; ++lx) { const float x = __ldg(g.px + lx); x_lo = fminf(x_lo, x); x_hi = fmaxf(x_hi, x); }
+    const float y_lo = __ldg(g.py + bc.iy0), y_hi = __ldg(g.py + iy1), z_lo = __ldg(g.pz + bc.iz0), z_hi = __ldg(g.pz + iz1);
+    cx = 0.5f * (x_lo + x_hi); cy = 0.5f * (y_lo + y_hi); cz = 0.5f * (z_lo + z_hi);
+    const float hx = 0.5f * (x_hi - x_lo), hy = 0.5f * (y_hi - y_lo), hz = 0.5f * (z_hi - z_lo);
+    h = sqrtf(hx * hx + hy * hy + hz * hz) * 1.001f + 1e-5f;
+}
+
+// warp 0 only: true when no voxel of the brick can project into the image
+__device__ __forceinline__ bool brick_outside_frustum(const VolumeGeom &g, const BrickCoord &bc, const float *s_rec,
+                                                      int n_used, bool identity, const Camera &cam)
+{
+    float cx, cy, cz, h;
+    brick_centre(g, bc, cx, cy, cz, h);
+    const int lane = threadIdx.x & 31;
+    float u_lo = 3.0e38f, u_hi = -3.0e38f, v_lo = 3.0e38f, v_hi = -3.0e38f;
+    int unbounded = 0;
+    const int n = identity ? 1 : n_used;
+    for (int i = lane; i < n; i += 32) {
+        float bx = cx, by = cy, bz = cz;
+        if (!identity) {
+            const float *r = s_rec + i * REC_STRIDE + 4;
+            bx = r[0] * cx + r[1] * cy + r[2] * cz + r[9];
+            by = r[3] * cx + r[4] * cy + r[5] * cz + r[10];
+            bz = r[6] * cx + r[7] * cy + r[8] * cz + r[11];
+        }
+        const PixBox b = ball_pixbox(bx, by, bz, h, cam);
+        unbounded |= b.unbounded;
+        u_lo = fminf(u_lo, b.u_lo); u_hi = fmaxf(u_hi, b.u_hi);
+        v_lo = fminf(v_lo, b.v_lo); v_hi = fmaxf(v_hi, b.v_hi);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        unbounded |= __shfl_xor_sync(0xffffffffu, unbounded, o);
+        u_lo = fminf(u_lo, __shfl_xor_sync(0xffffffffu, u_lo, o));
+        u_hi = fmaxf(u_hi, __shfl_xor_sync(0xffffffffu, u_hi, o));
+        v_lo = fminf(v_lo, __shfl_xor_sync(0xffffffffu, v_lo, o));
+        v_hi = fmaxf(v_hi, __shfl_xor_sync(0xffffffffu, v_hi, o));
+    }
+    if (unbounded) return false;
+    // pixel u is accepted when rint(u) in [0, W): u in [-0.5, W-0.5); keep a 1 px margin
+    return u_hi < -1.5f || u_lo > (float)cam.W + 0.5f || v_hi < -1.5f || v_lo > (float)cam.H + 0.5f;
+}
+
 template <int K, bool VEC, int MODE>
 __global__ void __launch_bounds__(BRICK_THREADS)
 fused_brick_kernel(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ weight, float *__restrict__ colour,
                    GraphArgs ga, FrameArgs fa, unsigned long long *__restrict__ stats, float *__restrict__ out_pts,
                    uint8_t *__restrict__ out_valid)
 {
-    __shared__ __align__(128) float s_rec[(MODE == MODE_IDENTITY ? 1 : MAX_BRICK_NODES) * NODE_REC_FLOATS];
+    __shared__ __align__(128) float s_rec[(MODE == MODE_IDENTITY ? 1 : MAX_BRICK_NODES) * REC_STRIDE];
     __shared__ __align__(8) uint64_t s_bar;
     __shared__ unsigned long long s_stat[3];
+    __shared__ int s_cull;
 
     const int b = (MODE == MODE_WARPED) ? ga.active[blockIdx.x] : (int)blockIdx.x;
     const BrickCoord bc = brick_coord(g, b);
@@ -91,25 +171,34 @@ fused_brick_kernel(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ w
     if constexpr (MODE != MODE_IDENTITY) {
         n_used = ga.cnt[b];
         if (threadIdx.x == 0) mbar_init(&s_bar, 1);
-        if (threadIdx.x < 3) s_stat[threadIdx.x] = 0ull;
-        __syncthreads();
+    }
+    if (threadIdx.x < 3) s_stat[threadIdx.x] = 0ull;
+    __syncthreads();
+    if constexpr (MODE != MODE_IDENTITY) {
         if (n_used > 0) {
             // TMA gather of the brick's node records: one 64-byte bulk copy per node
             if (threadIdx.x == 0) mbar_arrive_expect_tx(&s_bar, (uint32_t)n_used * NODE_REC_FLOATS * 4u);
             if (threadIdx.x < 32) {
                 const int o = ga.off[b];
                 for (int i = threadIdx.x; i < n_used; i += 32)
-                    bulk_g2s(s_rec + i * NODE_REC_FLOATS,
+                    bulk_g2s(s_rec + i * REC_STRIDE,
                              ga.node_rec + (int64_t)__ldg(ga.brick_nodes + o + i) * NODE_REC_FLOATS,
                              NODE_REC_FLOATS * 4u, &s_bar);
             }
+            mbar_wait(&s_bar, 0);
         }
-    } else {
-        if (threadIdx.x < 3) s_stat[threadIdx.x] = 0ull;
+    }
+    if constexpr (MODE != MODE_DEFORM) {
+        // brick-level frustum cull (warp 0 decides, everyone obeys)
+        if (threadIdx.x < 32) {
+            const bool out = brick_outside_frustum(g, bc, s_rec, n_used, MODE == MODE_IDENTITY, fa.cam);
+            if (threadIdx.x == 0) s_cull = out ? 1 : 0;
+        }
         __syncthreads();
+        if (s_cull) return;
     }
 
-    // anchor-cache words of this thread's voxels (overlaps the TMA gather)
+    // anchor-cache words of this thread's voxels
     uint32_t ids[VOX_PER_THREAD][2];
 #pragma unroll
     for (int e = 0; e < VOX_PER_THREAD; ++e) ids[e][0] = ids[e][1] = 0xFFFFFFFFu;
@@ -135,10 +224,7 @@ fused_brick_kernel(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ w
 
     float px = 0.f, py = 0.f;
     if (row_live) { px = __ldg(g.px + lx); py = __ldg(g.py + iy); }
-
-    if constexpr (MODE != MODE_IDENTITY) {
-        if (n_used > 0) mbar_wait(&s_bar, 0);
-    }
+    const float rdenom = (MODE != MODE_IDENTITY) ? __frcp_rn(ga.denom) : 0.f;
 
     unsigned upd = 0, n_valid = 0;
     double diff[VOX_PER_THREAD];
@@ -151,7 +237,7 @@ fused_brick_kernel(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ w
         bool skin_ok = true;                                          // source frame: all valid, tsdf.py:395-398
         if constexpr (MODE != MODE_IDENTITY) {
             skin_ok = (ids[e][0] & 0xFFu) != 0xFFu;
-            if (skin_ok) warp_voxel<K>(ids[e], s_rec, ga.cutoff, ga.denom, px, py, pz, qx, qy, qz);
+            if (skin_ok) warp_voxel<K>(ids[e], s_rec, ga.denom, rdenom, px, py, pz, qx, qy, qz);
         }
         if constexpr (MODE == MODE_DEFORM) {
             if (out_pts) { out_pts[3 * (vox0 + e)] = qx; out_pts[3 * (vox0 + e) + 1] = qy; out_pts[3 * (vox0 + e) + 2] = qz; }
@@ -190,7 +276,7 @@ fused_brick_kernel(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ w
 #pragma unroll
             for (int e = 0; e < VOX_PER_THREAD; ++e)
                 if (upd & (1u << e)) {
-                    fuse_voxel(t[e], w[e], c[e], diff[e], ncol[e], fa.trunc, fa.obs, fa.obsf);
+                    fuse_voxel(t[e], w[e], c[e], diff[e], ncol[e], fa.trunc, fa.rtrunc, fa.obs, fa.obsf);
                     wsum += (unsigned long long)w[e];
                 }
             if (VEC) {
@@ -282,7 +368,7 @@ extern "C" int ofx_integrate(ofx_volume *v, const float *depth, const float *col
     unsigned long long *st = reinterpret_cast<unsigned long long *>(stats ? stats : v->stats_scratch);
     OFX_CUDA(cudaMemsetAsync(st, 0, OFX_N_STATS * sizeof(uint64_t), s));
     FrameArgs fa{depth, colour_packed, Camera{intr_host[0], intr_host[1], intr_host[2], intr_host[3], H, W},
-                 v->desc.trunc_margin, obs_weight, (float)obs_weight};
+                 v->desc.trunc_margin, 1.0 / v->desc.trunc_margin, obs_weight, (float)obs_weight};
     if (identity_warp) {
         GraphArgs ga{};
         return launch_fused<4, MODE_IDENTITY>(v, v->n_bricks, ga, fa, st, nullptr, nullptr, s);

@@ -92,6 +92,47 @@ __device__ __forceinline__ bool skin_weights(const float (&bd)[K], float cutoff,
     return ok;
 }
 
+// ---- exact division through a correctly rounded reciprocal ---------------------------------------
+// a / b rounded to nearest, given y = RN(1/b) (__frcp_rn / __drcp_rn, or 1/b computed once):
+// Markstein's correction applied twice (q <- q + RN(a - b q) * y; the residual is exact in FMA
+// arithmetic).  Bit-identical to IEEE division for normal operands (checked against `/` on
+// 2e8 random pairs per type and on the whole colour/weight grid: tests/test_host_logic.py and
+// every GPU-vs-oracle test, the oracle uses plain `/`); the result for a = -0 is +0, which no
+// caller can observe.  ~5 issue slots instead of ~10 + a slow-path branch, and one reciprocal
+// serves every division that shares the divisor.
+__device__ __forceinline__ float div_rn(float a, float b, float y)
+{
+    float q = a * y;
+    float r = __fmaf_rn(-b, q, a);
+    q = __fmaf_rn(r, y, q);
+    r = __fmaf_rn(-b, q, a);
+    return __fmaf_rn(r, y, q);
+}
+__device__ __forceinline__ double div_rn(double a, double b, double y)
+{
+    double q = a * y;
+    double r = __fma_rn(-b, q, a);
+    q = __fma_rn(r, y, q);
+    r = __fma_rn(-b, q, a);
+    return __fma_rn(r, y, q);
+}
+
+// skin_weights for a voxel already known to have all K anchors inside the cutoff (anchor cache):
+// same values as skin_weights(), divisions through shared reciprocals.  rdenom = RN(1/denom).
+template <int K>
+__device__ __forceinline__ void skin_weights_valid(const float (&bd)[K], float denom, float rdenom, float (&w)[K])
+{
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        const float d = sqrtf(bd[k]);
+        w[k] = expf_det(div_rn(-(d * d), denom, rdenom));
+    }
+    const float s = sum_k<K>(w) + 1e-6f;
+    const float rs = __frcp_rn(s);
+#pragma unroll
+    for (int k = 0; k < K; ++k) w[k] = div_rn(w[k], s, rs);
+}
+
 // One anchor's contribution to the blend: acc += w * (R p + T)   (warpfield.py:225-226).
 // rec = {R00..R22 row-major, T0, T1, T2}.
 __device__ __forceinline__ void lbs_accumulate(const float *__restrict__ rec, float w, float px,
@@ -116,8 +157,9 @@ __device__ __forceinline__ bool project(float qx, float qy, float qz, const Came
 {
     if (!(qz > 0.0f)) return false;
     const double z = (double)qz;
-    const double fu = rint((double)qx * (double)cam.fx / z + (double)cam.cx);
-    const double fv = rint((double)qy * (double)cam.fy / z + (double)cam.cy);
+    const double rz = __drcp_rn(z);                  // one reciprocal, two exact divisions
+    const double fu = rint(div_rn((double)qx * (double)cam.fx, z, rz) + (double)cam.cx);
+    const double fv = rint(div_rn((double)qy * (double)cam.fy, z, rz) + (double)cam.cy);
     if (!(fu >= 0.0 && fu < (double)cam.W && fv >= 0.0 && fv < (double)cam.H)) return false;
     u = (int)fu;
     v = (int)fv;
@@ -127,13 +169,16 @@ __device__ __forceinline__ bool project(float qx, float qy, float qz, const Came
 // Running-average update of one voxel (tsdf.py:466, 373-375, 479-493).
 // diff = depth - z (float64), already known to satisfy depth > 0 && diff >= -trunc.
 __device__ __forceinline__ void fuse_voxel(float &tsdf, float &weight, float &colour, double diff,
-                                           float new_colour, double trunc, double obs, float obsf)
+                                           float new_colour, double trunc, double rtrunc, double obs, float obsf)
 {
-    const double dist = fmin(1.0, diff / trunc);
+    // rtrunc = RN(1/trunc), computed once on the host
+    const double dist = diff >= trunc ? 1.0 : fmin(1.0, div_rn(diff, trunc, rtrunc));
     const float w_old = weight;
     const float w_new = (float)((double)w_old + obs);
     const float prod = w_old * tsdf;
-    tsdf = (float)(((double)prod + obs * dist) / (double)w_new);
+    const double num = (double)prod + obs * dist, den = (double)w_new;
+    // free space seen again (tsdf = 1, dist = 1): num == den, the quotient is exactly 1
+    tsdf = (num == den && den != 0.0) ? 1.0f : (float)div_rn(num, den, __drcp_rn(den));
     weight = w_new;
 
     const float oc = colour, nc = new_colour;
@@ -143,9 +188,10 @@ __device__ __forceinline__ void fuse_voxel(float &tsdf, float &weight, float &co
     const float nb = floorf(nc / 65536.0f);
     const float ng = floorf((nc - nb * 65536.0f) / 256.0f);
     const float nr = nc - nb * 65536.0f - ng * 256.0f;
-    const float b = fminf(255.0f, rintf((w_old * ob + obsf * nb) / w_new));
-    const float g = fminf(255.0f, rintf((w_old * og + obsf * ng) / w_new));
-    const float r = fminf(255.0f, rintf((w_old * orr + obsf * nr) / w_new));
+    const float rw = __frcp_rn(w_new);
+    const float b = fminf(255.0f, rintf(div_rn(w_old * ob + obsf * nb, w_new, rw)));
+    const float g = fminf(255.0f, rintf(div_rn(w_old * og + obsf * ng, w_new, rw)));
+    const float r = fminf(255.0f, rintf(div_rn(w_old * orr + obsf * nr, w_new, rw)));
     colour = b * 65536.0f + g * 256.0f + r;
 }
 

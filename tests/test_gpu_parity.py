@@ -152,7 +152,7 @@ def test_synthetic_tiny_bit_exact(oracle):
     a, wt, v = wf.skin_tsdf()
     oa, owt, ovl = ov.skin_tsdf()
     assert np.array_equal(a, oa) and np.array_equal(wt, owt) and np.array_equal(v, ovl)
-    assert stats[1][0]["skin_valid"] == int(ovl.sum())
+    assert 0 < stats[1][0]["skin_valid"] <= int(ovl.sum())        # bricks outside the frustum are not visited
 
 
 def test_synthetic_dense_and_obs_weight(oracle):
@@ -160,7 +160,8 @@ def test_synthetic_dense_and_obs_weight(oracle):
     w = Workload("c1-dense", dim=[48, 40, 64], voxel=0.02, n_nodes=64, H=120, W=160)
     vol, ov, wf, stats = _run_pair(w, oracle, n_frames=3, obs_weight=2.0)
     _assert_bit_equal(vol, ov)
-    assert stats[1][0]["skin_valid"] == w.dims[0] * w.dims[1] * w.dims[2]     # every voxel has K anchors
+    assert wf.deform_tsdf()[1].all()                                  # every voxel has K anchors
+    assert stats[1][1] <= stats[1][0]["skin_valid"] <= w.dims[0] * w.dims[1] * w.dims[2]
 
 
 @pytest.mark.parametrize("dims", [[13, 17, 19], [8, 8, 33], [5, 3, 4]])
