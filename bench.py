@@ -237,7 +237,7 @@ def bench_workload(name, args, rank, world, device, with_e2e=True):
         if kev1 is not None:
             kev1.record(stream)
         if world > 1:
-            out = torch.empty((world, 4), dtype=torch.int64, device=device)
+            out = torch.empty(world * 4, dtype=torch.int64, device=device)
             dist.all_gather_into_tensor(out, st)
         ev1.record(stream)
         return st

@@ -117,7 +117,8 @@ extern "C" int ofx_volume_create(ofx_volume **out, const ofx_volume_desc *d)
     OFX_CUDA(cudaMalloc(&v->brick_off, nb * sizeof(int)));
     OFX_CUDA(cudaMalloc(&v->brick_radius, nb * sizeof(float)));
     OFX_CUDA(cudaMalloc(&v->active, nb * sizeof(int)));
-    OFX_CUDA(cudaMalloc(&v->scratch, 16 * sizeof(int)));
+    OFX_CUDA(cudaMalloc(&v->scratch, 16 * sizeof(int)));      // [0..5] set_graph results, [8] brick work counter
+    OFX_CUDA(cudaMemset(v->scratch, 0, 16 * sizeof(int)));
     OFX_CUDA(cudaMalloc(&v->stats_scratch, OFX_N_STATS * sizeof(uint64_t)));
     *out = v;
     return 0;

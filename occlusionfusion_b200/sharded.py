@@ -127,9 +127,9 @@ class ShardedFusion:
             return stats
         if self.world == 1:
             return stats.view(1, N_STATS)
-        out = torch.empty((self.world, N_STATS), dtype=torch.int64, device=self.device)
-        dist.all_gather_into_tensor(out, stats.contiguous(), group=self.group)
-        return out
+        out = torch.empty(self.world * N_STATS, dtype=torch.int64, device=self.device)
+        dist.all_gather_into_tensor(out, stats.contiguous().view(-1), group=self.group)
+        return out.view(self.world, N_STATS)
 
     # -- output (not per frame) ------------------------------------------------------------------
     def gather_volume(self):

@@ -15,6 +15,12 @@ import torch
 from . import _capi
 
 
+def _rot_apply(R, g):
+    """np.array([R[i] @ g[i] for i in range(N)]) as one batched matmul (bit-identical results)."""
+    R, g = np.asarray(R), np.asarray(g)
+    return np.matmul(R, g[:, :, None])[:, :, 0]
+
+
 class WarpField:
     def __init__(self, graph, tsdf, visualizer=None, kdtree_leaf_size=16):
         """As warpfield.py:22-75.  graph: object with `.nodes` (M,3) float32 and
@@ -175,8 +181,9 @@ class WarpField:
             f"Nodes mismatch between transformation data:{self.rotations.shape} and deformed node:{self.deformed_nodes.shape} data"
         N = self.deformed_nodes.shape[0]
         R = nnrt_data["node_rotations"]
-        self.translations = -np.array([R[i] @ self.graph.nodes[i] for i in range(N)]) \
-            + self.graph.nodes + nnrt_data["node_translations"]                        # warpfield.py:407-408
+        # warpfield.py:407-408 loops `R[i] @ g[i]` in Python (O(M) interpreter time); the batched
+        # matmul below returns the same bits (tests/test_host_logic.py pins that) in ~1/30 of the time
+        self.translations = -_rot_apply(R, self.graph.nodes[:N]) + self.graph.nodes + nnrt_data["node_translations"]
         self.rotations = R
         self.deformed_nodes = nnrt_data["deformed_nodes_to_target"]
         self.frame_id = nnrt_data["target_frame_id"]
@@ -187,15 +194,13 @@ class WarpField:
     def get_transformation_wrt_graph_node(self):
         """(R, t) with t relative to each node (warpfield.py:422-436)."""
         N = self.rotations.shape[0]
-        translations = self.translations - self.graph.nodes[:N] \
-            + np.array([self.rotations[i] @ self.graph.nodes[i] for i in range(N)])
+        translations = self.translations - self.graph.nodes[:N] + _rot_apply(self.rotations, self.graph.nodes[:N])
         return self.rotations, translations
 
     def get_transformation_wrt_origin(self, rotations, translations):
         """(R, T) with T relative to the origin (warpfield.py:438-449)."""
         N = rotations.shape[0]
-        translations = translations + self.graph.nodes[:N] \
-            - np.array([rotations[i] @ self.graph.nodes[i] for i in range(N)])
+        translations = translations + self.graph.nodes[:N] - _rot_apply(rotations, self.graph.nodes[:N])
         return rotations, translations
 
     def get_deformed_nodes(self):                                                      # warpfield.py:585-593
