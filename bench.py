@@ -38,6 +38,7 @@ def parse():
     ap.add_argument("--impl", default="ofx", choices=["ofx", "reference"])
     ap.add_argument("--also", default="c2,c1", help="extra workloads reported under 'also' (N=1 only); '' = none")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of a CUDA graph replay")
     ap.add_argument("--cpu-planes", type=int, default=0, help="x-planes in the CPU sample (0 = auto)")
     return ap.parse_args()
 
@@ -178,7 +179,8 @@ def workload_config(w, n_gpus):
                         f"{w.W}x{w.H} synthetic depth+colour, {w.M} nodes, K={w.K}, scene={w.scene}, warped frames, "
                         f"steady state (graph unchanged)",
             "sharding": f"x-plane blocks of 4 dealt round-robin over {n_gpus} GPU(s)" if n_gpus > 1 else "single GPU",
-            "l2": "volume state > L2 and a 256 MiB buffer is written between timed steps"}
+            "l2": "volume state > L2 and a 256 MiB buffer is written between timed steps",
+            "launch": "per-frame launch sequence replayed as one CUDA graph (falls back to eager launches)"}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -223,23 +225,21 @@ def bench_workload(name, args, rank, world, device, with_e2e=True):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)
     stream = torch.cuda.current_stream(device)
 
-    def one_step(i, ev0, ev1, kev0=None, kev1=None):
-        flush.fill_(i & 0xFF)                                  # evict the volume lines from L2
-        sf.buf.copy_(packets[i % n_frames])                    # rank 0's packet for this frame (device copy, untimed)
-        ev0.record(stream)
+    gath = torch.empty(world * 4, dtype=torch.int64, device=device)
+
+    def core(kev0=None, kev1=None):
+        """the per-frame device work: [broadcast] -> node transforms -> fused kernel -> [counter all-gather]"""
         if world > 1:
             dist.broadcast(sf.buf, src=0)
         v = sf.views
         sf.be.set_transforms(v["R"], v["T"])
         if kev0 is not None:
-            kev0.record(stream)
+            kev0.record(torch.cuda.current_stream(device))
         st = sf.be.integrate(v["depth"], v["colour"], False, 1.0)
         if kev1 is not None:
-            kev1.record(stream)
+            kev1.record(torch.cuda.current_stream(device))
         if world > 1:
-            out = torch.empty(world * 4, dtype=torch.int64, device=device)
-            dist.all_gather_into_tensor(out, st)
-        ev1.record(stream)
+            dist.all_gather_into_tensor(gath, st)
         return st
 
     def barrier():
@@ -247,25 +247,59 @@ def bench_workload(name, args, rank, world, device, with_e2e=True):
             dist.barrier()
         torch.cuda.synchronize(device)
 
+    def prep(i):
+        flush.fill_(i & 0xFF)                                  # evict the volume lines from L2
+        sf.buf.copy_(packets[i % n_frames])                    # this frame's packet (device copy, untimed)
+
     mk = lambda: torch.cuda.Event(enable_timing=True)
     for i in range(max(3, args.warmup)):
-        one_step(i, mk(), mk())
+        prep(i)
+        core()
     barrier()
     K = args.steps
-    evs = [(mk(), mk(), mk(), mk()) for _ in range(K)]
-    upd_total = 0
+
+    # pass A (eager launches): kernel-only duration of the fused kernel + the counters
+    kevs = [(mk(), mk()) for _ in range(K)]
+    stats_acc = torch.zeros(4, dtype=torch.int64, device=device)
+    for i in range(K):
+        prep(i)
+        stats_acc += core(*kevs[i])
+    barrier()
+
+    # the per-frame launch sequence is short and launch-bound: replay it as one CUDA graph
+    graph = None
+    if not args.no_graph:
+        try:
+            g_ = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g_):
+                core()
+            graph = g_
+            prep(0); graph.replay()
+            barrier()
+        except Exception as e:            # noqa: BLE001
+            print(f"[bench] CUDA graph capture unavailable ({type(e).__name__}: {e}); timing eager launches", file=sys.stderr)
+            graph = None
+            barrier()
+
+    # pass B: the timed K steps
+    evs = [(mk(), mk()) for _ in range(K)]
     sampler = ClockSampler(device.index or 0)
     if rank == 0:
         sampler.start()
     barrier()
     t_wall0 = time.perf_counter()
-    stats_acc = torch.zeros(4, dtype=torch.int64, device=device)
     for i in range(K):
-        st = one_step(i, *evs[i])
-        stats_acc += st
+        prep(i)
+        evs[i][0].record(stream)
+        if graph is not None:
+            graph.replay()
+        else:
+            core()
+        evs[i][1].record(stream)
     barrier()
     t_wall = time.perf_counter() - t_wall0
     clocks = sampler.stop() if rank == 0 else None
+    evs = [(a_, b_, c_, d_) for (a_, b_), (c_, d_) in zip(evs, kevs)]
     step_ms = sum(a.elapsed_time(b) for a, b, _, _ in evs)
     kern_ms = sum(c.elapsed_time(d) for _, _, c, d in evs)
     tot = torch.tensor([step_ms, kern_ms], dtype=torch.float64, device=device)
@@ -280,7 +314,7 @@ def bench_workload(name, args, rank, world, device, with_e2e=True):
     local_upd = float(stats_acc[_capi.STAT_UPDATED]) / K
     res = dict(workload=w, ms_per_step=step_ms, kernel_ms=kern_ms, updated=upd, skin_valid=valid, bricks=bricks,
                value=upd / (step_ms * 1e-3), wall_ms_per_step=t_wall * 1e3 / K, clocks=clocks,
-               local_updated=local_upd, launches_per_step=2)
+               local_updated=local_upd, launches_per_step=2, graph=graph is not None)
     # roofline of the fused kernel on this rank's shard (rank 0 reports its own shard)
     alg_bytes = 24.0 * local_upd + 8.0 * H * W + 60.0 * w.M
     res["alg_bytes"] = alg_bytes
@@ -308,8 +342,8 @@ def bench_e2e(w, vol, wf, sf, frames, ests, args, rank, world, device):
     n_frames = len(ests)
     K, Wm = args.steps, max(3, args.warmup)
     H, W = w.H, w.W
-    fid = [vol.frame_id]
-    wf.frame_id = vol.frame_id           # the warp field follows the volume's frame counter (warpfield.py:399)
+    fid = [getattr(vol, "frame_id", 0)]
+    wf.frame_id = fid[0]                 # the warp field follows the volume's frame counter (warpfield.py:399)
 
     def step(i):
         est = dict(ests[i % n_frames])
@@ -353,6 +387,9 @@ def bench_e2e(w, vol, wf, sf, frames, ests, args, rank, world, device):
 # ------------------------------------------------------------------------------------------------
 def main():
     args = parse()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)                          # anything a library prints (e.g. "NCCL version ...") goes to stderr
+    sys.stdout = real_stdout
     if args.impl == "reference":
         return run_reference(args)
     import torch
