@@ -2,6 +2,8 @@
 // the per-voxel warp (cached anchors -> weights -> linear blend), brick-level frustum culling and
 // the per-thread body (4 consecutive z voxels: warp, project, test, fuse, store).
 #pragma once
+#include <cmath>
+
 #include "ofx_volume.cuh"
 
 namespace ofx {
@@ -12,9 +14,27 @@ struct FrameArgs {
     const float *depth;
     const float *colour_im;
     Camera cam;
+    FastCam fc;                  // the same intrinsics + the error terms of the certified float32 pixel
     double trunc, rtrunc, obs;   // rtrunc = RN(1/trunc)
     float obsf;
+    float ntrunc_up, ntrunc_dn;  // the two float32 neighbours of -trunc (up >= -trunc >= dn)
 };
+
+// host: FrameArgs for one frame
+static inline FrameArgs make_frame_args(const float *depth, const float *colour, const float *intr, int H, int W,
+                                        double trunc, double obs)
+{
+    FrameArgs fa{};
+    fa.depth = depth; fa.colour_im = colour;
+    fa.cam = Camera{intr[0], intr[1], intr[2], intr[3], H, W};
+    fa.fc = FastCam{intr[0], intr[1], intr[2], intr[3], 6.2e-8f * fabsf(intr[2]) + 1e-6f,
+                    6.2e-8f * fabsf(intr[3]) + 1e-6f, W, H};
+    fa.trunc = trunc; fa.rtrunc = 1.0 / trunc; fa.obs = obs; fa.obsf = (float)obs;
+    const float t = (float)(-trunc);
+    if ((double)t >= -trunc) { fa.ntrunc_up = t; fa.ntrunc_dn = ((double)t == -trunc) ? t : nextafterf(t, -INFINITY); }
+    else { fa.ntrunc_dn = t; fa.ntrunc_up = nextafterf(t, INFINITY); }
+    return fa;
+}
 
 struct GraphArgs {
     const float *node_rec;
@@ -48,7 +68,7 @@ __device__ __forceinline__ void warp_voxel(const uint32_t (&ids)[2], const float
     float ax = 0.f, ay = 0.f, az = 0.f;
 #pragma unroll
     for (int k = 0; k < K; ++k) {
-        if (w[k] == 0.0f) continue;                                  // warpfield.py:219
+        // (the reference skips w == 0, warpfield.py:219: cached voxels have w >= exp(-8.0001) / (K + 1e-6) > 0)
         float r12[12];
         const float4 a = *reinterpret_cast<const float4 *>(rec[k] + 4);
         const float4 b = *reinterpret_cast<const float4 *>(rec[k] + 8);
@@ -182,7 +202,7 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
     const float px = __ldg(g.px + lx), py = __ldg(g.py + iy);
 
     unsigned upd = 0;
-    double diff[VOX_PER_THREAD];
+    float dsel[VOX_PER_THREAD], zsel[VOX_PER_THREAD];
     float ncol[VOX_PER_THREAD];
 #pragma unroll
     for (int e = 0; e < VOX_PER_THREAD; ++e) {
@@ -201,12 +221,19 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
             if (!skin_ok) continue;                                   // tsdf.py:464
             ++c_valid;
             int u, v;
-            if (!project(qx, qy, qz, fa.cam, u, v)) continue;         // tsdf.py:589-593
-            const int64_t pix = (int64_t)v * fa.cam.W + u;
-            const double d = (double)__ldg(fa.depth + pix);
-            const double df = d - (double)qz;                         // tsdf.py:608
-            if (!(d > 0.0 && df >= -fa.trunc)) continue;              // tsdf.py:609
-            diff[e] = df;
+            const int st = project_fast(qx, qy, qz, fa.fc, u, v);     // tsdf.py:589-593, certified float32
+            if (st == 0) continue;
+            if (st == 2 && !project(qx, qy, qz, fa.cam, u, v)) continue;   // undecided: the float64 original
+            const int pix = v * fa.cam.W + u;
+            const float d = __ldg(fa.depth + pix);
+            // depth - z >= -trunc in float64 (tsdf.py:608-609).  fl32 is monotone: a float32 difference
+            // above / below the float32 neighbours of -trunc decides; only a tie needs float64
+            const float df = d - qz;
+            if (!(d > 0.0f)) continue;
+            if (!(df > fa.ntrunc_up)) {
+                if (df < fa.ntrunc_dn || !((double)d - (double)qz >= -fa.trunc)) continue;
+            }
+            dsel[e] = d; zsel[e] = qz;
             ncol[e] = __ldg(fa.colour_im + pix);
             upd |= 1u << e;
         }
@@ -230,7 +257,8 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
 #pragma unroll
         for (int e = 0; e < VOX_PER_THREAD; ++e)
             if (upd & (1u << e)) {
-                fuse_voxel(tt[e], ww[e], cc[e], diff[e], ncol[e], fa.trunc, fa.rtrunc, fa.obs, fa.obsf);
+                fuse_voxel(tt[e], ww[e], cc[e], (double)dsel[e] - (double)zsel[e], ncol[e], fa.trunc, fa.rtrunc, fa.obs,
+                           fa.obsf);
                 c_wsum += (unsigned)ww[e];
             }
         if (VEC) {

@@ -89,6 +89,74 @@ fused_brick_kernel(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ w
     }
 }
 
+// ---- per-frame brick cull: active bricks -> live list -----------------------------------------------
+// Eight lanes per active brick walk the brick's node list (records come from L2), bound the pixel
+// box of the warped brick (ofx_brick.cuh: ball_pixbox) and drop the bricks that cannot reach the
+// image.  Survivors are appended to live[] (one atomic per CTA of 32 bricks); the fused kernel
+// then sees only bricks that do arithmetic, so its dynamic scheduler balances equal-cost units.
+constexpr int CULL_LANES = 8;
+constexpr int CULL_THREADS = 256;
+constexpr int CULL_BRICKS_PER_CTA = CULL_THREADS / CULL_LANES;
+
+__global__ void __launch_bounds__(CULL_THREADS)
+brick_cull_kernel(GraphArgs ga, const float4 *__restrict__ brick_box, int n_active, Camera cam, int *__restrict__ live,
+                  int *__restrict__ n_live, unsigned long long *__restrict__ stats)
+{
+    __shared__ int s_mask[CULL_THREADS / 32];
+    __shared__ int s_base;
+    const int slot = threadIdx.x / CULL_LANES, sub = threadIdx.x % CULL_LANES;
+    const int idx = blockIdx.x * CULL_BRICKS_PER_CTA + slot;
+    int b = -1, n_used = 0, o = 0;
+    float4 box = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (idx < n_active) {
+        b = __ldg(ga.active + idx);
+        n_used = __ldg(ga.cnt + b);
+        o = __ldg(ga.off + b);
+        box = __ldg(brick_box + b);
+    }
+    float u_lo = 3.0e38f, u_hi = -3.0e38f, v_lo = 3.0e38f, v_hi = -3.0e38f;
+    int unbounded = 0;
+    for (int i = sub; i < n_used; i += CULL_LANES) {
+        const float4 *r = reinterpret_cast<const float4 *>(ga.node_rec + (int64_t)__ldg(ga.brick_nodes + o + i) * NODE_REC_FLOATS);
+        const float4 a = __ldg(r + 1), c = __ldg(r + 2), d = __ldg(r + 3);   // R00..R22, T0..T2
+        const float bx = a.x * box.x + a.y * box.y + a.z * box.z + d.y;
+        const float by = a.w * box.x + c.x * box.y + c.y * box.z + d.z;
+        const float bz = c.z * box.x + c.w * box.y + d.x * box.z + d.w;
+        const PixBox pb = ball_pixbox(bx, by, bz, box.w, cam);
+        unbounded |= pb.unbounded;
+        u_lo = fminf(u_lo, pb.u_lo); u_hi = fmaxf(u_hi, pb.u_hi);
+        v_lo = fminf(v_lo, pb.v_lo); v_hi = fmaxf(v_hi, pb.v_hi);
+    }
+#pragma unroll
+    for (int o2 = CULL_LANES / 2; o2 > 0; o2 >>= 1) {
+        unbounded |= __shfl_xor_sync(0xffffffffu, unbounded, o2);
+        u_lo = fminf(u_lo, __shfl_xor_sync(0xffffffffu, u_lo, o2));
+        u_hi = fmaxf(u_hi, __shfl_xor_sync(0xffffffffu, u_hi, o2));
+        v_lo = fminf(v_lo, __shfl_xor_sync(0xffffffffu, v_lo, o2));
+        v_hi = fmaxf(v_hi, __shfl_xor_sync(0xffffffffu, v_hi, o2));
+    }
+    // rint(u) in [0, W) <=> u in [-0.5, W - 0.5); 1 px margin
+    const bool out = !unbounded && (u_hi < -1.5f || u_lo > (float)cam.W + 0.5f || v_hi < -1.5f || v_lo > (float)cam.H + 0.5f);
+    const bool keep = b >= 0 && !out;
+    const unsigned bal = __ballot_sync(0xffffffffu, keep && sub == 0);
+    if ((threadIdx.x & 31) == 0) s_mask[threadIdx.x >> 5] = (int)bal;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int tot = 0;
+        for (int w = 0; w < CULL_THREADS / 32; ++w) tot += __popc((unsigned)s_mask[w]);
+        s_base = tot ? atomicAdd(n_live, tot) : 0;
+        if (tot) atomicAdd(stats + OFX_STAT_BRICKS, (unsigned long long)tot);
+    }
+    __syncthreads();
+    if (keep && sub == 0) {
+        int rank = 0;
+        const int w = threadIdx.x >> 5;
+        for (int k = 0; k < w; ++k) rank += __popc((unsigned)s_mask[k]);
+        rank += __popc((unsigned)s_mask[w] & ((1u << (threadIdx.x & 31)) - 1u));
+        live[s_base + rank] = b;
+    }
+}
+
 // ---- persistent, warp-specialised kernel for warped frames ----------------------------------------
 constexpr int N_STAGES = 2;
 constexpr int CONSUMER_WARPS = BRICK_THREADS / 32;          // 8
@@ -97,14 +165,13 @@ constexpr int PERSISTENT_THREADS = BRICK_THREADS + 32;      // + 1 producer warp
 struct StageInfo {
     int lx0, iy0, iz0;
     int n_used;      // -1 = no more bricks
-    int cull;
 };
 
 template <int K, bool VEC>
 __global__ void __launch_bounds__(PERSISTENT_THREADS, 4)
 fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ weight, float *__restrict__ colour,
-                        GraphArgs ga, FrameArgs fa, int n_active, int *__restrict__ work_counter,
-                        unsigned long long *__restrict__ stats)
+                        GraphArgs ga, FrameArgs fa, const int *__restrict__ live, const int *__restrict__ n_live_ptr,
+                        int *__restrict__ work_counter, unsigned long long *__restrict__ stats)
 {
     extern __shared__ __align__(128) unsigned char s_raw[];
     float *s_rec = reinterpret_cast<float *>(s_raw);                       // [N_STAGES][MAX_BRICK_NODES * REC_STRIDE]
@@ -123,50 +190,48 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
     __syncthreads();
 
     if (warp == CONSUMER_WARPS) {
-        // ===== producer warp: TMA gather of the next brick's node records + frustum cull =====
-        // Bricks are handed out dynamically (culled bricks cost ~1/50 of live ones and the two kinds
-        // are spatially sorted): the first brick is blockIdx.x, later ones come from an atomic
-        // counter.  Exactly n_active fetches happen per launch; whoever draws the last one
-        // resets the counter for the next launch.
+        // ===== producer warp: TMA gather of the next live brick's node records =====
+        // Bricks are handed out dynamically: the first is blockIdx.x, later ones come from an atomic
+        // counter (zeroed by ofx_integrate before the cull kernel).  The producer spends most of its
+        // life waiting for a free stage; it sleeps between polls so that it does not take issue slots
+        // from the four schedulers' consumer warps.
+        const int n_live = *n_live_ptr;
         int idx = blockIdx.x;
         for (int it = 0;; ++it) {
             if (it > 0) {
                 int f = 0;
-                if (lane == 0) {
-                    f = atomicAdd(work_counter, 1);
-                    if (f == n_active - 1) atomicExch(work_counter, 0);
-                }
+                if (lane == 0) f = atomicAdd(work_counter, 1);
                 idx = (int)gridDim.x + __shfl_sync(0xffffffffu, f, 0);
             }
             const int st = it % N_STAGES;
             const uint32_t ph = (uint32_t)(it / N_STAGES) & 1u;
-            if (it >= N_STAGES) mbar_wait(&bar_empty[st], ph ^ 1u);        // consumers released this stage
-            if (idx >= n_active) {
+            if (it >= N_STAGES) mbar_wait_sleep(&bar_empty[st], ph ^ 1u);  // consumers released this stage
+            if (idx >= n_live) {
                 if (lane == 0) { s_info[st].n_used = -1; mbar_arrive(&bar_full[st]); }
                 break;
             }
-            const int b = __ldg(ga.active + idx);
+            const int b = __ldg(live + idx);
             const int n_used = __ldg(ga.cnt + b), o = __ldg(ga.off + b);
             const BrickCoord bc = brick_coord(g, b);
             float *rec = s_rec + st * STAGE_FLOATS;
-            if (lane == 0) mbar_arrive_expect_tx(&bar_data[st], (uint32_t)n_used * NODE_REC_FLOATS * 4u);
+            if (lane == 0) {
+                s_info[st].lx0 = bc.lx0; s_info[st].iy0 = bc.iy0; s_info[st].iz0 = bc.iz0;
+                s_info[st].n_used = n_used;
+                mbar_arrive_expect_tx(&bar_data[st], (uint32_t)n_used * NODE_REC_FLOATS * 4u);
+            }
+            __syncwarp();
             for (int i = lane; i < n_used; i += 32)
                 bulk_g2s(rec + i * REC_STRIDE, ga.node_rec + (int64_t)__ldg(ga.brick_nodes + o + i) * NODE_REC_FLOATS,
                          NODE_REC_FLOATS * 4u, &bar_data[st]);
-            mbar_wait(&bar_data[st], ph);
-            const bool out = brick_outside_frustum(g, bc, rec, n_used, false, fa.cam);
-            if (lane == 0) {
-                s_info[st].lx0 = bc.lx0; s_info[st].iy0 = bc.iy0; s_info[st].iz0 = bc.iz0;
-                s_info[st].n_used = n_used; s_info[st].cull = out ? 1 : 0;
-                mbar_arrive(&bar_full[st]);                                // release: info + records visible
-            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bar_full[st]);                     // release: info visible; data has its own barrier
         }
         return;
     }
 
     // ===== consumer warps =====
     const float rdenom = __frcp_rn(ga.denom);
-    unsigned c_upd = 0, c_valid = 0, c_bricks = 0;
+    unsigned c_upd = 0, c_valid = 0;
     unsigned long long c_wsum = 0;
     for (int it = 0;; ++it) {
         const int st = it % N_STAGES;
@@ -174,16 +239,12 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
         mbar_wait(&bar_full[st], ph);
         const StageInfo info = s_info[st];
         if (info.n_used < 0) break;
-        if (!info.cull) {
-            mbar_wait(&bar_data[st], ph);          // already complete; orders the TMA writes before our reads
-            const BrickCoord bc{info.lx0, info.iy0, info.iz0};
-            unsigned w32 = 0;
-            brick_thread_work<K, VEC, MODE_WARPED>(g, tsdf, weight, colour, ga, fa, s_rec + st * STAGE_FLOATS, bc,
-                                                   info.n_used, rdenom, threadIdx.x, nullptr, nullptr, c_upd, c_valid,
-                                                   w32);
-            c_wsum += w32;
-            if (threadIdx.x == 0) ++c_bricks;
-        }
+        mbar_wait(&bar_data[st], ph);              // the TMA bytes of this stage have landed
+        const BrickCoord bc{info.lx0, info.iy0, info.iz0};
+        unsigned w32 = 0;
+        brick_thread_work<K, VEC, MODE_WARPED>(g, tsdf, weight, colour, ga, fa, s_rec + st * STAGE_FLOATS, bc,
+                                               info.n_used, rdenom, threadIdx.x, nullptr, nullptr, c_upd, c_valid, w32);
+        c_wsum += w32;
         __syncwarp();
         if (lane == 0) mbar_arrive(&bar_empty[st]);
     }
@@ -196,7 +257,6 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
         if (c_upd) atomicAdd(stats + OFX_STAT_UPDATED, (unsigned long long)c_upd);
         if (c_valid) atomicAdd(stats + OFX_STAT_SKIN_VALID, (unsigned long long)c_valid);
         if (c_wsum) atomicAdd(stats + OFX_STAT_WEIGHT_SUM, c_wsum);
-        if (c_bricks) atomicAdd(stats + OFX_STAT_BRICKS, (unsigned long long)c_bricks);
     }
 }
 
@@ -242,12 +302,18 @@ static int launch_persistent_t(ofx_volume *v, const FrameArgs &fa, unsigned long
                                                                PERSISTENT_THREADS, smem));
         if (blocks_per_sm < 1) blocks_per_sm = 1;
     }
+    if (v->n_active <= 0) return 0;
+    int *n_live = v->scratch + 8, *work = v->scratch + 9;
+    OFX_CUDA(cudaMemsetAsync(n_live, 0, 2 * sizeof(int), s));
+    const GraphArgs ga = graph_args(v);
+    brick_cull_kernel<<<(v->n_active + CULL_BRICKS_PER_CTA - 1) / CULL_BRICKS_PER_CTA, CULL_THREADS, 0, s>>>(
+        ga, v->brick_box, v->n_active, fa.cam, v->live, n_live, stats);
+    OFX_LAUNCH_CHECK();
     const int cap = sm_count() * blocks_per_sm;       // persistent grid: a multiple of the SM count
-    const int grid = v->n_active < cap ? v->n_active : cap;
-    if (grid <= 0) return 0;
+    const int grid = v->n_active < cap ? v->n_active : cap;   // CTAs beyond the live count retire at once
     fused_warped_persistent<K, VEC><<<grid, PERSISTENT_THREADS, smem, s>>>(v->geom, v->desc.tsdf, v->desc.weight,
-                                                                          v->desc.colour, graph_args(v), fa,
-                                                                          v->n_active, v->scratch + 8, stats);
+                                                                          v->desc.colour, ga, fa, v->live, n_live, work,
+                                                                          stats);
     OFX_LAUNCH_CHECK();
     return 0;
 }
@@ -266,8 +332,7 @@ extern "C" int ofx_integrate(ofx_volume *v, const float *depth, const float *col
     cudaStream_t s = (cudaStream_t)stream;
     unsigned long long *st = reinterpret_cast<unsigned long long *>(stats ? stats : v->stats_scratch);
     OFX_CUDA(cudaMemsetAsync(st, 0, OFX_N_STATS * sizeof(uint64_t), s));
-    FrameArgs fa{depth, colour_packed, Camera{intr_host[0], intr_host[1], intr_host[2], intr_host[3], H, W},
-                 v->desc.trunc_margin, 1.0 / v->desc.trunc_margin, obs_weight, (float)obs_weight};
+    const FrameArgs fa = make_frame_args(depth, colour_packed, intr_host, H, W, v->desc.trunc_margin, obs_weight);
     if (identity_warp) {
         GraphArgs ga{};
         return launch_brick<4, MODE_IDENTITY>(v, v->n_bricks, ga, fa, st, nullptr, nullptr, s);

@@ -32,6 +32,26 @@ __device__ __forceinline__ float expf_det(float x)
     return y * __int_as_float(((int)n + 127) << 23);
 }
 
+// expf_det for -87 < x <= 0 (the cached-voxel path: x >= -8.0001 because every anchor lies inside
+// 4*coverage).  Same value, fewer issue slots: rintf through the 1.5*2^23 magic constant
+// (round-half-even, exact for |t| < 2^22) and the power-of-two scale as an exponent-field add
+// (y in (0.4, 1], n >= -126 + 2: the product is normal, so adding n << 23 to the bits of y IS y * 2^n).
+__device__ __forceinline__ float expf_det_neg(float x)
+{
+    const float tm = x * 1.44269504088896341f + 12582912.0f;
+    const float n = tm - 12582912.0f;
+    float r = __fmaf_rn(n, -0.693145751953125f, x);
+    r = __fmaf_rn(n, -1.42860682030941723e-06f, r);
+    float p = 1.9875691500e-4f;
+    p = __fmaf_rn(p, r, 1.3981999507e-3f);
+    p = __fmaf_rn(p, r, 8.3334519073e-3f);
+    p = __fmaf_rn(p, r, 4.1665795894e-2f);
+    p = __fmaf_rn(p, r, 1.6666665459e-1f);
+    p = __fmaf_rn(p, r, 5.0000001201e-1f);
+    const float y = __fmaf_rn(p, r * r, r) + 1.0f;
+    return __int_as_float(__float_as_int(y) + (__float_as_int(tm) << 23));
+}
+
 // pykdtree's float32 squared distance: ((dx*dx)+(dy*dy))+(dz*dz)   (warpfield.py:104)
 __device__ __forceinline__ float dist2(float px, float py, float pz, float gx, float gy, float gz)
 {
@@ -125,7 +145,7 @@ __device__ __forceinline__ void skin_weights_valid(const float (&bd)[K], float d
 #pragma unroll
     for (int k = 0; k < K; ++k) {
         const float d = sqrtf(bd[k]);
-        w[k] = expf_det(div_rn(-(d * d), denom, rdenom));
+        w[k] = expf_det_neg(div_rn(-(d * d), denom, rdenom));
     }
     const float s = sum_k<K>(w) + 1e-6f;
     const float rs = __frcp_rn(s);
@@ -164,6 +184,48 @@ __device__ __forceinline__ bool project(float qx, float qy, float qz, const Came
     u = (int)fu;
     v = (int)fv;
     return true;
+}
+
+// Certified float32 evaluation of the same pixel.  m = fl(fl(qx*fx) * rcp(qz)) carries a relative
+// error <= 2^-24 + 2^-23 (MUFU.RCP, 1 ulp) + 2^-24 < 2.5e-7 against qx*fx/qz, u = fl(m + cx) adds
+// <= 2^-24 |u| <= 6e-8 (|m| + |c|): the float32 u lies within eps = 3.2e-7 |m| + eps0 of the float64
+// value the reference rounds (eps0 = 6.2e-8 |c| + 1e-6 also covers the reference's own 1e-12).
+// If u is farther than eps from a half-integer, rint(u) IS the reference pixel; otherwise (about
+// 1e-4 of the voxels), and for any NaN/Inf, the caller evaluates project().
+struct FastCam {
+    float fx, fy, cx, cy;
+    float eps0x, eps0y;     // 6.2e-8 |cx| + 1e-6, 6.2e-8 |cy| + 1e-6
+    int W, H;
+};
+
+__device__ __forceinline__ bool fast_pixel(float q, float f, float c, float eps0, float rz, int lim, int &ni,
+                                           bool &inside)
+{
+    const float m = (q * f) * rz;
+    const float u = m + c;
+    const float tm = u + 12582912.0f;                         // 1.5 * 2^23: the sum rounds u half-to-even
+    const float n = tm - 12582912.0f;                         // rint(u) for |u| < 2^22
+    const float frac = u - n;                                 // exact
+    const float eps = __fmaf_rn(fabsf(m), 3.2e-7f, eps0);     // > 0.5 long before the magic constant breaks down
+    // low mantissa bits of tm = rint(u); anything outside [-0.5, lim - 0.5] (NaN, Inf included) maps
+    // to a value that fails the unsigned compare
+    ni = __float_as_int(tm) - 0x4B400000;
+    inside = (unsigned)ni < (unsigned)lim;
+    return fabsf(frac) + eps < 0.5f;                          // false for NaN
+}
+
+// 0 = certainly no pixel, 1 = pixel (u, v) certain, 2 = undecided (use project()).
+__device__ __forceinline__ int project_fast(float qx, float qy, float qz, const FastCam &fc, int &u, int &v)
+{
+    if (!(qz > 0.0f)) return 0;
+    float rz;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rz) : "f"(qz));
+    bool in_u, in_v;
+    const bool ok_u = fast_pixel(qx, fc.fx, fc.cx, fc.eps0x, rz, fc.W, u, in_u);
+    const bool ok_v = fast_pixel(qy, fc.fy, fc.cy, fc.eps0y, rz, fc.H, v, in_v);
+    // a coordinate that is certainly outside decides the voxel even if the other one is undecided
+    if ((ok_u && !in_u) || (ok_v && !in_v)) return 0;
+    return (ok_u && ok_v) ? 1 : 2;
 }
 
 // Running-average update of one voxel (tsdf.py:466, 373-375, 479-493).
@@ -225,6 +287,24 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
         "}\n" ::"r"(smem_u32(bar)),
         "r"(parity)
         : "memory");
+}
+// the same wait for a warp that expects to wait long (the producer): sleep between polls
+__device__ __forceinline__ void mbar_wait_sleep(uint64_t *bar, uint32_t parity)
+{
+    uint32_t done = 0;
+    while (true) {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(done)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+        if (done) break;
+        __nanosleep(256);
+    }
 }
 // global -> shared bulk copy through the TMA unit (SASS: UBLKCP); bytes % 16 == 0, both
 // addresses 16-byte aligned; completion is signalled on `bar` as transaction bytes.

@@ -52,7 +52,7 @@ __device__ __forceinline__ BrickBox brick_box(const VolumeGeom &g, int b)
 __global__ void __launch_bounds__(128) brick_bound_kernel(VolumeGeom g, int n_bricks, const float *__restrict__ node_rec,
                                                           int M, int K, float cutoff, float *__restrict__ radius,
                                                           int *__restrict__ cnt, const int *__restrict__ off,
-                                                          int *__restrict__ cand)
+                                                          int *__restrict__ cand, float4 *__restrict__ box_out)
 {
     __shared__ float s_n[BOUND_NODE_TILE * 3];
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
@@ -91,6 +91,9 @@ __global__ void __launch_bounds__(128) brick_bound_kernel(VolumeGeom g, int n_br
             // dead brick: even the nearest corner is farther than the cutoff from its K-th node
             R = (sqrtf(bd[K - 1]) - bb.h > cut) ? -1.0f : fminf(dk + 2.0f * bb.h, cut + bb.h);
             radius[b] = R;
+            // centre + bounding radius for the per-frame cull (brick_cull_kernel); wider slack: the
+            // cull also absorbs the float32 rounding of the transformed centre
+            box_out[b] = make_float4(bb.cx, bb.cy, bb.cz, bb.h * 1.001f + 1e-5f);
         }
     }
     int count = 0;
@@ -337,7 +340,7 @@ extern "C" int ofx_set_graph(ofx_volume *v, const float *nodes, int32_t M, doubl
     const int nb = v->n_bricks;
     OFX_CUDA(cudaMemsetAsync(v->scratch, 0, 16 * sizeof(int), s));
     brick_bound_kernel<<<(nb + 127) / 128, 128, 0, s>>>(v->geom, nb, v->node_rec, M, K, v->cutoff, v->brick_radius,
-                                                        v->brick_cnt, nullptr, nullptr);
+                                                        v->brick_cnt, nullptr, nullptr, v->brick_box);
     OFX_LAUNCH_CHECK();
     scan_kernel<<<1, 1024, 0, s>>>(v->brick_cnt, nb, v->brick_off, nullptr, v->scratch);
     OFX_LAUNCH_CHECK();
@@ -357,7 +360,7 @@ extern "C" int ofx_set_graph(ofx_volume *v, const float *nodes, int32_t M, doubl
     }
     if (total > 0) {
         brick_bound_kernel<<<(nb + 127) / 128, 128, 0, s>>>(v->geom, nb, v->node_rec, M, K, v->cutoff,
-                                                            v->brick_radius, v->brick_cnt, v->brick_off, v->cand);
+                                                            v->brick_radius, v->brick_cnt, v->brick_off, v->cand, v->brick_box);
         OFX_LAUNCH_CHECK();
     }
     int rc = 0;

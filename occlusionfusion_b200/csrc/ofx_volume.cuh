@@ -65,7 +65,11 @@ struct ofx_volume {
     int64_t list_capacity;
     int *active;                 // bricks with at least one skin-valid voxel
     int n_active;
-    int *scratch;                // small device scratch: [0]=total [1]=max [2]=error
+    float4 *brick_box;           // n_bricks: brick centre (world) + bounding radius h, written by ofx_set_graph
+    int *live;                   // per frame: active bricks that survive the frustum / depth cull (n_bricks capacity)
+    float *depth_tiles;          // per frame: max depth of each DEPTH_TILE x DEPTH_TILE pixel tile
+    int depth_tiles_capacity;
+    int *scratch;                // small device scratch: [0]=total [1]=max [2]=error [8]=n_live [9]=work counter
     uint64_t *stats_scratch;     // OFX_N_STATS counters when the caller passes NULL
     bool graph_ready, transforms_ready;
 };
