@@ -42,37 +42,34 @@ struct GraphArgs {
     const int *off;
     const int *cnt;
     const int *brick_nodes;
-    const uint8_t *cache;
+    const int *brick_slot;   // cache slot of a brick
+    const uint8_t *cache_ids;
+    const float *cache_w;
+    int id_bytes;            // 4 or 8
     float cutoff, denom;
 };
 
-// Node records sit in shared memory at a stride of 20 floats (80 B): consecutive records start
-// 20 banks apart, so the eight float4 loads of a quarter-warp hit eight distinct 4-bank groups.
-constexpr int REC_STRIDE = 20;
+// Node transforms {R (9), T (3)} sit in shared memory at a stride of 12 floats (48 B): consecutive
+// records start 12 banks apart, so the eight float4 loads of a quarter-warp on eight consecutive
+// records hit eight distinct 4-bank groups.
+constexpr int REC_STRIDE = NODE_XFORM_FLOATS;
+constexpr uint32_t REC_BYTES = NODE_XFORM_FLOATS * 4u;
 
+// q = sum_k w_k (R_k p + T_k) with the cached anchors and weights of one voxel (warpfield.py:225-226).
+// (The reference skips w == 0, warpfield.py:219: cached voxels have w >= exp(-8.0001) / (K + 1e-6) > 0.)
 template <int K>
-__device__ __forceinline__ void warp_voxel(const uint32_t (&ids)[2], const float *__restrict__ s_rec, float denom,
-                                           float rdenom, float px, float py, float pz, float &qx, float &qy, float &qz)
+__device__ __forceinline__ void warp_voxel(const uint32_t (&ids)[2], const float (&w)[K], const float *__restrict__ s_rec,
+                                           float px, float py, float pz, float &qx, float &qy, float &qz)
 {
-    const float *rec[K];
-    float bd[K];
-#pragma unroll
-    for (int k = 0; k < K; ++k) {
-        const uint32_t id = (ids[k >> 2] >> (8 * (k & 3))) & 0xFFu;
-        rec[k] = s_rec + id * REC_STRIDE;
-        const float4 g4 = *reinterpret_cast<const float4 *>(rec[k]);
-        bd[k] = dist2(px, py, pz, g4.x, g4.y, g4.z);
-    }
-    float w[K];
-    skin_weights_valid<K>(bd, denom, rdenom, w);       // cached voxel: all K anchors are inside the cutoff
     float ax = 0.f, ay = 0.f, az = 0.f;
 #pragma unroll
     for (int k = 0; k < K; ++k) {
-        // (the reference skips w == 0, warpfield.py:219: cached voxels have w >= exp(-8.0001) / (K + 1e-6) > 0)
+        const uint32_t id = (ids[k >> 2] >> (8 * (k & 3))) & 0xFFu;
+        const float *rec = s_rec + id * REC_STRIDE;
         float r12[12];
-        const float4 a = *reinterpret_cast<const float4 *>(rec[k] + 4);
-        const float4 b = *reinterpret_cast<const float4 *>(rec[k] + 8);
-        const float4 c = *reinterpret_cast<const float4 *>(rec[k] + 12);
+        const float4 a = *reinterpret_cast<const float4 *>(rec);
+        const float4 b = *reinterpret_cast<const float4 *>(rec + 4);
+        const float4 c = *reinterpret_cast<const float4 *>(rec + 8);
         r12[0] = a.x; r12[1] = a.y; r12[2] = a.z; r12[3] = a.w; r12[4] = b.x; r12[5] = b.y; r12[6] = b.z; r12[7] = b.w;
         r12[8] = c.x; r12[9] = c.y; r12[10] = c.z; r12[11] = c.w;
         lbs_accumulate(r12, w[k], px, py, pz, ax, ay, az);
@@ -133,7 +130,7 @@ __device__ __forceinline__ bool brick_outside_frustum(const VolumeGeom &g, const
     for (int i = lane; i < n; i += 32) {
         float bx = cx, by = cy, bz = cz;
         if (!identity) {
-            const float *r = s_rec + i * REC_STRIDE + 4;
+            const float *r = s_rec + i * REC_STRIDE;
             bx = r[0] * cx + r[1] * cy + r[2] * cz + r[9];
             by = r[3] * cx + r[4] * cy + r[5] * cz + r[10];
             bz = r[6] * cx + r[7] * cy + r[8] * cz + r[11];
@@ -165,7 +162,7 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
                                                   float *__restrict__ weight, float *__restrict__ colour,
                                                   const GraphArgs &ga, const FrameArgs &fa,
                                                   const float *__restrict__ s_rec, const BrickCoord &bc, int n_used,
-                                                  float rdenom, int t, float *__restrict__ out_pts,
+                                                  int slot, int t, float *__restrict__ out_pts,
                                                   uint8_t *__restrict__ out_valid, unsigned &c_upd, unsigned &c_valid,
                                                   unsigned &c_wsum)
 {
@@ -176,26 +173,27 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
     const int64_t vox0 = ((int64_t)lx * g.Dy + iy) * g.Dz + iz0;
     const int n_vox = min(VOX_PER_THREAD, g.Dz - iz0);
 
-    // anchor-cache words of this thread's voxels
+    // skin-cache words of this thread's four voxels: ids (one or two 16-byte loads) + K weight float4s
     uint32_t ids[VOX_PER_THREAD][2];
+    float wk[VOX_PER_THREAD][K];
 #pragma unroll
     for (int e = 0; e < VOX_PER_THREAD; ++e) ids[e][0] = ids[e][1] = 0xFFFFFFFFu;
     if constexpr (MODE != MODE_IDENTITY) {
         if (n_used > 0) {
+            const int64_t j0 = (int64_t)slot * BRICK_VOXELS + t * VOX_PER_THREAD;
             if constexpr (K <= 4) {
-                const uint32_t *c = reinterpret_cast<const uint32_t *>(ga.cache) + vox0;
-                if (VEC) {
-                    const uint4 q = __ldg(reinterpret_cast<const uint4 *>(c));
-                    ids[0][0] = q.x; ids[1][0] = q.y; ids[2][0] = q.z; ids[3][0] = q.w;
-                } else {
-                    for (int e = 0; e < n_vox; ++e) ids[e][0] = __ldg(c + e);
-                }
+                const uint4 q = __ldg(reinterpret_cast<const uint4 *>(ga.cache_ids + j0 * 4));
+                ids[0][0] = q.x; ids[1][0] = q.y; ids[2][0] = q.z; ids[3][0] = q.w;
             } else {
-                const uint2 *c = reinterpret_cast<const uint2 *>(ga.cache) + vox0;
-                for (int e = 0; e < n_vox; ++e) {
-                    const uint2 q = __ldg(c + e);
-                    ids[e][0] = q.x; ids[e][1] = q.y;
-                }
+                const uint4 *c = reinterpret_cast<const uint4 *>(ga.cache_ids + j0 * 8);
+                const uint4 q0 = __ldg(c), q1 = __ldg(c + 1);
+                ids[0][0] = q0.x; ids[0][1] = q0.y; ids[1][0] = q0.z; ids[1][1] = q0.w;
+                ids[2][0] = q1.x; ids[2][1] = q1.y; ids[3][0] = q1.z; ids[3][1] = q1.w;
+            }
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                const float4 w4 = __ldg(reinterpret_cast<const float4 *>(ga.cache_w + ((int64_t)slot * K + k) * BRICK_VOXELS) + t);
+                wk[0][k] = w4.x; wk[1][k] = w4.y; wk[2][k] = w4.z; wk[3][k] = w4.w;
             }
         }
     }
@@ -212,7 +210,7 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
         bool skin_ok = true;                                          // source frame: all valid, tsdf.py:395-398
         if constexpr (MODE != MODE_IDENTITY) {
             skin_ok = (ids[e][0] & 0xFFu) != 0xFFu;
-            if (skin_ok) warp_voxel<K>(ids[e], s_rec, ga.denom, rdenom, px, py, pz, qx, qy, qz);
+            if (skin_ok) warp_voxel<K>(ids[e], wk[e], s_rec, px, py, pz, qx, qy, qz);
         }
         if constexpr (MODE == MODE_DEFORM) {
             if (out_pts) { out_pts[3 * (vox0 + e)] = qx; out_pts[3 * (vox0 + e) + 1] = qy; out_pts[3 * (vox0 + e) + 2] = qz; }

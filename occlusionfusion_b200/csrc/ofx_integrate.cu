@@ -47,13 +47,13 @@ fused_brick_kernel(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ w
     __syncthreads();
     if constexpr (MODE != MODE_IDENTITY) {
         if (n_used > 0) {
-            if (threadIdx.x == 0) mbar_arrive_expect_tx(&s_bar, (uint32_t)n_used * NODE_REC_FLOATS * 4u);
+            if (threadIdx.x == 0) mbar_arrive_expect_tx(&s_bar, (uint32_t)n_used * REC_BYTES);
             if (threadIdx.x < 32) {
                 const int o = ga.off[b];
                 for (int i = threadIdx.x; i < n_used; i += 32)
                     bulk_g2s(s_rec + i * REC_STRIDE,
-                             ga.node_rec + (int64_t)__ldg(ga.brick_nodes + o + i) * NODE_REC_FLOATS,
-                             NODE_REC_FLOATS * 4u, &s_bar);
+                             ga.node_rec + (int64_t)__ldg(ga.brick_nodes + o + i) * NODE_REC_FLOATS + NODE_XFORM_OFFSET,
+                             REC_BYTES, &s_bar);
             }
             mbar_wait(&s_bar, 0);
         }
@@ -66,9 +66,9 @@ fused_brick_kernel(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ w
         __syncthreads();
         if (s_cull) return;
     }
-    const float rdenom = (MODE != MODE_IDENTITY) ? __frcp_rn(ga.denom) : 0.f;
+    const int slot = (MODE != MODE_IDENTITY && n_used > 0) ? ga.brick_slot[b] : 0;
     unsigned c_upd = 0, c_valid = 0, c_wsum = 0;
-    brick_thread_work<K, VEC, MODE>(g, tsdf, weight, colour, ga, fa, s_rec, bc, n_used, rdenom, threadIdx.x, out_pts,
+    brick_thread_work<K, VEC, MODE>(g, tsdf, weight, colour, ga, fa, s_rec, bc, n_used, slot, threadIdx.x, out_pts,
                                     out_valid, c_upd, c_valid, c_wsum);
     if constexpr (MODE != MODE_DEFORM) {
         c_upd = __reduce_add_sync(0xffffffffu, c_upd);
@@ -158,30 +158,38 @@ brick_cull_kernel(GraphArgs ga, const float4 *__restrict__ brick_box, int n_acti
 }
 
 // ---- persistent, warp-specialised kernel for warped frames ----------------------------------------
-constexpr int N_STAGES = 2;
+// Eight consumer warps process bricks; one producer warp runs ahead of them by up to N_SLOTS bricks.
+// The producer draws live bricks (first = blockIdx.x, then an atomic counter), allocates room for the
+// brick's node transforms in a ring of RING_RECS records, gathers them with the TMA unit (one 48-byte
+// cp.async.bulk per node) and publishes a descriptor.  Three mbarriers per descriptor slot:
+//   bar_full   producer -> consumers: descriptor written
+//   bar_data   TMA -> consumers: the transforms have landed (transaction bytes)
+//   bar_empty  consumers -> producer: all eight warps are done with the slot and its records
+constexpr int N_SLOTS = 8;
+constexpr int RING_RECS = 512;                              // >= 2 * MAX_BRICK_NODES: two of the largest bricks
 constexpr int CONSUMER_WARPS = BRICK_THREADS / 32;          // 8
 constexpr int PERSISTENT_THREADS = BRICK_THREADS + 32;      // + 1 producer warp
 
-struct StageInfo {
+struct SlotInfo {
     int lx0, iy0, iz0;
     int n_used;      // -1 = no more bricks
+    int rec_off;     // first record of the brick in the ring
+    int cache_slot;
 };
 
 template <int K, bool VEC>
-__global__ void __launch_bounds__(PERSISTENT_THREADS, 4)
+__global__ void __launch_bounds__(PERSISTENT_THREADS, K <= 4 ? 4 : 3)
 fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ weight, float *__restrict__ colour,
                         GraphArgs ga, FrameArgs fa, const int *__restrict__ live, const int *__restrict__ n_live_ptr,
                         int *__restrict__ work_counter, unsigned long long *__restrict__ stats)
 {
-    extern __shared__ __align__(128) unsigned char s_raw[];
-    float *s_rec = reinterpret_cast<float *>(s_raw);                       // [N_STAGES][MAX_BRICK_NODES * REC_STRIDE]
-    constexpr int STAGE_FLOATS = MAX_BRICK_NODES * REC_STRIDE;
-    __shared__ __align__(8) uint64_t bar_data[N_STAGES], bar_full[N_STAGES], bar_empty[N_STAGES];
-    __shared__ StageInfo s_info[N_STAGES];
+    __shared__ __align__(128) float s_rec[RING_RECS * REC_STRIDE];
+    __shared__ __align__(8) uint64_t bar_data[N_SLOTS], bar_full[N_SLOTS], bar_empty[N_SLOTS];
+    __shared__ SlotInfo s_info[N_SLOTS];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
-        for (int s = 0; s < N_STAGES; ++s) {
+        for (int s = 0; s < N_SLOTS; ++s) {
             mbar_init(&bar_data[s], 1);
             mbar_init(&bar_full[s], 1);
             mbar_init(&bar_empty[s], CONSUMER_WARPS);
@@ -190,63 +198,83 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
     __syncthreads();
 
     if (warp == CONSUMER_WARPS) {
-        // ===== producer warp: TMA gather of the next live brick's node records =====
-        // Bricks are handed out dynamically: the first is blockIdx.x, later ones come from an atomic
-        // counter (zeroed by ofx_integrate before the cull kernel).  The producer spends most of its
-        // life waiting for a free stage; it sleeps between polls so that it does not take issue slots
-        // from the four schedulers' consumer warps.
+        // ===== producer warp (all lanes keep the same bookkeeping; lane 0 talks to the barriers) =====
         const int n_live = *n_live_ptr;
         int idx = blockIdx.x;
+        int rel = 0;                  // iterations [0, rel) have been released by the consumers
+        int head = 0, tail = 0;       // ring: next free record / first record of the oldest unreleased brick
+        bool wrapped = false;         // in use: [tail, head) when !wrapped, [tail, end) + [0, head) when wrapped
         for (int it = 0;; ++it) {
-            if (it > 0) {
-                int f = 0;
-                if (lane == 0) f = atomicAdd(work_counter, 1);
-                idx = (int)gridDim.x + __shfl_sync(0xffffffffu, f, 0);
+            const int slot = it % N_SLOTS;
+            int b = 0, n_used = 0, o = 0, cslot = 0;
+            const bool more = idx < n_live;
+            if (more) {
+                b = __ldg(live + idx);
+                n_used = __ldg(ga.cnt + b);
+                o = __ldg(ga.off + b);
+                cslot = __ldg(ga.brick_slot + b);
             }
-            const int st = it % N_STAGES;
-            const uint32_t ph = (uint32_t)(it / N_STAGES) & 1u;
-            if (it >= N_STAGES) mbar_wait_sleep(&bar_empty[st], ph ^ 1u);  // consumers released this stage
-            if (idx >= n_live) {
-                if (lane == 0) { s_info[st].n_used = -1; mbar_arrive(&bar_full[st]); }
+            // room: a free descriptor slot and n_used contiguous records
+            int start = -1;
+            while (true) {
+                if (it - rel < N_SLOTS) {
+                    if (it == rel) { head = 0; tail = 0; wrapped = false; }
+                    if (!wrapped) {
+                        if (RING_RECS - head >= n_used) { start = head; head += n_used; }
+                        else if (tail >= n_used) { start = 0; head = n_used; wrapped = true; }
+                    } else if (tail - head >= n_used) { start = head; head += n_used; }
+                    if (start >= 0) break;
+                }
+                mbar_wait_sleep(&bar_empty[rel % N_SLOTS], (uint32_t)(rel / N_SLOTS) & 1u);   // oldest brick done
+                ++rel;
+                if (rel < it) {
+                    const int nt = s_info[rel % N_SLOTS].rec_off;
+                    if (nt < tail) wrapped = false;
+                    tail = nt;
+                }
+            }
+            if (!more) {
+                if (lane == 0) { s_info[slot].n_used = -1; mbar_arrive(&bar_full[slot]); }
                 break;
             }
-            const int b = __ldg(live + idx);
-            const int n_used = __ldg(ga.cnt + b), o = __ldg(ga.off + b);
             const BrickCoord bc = brick_coord(g, b);
-            float *rec = s_rec + st * STAGE_FLOATS;
             if (lane == 0) {
-                s_info[st].lx0 = bc.lx0; s_info[st].iy0 = bc.iy0; s_info[st].iz0 = bc.iz0;
-                s_info[st].n_used = n_used;
-                mbar_arrive_expect_tx(&bar_data[st], (uint32_t)n_used * NODE_REC_FLOATS * 4u);
+                s_info[slot].lx0 = bc.lx0; s_info[slot].iy0 = bc.iy0; s_info[slot].iz0 = bc.iz0;
+                s_info[slot].n_used = n_used; s_info[slot].rec_off = start; s_info[slot].cache_slot = cslot;
+                mbar_arrive_expect_tx(&bar_data[slot], (uint32_t)n_used * REC_BYTES);
+                mbar_arrive(&bar_full[slot]);          // release: descriptor visible; the data has its own barrier
             }
             __syncwarp();
+            float *rec = s_rec + start * REC_STRIDE;
             for (int i = lane; i < n_used; i += 32)
-                bulk_g2s(rec + i * REC_STRIDE, ga.node_rec + (int64_t)__ldg(ga.brick_nodes + o + i) * NODE_REC_FLOATS,
-                         NODE_REC_FLOATS * 4u, &bar_data[st]);
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&bar_full[st]);                     // release: info visible; data has its own barrier
+                bulk_g2s(rec + i * REC_STRIDE,
+                         ga.node_rec + (int64_t)__ldg(ga.brick_nodes + o + i) * NODE_REC_FLOATS + NODE_XFORM_OFFSET,
+                         REC_BYTES, &bar_data[slot]);
+            int f = 0;
+            if (lane == 0) f = atomicAdd(work_counter, 1);
+            idx = (int)gridDim.x + __shfl_sync(0xffffffffu, f, 0);
         }
         return;
     }
 
     // ===== consumer warps =====
-    const float rdenom = __frcp_rn(ga.denom);
     unsigned c_upd = 0, c_valid = 0;
     unsigned long long c_wsum = 0;
     for (int it = 0;; ++it) {
-        const int st = it % N_STAGES;
-        const uint32_t ph = (uint32_t)(it / N_STAGES) & 1u;
-        mbar_wait(&bar_full[st], ph);
-        const StageInfo info = s_info[st];
+        const int slot = it % N_SLOTS;
+        const uint32_t ph = (uint32_t)(it / N_SLOTS) & 1u;
+        mbar_wait(&bar_full[slot], ph);
+        const SlotInfo info = s_info[slot];
         if (info.n_used < 0) break;
-        mbar_wait(&bar_data[st], ph);              // the TMA bytes of this stage have landed
+        mbar_wait(&bar_data[slot], ph);            // the TMA bytes of this brick have landed
         const BrickCoord bc{info.lx0, info.iy0, info.iz0};
         unsigned w32 = 0;
-        brick_thread_work<K, VEC, MODE_WARPED>(g, tsdf, weight, colour, ga, fa, s_rec + st * STAGE_FLOATS, bc,
-                                               info.n_used, rdenom, threadIdx.x, nullptr, nullptr, c_upd, c_valid, w32);
+        brick_thread_work<K, VEC, MODE_WARPED>(g, tsdf, weight, colour, ga, fa, s_rec + info.rec_off * REC_STRIDE, bc,
+                                               info.n_used, info.cache_slot, threadIdx.x, nullptr, nullptr, c_upd,
+                                               c_valid, w32);
         c_wsum += w32;
         __syncwarp();
-        if (lane == 0) mbar_arrive(&bar_empty[st]);
+        if (lane == 0) mbar_arrive(&bar_empty[slot]);
     }
     // counters: once per CTA lifetime
     c_upd = __reduce_add_sync(0xffffffffu, c_upd);
@@ -266,14 +294,14 @@ using namespace ofx;
 
 static bool volume_vec_ok(const ofx_volume *v)
 {
-    const uintptr_t a = (uintptr_t)v->desc.tsdf | (uintptr_t)v->desc.weight | (uintptr_t)v->desc.colour |
-                        (uintptr_t)v->anchor_cache;
+    const uintptr_t a = (uintptr_t)v->desc.tsdf | (uintptr_t)v->desc.weight | (uintptr_t)v->desc.colour;
     return v->geom.Dz % 4 == 0 && (a & 15) == 0;
 }
 
 static GraphArgs graph_args(const ofx_volume *v)
 {
-    return GraphArgs{v->node_rec, v->active, v->brick_off, v->brick_cnt, v->brick_nodes, v->anchor_cache, v->cutoff, v->denom};
+    return GraphArgs{v->node_rec, v->active, v->brick_off, v->brick_cnt, v->brick_nodes, v->brick_slot, v->cache_ids,
+                     v->cache_w, v->cache_bytes_per_voxel, v->cutoff, v->denom};
 }
 
 template <int K, int MODE>
@@ -295,9 +323,8 @@ template <int K, bool VEC>
 static int launch_persistent_t(ofx_volume *v, const FrameArgs &fa, unsigned long long *stats, cudaStream_t s)
 {
     static int blocks_per_sm = 0;      // per instantiation
-    const size_t smem = (size_t)N_STAGES * MAX_BRICK_NODES * REC_STRIDE * sizeof(float);
+    const size_t smem = 0;
     if (blocks_per_sm == 0) {
-        OFX_CUDA(cudaFuncSetAttribute(fused_warped_persistent<K, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         OFX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, fused_warped_persistent<K, VEC>,
                                                                PERSISTENT_THREADS, smem));
         if (blocks_per_sm < 1) blocks_per_sm = 1;

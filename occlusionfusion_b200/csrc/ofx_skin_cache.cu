@@ -2,20 +2,23 @@
 // WarpField.skin_tsdf (warpfield.py:131-141), which the reference recomputes only when the graph
 // changes (node insertion, warpfield.py:493,532-533).
 //
-// The reference caches 33 B/voxel (anchors i32 x4, weights f32 x4, valid).  Here the cache is
-// K bytes per voxel (padded to 4 or 8): brick-local anchor ids into a per-brick list of the
-// nodes its voxels actually use; weights are recomputed from the node positions (same float
-// ops, so bit-identical) in the fused kernel.  Bricks without a single skin-valid voxel never
-// enter the work list, so the 4*coverage cutoff (warpfield.py:109) culls whole bricks exactly.
+// The reference caches 33 B/voxel (anchors i32 x4, weights f32 x4, valid) for every voxel.  Here
+// the cache exists only for bricks that can hold a skin-valid voxel (one "slot" per such brick,
+// brick-major so that a thread's four voxels are one 16-byte word): K bytes of brick-local anchor
+// ids per voxel (padded to 4 or 8; an id indexes the brick's list of the nodes its voxels use)
+// and the K normalised float32 weights, computed once here with the contract arithmetic
+// (ofx_math.cuh: skin_weights_valid) exactly as the reference computes world_weights once.
+// Bricks without a single skin-valid voxel never enter the work list, so the 4*coverage cutoff
+// (warpfield.py:109) culls whole bricks exactly.
 //
 // Pipeline (all on `stream`; ends with one small device->host read, i.e. it synchronises):
 //   1 brick_bound_kernel   per brick: K-th nearest node distance D_K from the brick centre;
 //                          exact candidate radius R = min(D_K + 2h, cutoff + h) (h = half
 //                          diagonal); bricks with D_K - h > cutoff are dead
-//   2 scan                 offsets of the candidate lists
+//   2 scan x2              offsets of the candidate lists; cache slots of the bricks that have candidates
 //   3 brick_fill_kernel    candidate node ids, ascending
 //   4 skin_brick_kernel    per voxel exact top-K over the brick's candidates (registers),
-//                          used-node marking, compaction, byte ids -> anchor cache
+//                          used-node marking, compaction, byte ids + weights -> skin cache
 //   5 scan                 work list of active bricks
 #include <vector>
 
@@ -177,10 +180,13 @@ constexpr int CAND_TILE = 512;
 
 template <int K>
 __global__ void __launch_bounds__(BRICK_THREADS) skin_brick_kernel(VolumeGeom g, const float *__restrict__ node_rec,
-                                                                   float cutoff, const int *__restrict__ off,
+                                                                   float cutoff, float denom,
+                                                                   const int *__restrict__ off,
                                                                    int *__restrict__ cnt, const int *__restrict__ cand,
                                                                    int *__restrict__ brick_nodes,
-                                                                   uint8_t *__restrict__ cache, int cache_bpv,
+                                                                   const int *__restrict__ brick_slot,
+                                                                   uint8_t *__restrict__ cache_ids,
+                                                                   float *__restrict__ cache_w,
                                                                    int *__restrict__ error_flag)
 {
     extern __shared__ __align__(16) unsigned char s_raw[];
@@ -196,13 +202,13 @@ __global__ void __launch_bounds__(BRICK_THREADS) skin_brick_kernel(VolumeGeom g,
     const int tz = threadIdx.x & 7, ty = (threadIdx.x >> 3) & 7, tx = threadIdx.x >> 6;
     const int lx = bc.lx0 + tx, iy = bc.iy0 + ty, iz0 = bc.iz0 + tz * VOX_PER_THREAD;
     const bool row_live = lx < g.nx && iy < g.Dy;
-    const int64_t vox0 = ((int64_t)lx * g.Dy + iy) * g.Dz + iz0;
+    const int64_t slot = brick_slot[b];
 
     bool any_valid = false;
     int bi[VOX_PER_THREAD][K];
     bool ok[VOX_PER_THREAD];
+    float bd[VOX_PER_THREAD][K];
     if (n_cand > 0) {
-        float bd[VOX_PER_THREAD][K];
 #pragma unroll
         for (int e = 0; e < VOX_PER_THREAD; ++e)
 #pragma unroll
@@ -280,19 +286,43 @@ __global__ void __launch_bounds__(BRICK_THREADS) skin_brick_kernel(VolumeGeom g,
         if (n_used > MAX_BRICK_NODES) atomicExch(error_flag, n_used);
     }
 
-    // byte ids -> cache (0xFF = no anchor)
-    if (row_live) {
+    // byte ids (0xFF = no anchor) and normalised weights -> the brick's cache slot; threads outside
+    // the volume write "invalid" so that the fused kernel can always load whole 16-byte words
+    constexpr int ID_BYTES = K <= 4 ? 4 : 8;
+    const float rdenom = __frcp_rn(denom);
+    uint32_t words[VOX_PER_THREAD][2];
+    float wq[K][VOX_PER_THREAD];
 #pragma unroll
-        for (int e = 0; e < VOX_PER_THREAD; ++e) {
-            if (iz0 + e >= g.Dz) continue;
-            uint8_t *c = cache + (vox0 + e) * cache_bpv;
-            for (int k = 0; k < cache_bpv; ++k) {
-                uint8_t id = 0xFF;
-                if (k < K && ok[e]) id = (uint8_t)min((int)s_rank[bi[e][k]], 254);
-                c[k] = id;
+    for (int e = 0; e < VOX_PER_THREAD; ++e) {
+        words[e][0] = words[e][1] = 0xFFFFFFFFu;
+        float w[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) w[k] = 0.0f;
+        if (ok[e]) {
+            words[e][0] = words[e][1] = 0u;
+#pragma unroll
+            for (int k = 0; k < ID_BYTES; ++k) {
+                uint32_t id = 0xFFu;
+                if (k < K) id = (uint32_t)min((int)s_rank[bi[e][k < K ? k : 0]], 254);
+                words[e][k >> 2] |= id << (8 * (k & 3));
             }
+            skin_weights_valid<K>(bd[e], denom, rdenom, w);             // warpfield.py:104-121
         }
+#pragma unroll
+        for (int k = 0; k < K; ++k) wq[k][e] = w[k];
     }
+    const int64_t j0 = slot * BRICK_VOXELS + threadIdx.x * VOX_PER_THREAD;
+    if constexpr (ID_BYTES == 4) {
+        *reinterpret_cast<uint4 *>(cache_ids + j0 * 4) = make_uint4(words[0][0], words[1][0], words[2][0], words[3][0]);
+    } else {
+        uint4 *c = reinterpret_cast<uint4 *>(cache_ids + j0 * 8);
+        c[0] = make_uint4(words[0][0], words[0][1], words[1][0], words[1][1]);
+        c[1] = make_uint4(words[2][0], words[2][1], words[3][0], words[3][1]);
+    }
+#pragma unroll
+    for (int k = 0; k < K; ++k)
+        *reinterpret_cast<float4 *>(cache_w + (slot * K + k) * BRICK_VOXELS + threadIdx.x * VOX_PER_THREAD) =
+            make_float4(wq[k][0], wq[k][1], wq[k][2], wq[k][3]);
     (void)any_valid;
 }
 
@@ -306,9 +336,9 @@ static int launch_skin_brick(ofx_volume *v, int max_cnt, cudaStream_t s)
     const size_t smem = 3 * CAND_TILE * sizeof(float) + (size_t)max_cnt * sizeof(unsigned short) + 16;
     OFX_REQUIRE(smem <= 200 * 1024, "ofx_set_graph: a brick has %d candidate nodes; unsupported", max_cnt);
     OFX_CUDA(cudaFuncSetAttribute(skin_brick_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    skin_brick_kernel<K><<<v->n_bricks, BRICK_THREADS, smem, s>>>(v->geom, v->node_rec, v->cutoff, v->brick_off,
-                                                                  v->brick_cnt, v->cand, v->brick_nodes,
-                                                                  v->anchor_cache, v->cache_bytes_per_voxel,
+    skin_brick_kernel<K><<<v->n_bricks, BRICK_THREADS, smem, s>>>(v->geom, v->node_rec, v->cutoff, v->denom,
+                                                                  v->brick_off, v->brick_cnt, v->cand, v->brick_nodes,
+                                                                  v->brick_slot, v->cache_ids, v->cache_w,
                                                                   v->scratch + 2);
     OFX_LAUNCH_CHECK();
     return 0;
@@ -329,13 +359,7 @@ extern "C" int ofx_set_graph(ofx_volume *v, const float *nodes, int32_t M, doubl
     v->cutoff = (float)(4.0 * node_coverage);                        // warpfield.py:109
     v->denom = (float)(2.0 * (node_coverage * node_coverage));       // warpfield.py:114
 
-    const int bpv = K <= 4 ? 4 : 8;
-    if (!v->anchor_cache || bpv != v->cache_bytes_per_voxel) {
-        if (v->anchor_cache) OFX_CUDA(cudaFree(v->anchor_cache));
-        v->anchor_cache = nullptr;
-        OFX_CUDA(cudaMalloc(&v->anchor_cache, (size_t)v->n_voxels * bpv));
-        v->cache_bytes_per_voxel = bpv;
-    }
+    v->cache_bytes_per_voxel = K <= 4 ? 4 : 8;
 
     const int nb = v->n_bricks;
     OFX_CUDA(cudaMemsetAsync(v->scratch, 0, 16 * sizeof(int), s));
@@ -344,11 +368,29 @@ extern "C" int ofx_set_graph(ofx_volume *v, const float *nodes, int32_t M, doubl
     OFX_LAUNCH_CHECK();
     scan_kernel<<<1, 1024, 0, s>>>(v->brick_cnt, nb, v->brick_off, nullptr, v->scratch);
     OFX_LAUNCH_CHECK();
-    int tm[2] = {0, 0};
+    // cache slots: rank of the brick among the bricks that have candidates (v->live is free scratch here)
+    scan_kernel<<<1, 1024, 0, s>>>(v->brick_cnt, nb, v->brick_slot, v->live, v->scratch + 6);
+    OFX_LAUNCH_CHECK();
+    int tm[8] = {0};
     OFX_CUDA(cudaMemcpyAsync(tm, v->scratch, sizeof(tm), cudaMemcpyDeviceToHost, s));
     OFX_CUDA(cudaStreamSynchronize(s));
     const int64_t total = tm[0];
     const int max_cnt = tm[1];
+    v->n_slots = tm[6];
+    const int64_t need_ids = (int64_t)v->n_slots * BRICK_VOXELS * v->cache_bytes_per_voxel;
+    const int64_t need_w = (int64_t)v->n_slots * BRICK_VOXELS * K;
+    if (need_ids > v->cache_ids_capacity) {
+        if (v->cache_ids) OFX_CUDA(cudaFree(v->cache_ids));
+        v->cache_ids = nullptr; v->cache_ids_capacity = 0;
+        OFX_CUDA(cudaMalloc(&v->cache_ids, (size_t)(need_ids + need_ids / 8)));
+        v->cache_ids_capacity = need_ids + need_ids / 8;
+    }
+    if (need_w > v->cache_w_capacity) {
+        if (v->cache_w) OFX_CUDA(cudaFree(v->cache_w));
+        v->cache_w = nullptr; v->cache_w_capacity = 0;
+        OFX_CUDA(cudaMalloc(&v->cache_w, (size_t)(need_w + need_w / 8) * sizeof(float)));
+        v->cache_w_capacity = need_w + need_w / 8;
+    }
     if (total > v->list_capacity) {
         if (v->cand) OFX_CUDA(cudaFree(v->cand));
         if (v->brick_nodes) OFX_CUDA(cudaFree(v->brick_nodes));

@@ -14,7 +14,9 @@ constexpr int BX = 4, BY = 8, BZ = 32;
 constexpr int VOX_PER_THREAD = 4;
 constexpr int BRICK_THREADS = BX * BY * (BZ / VOX_PER_THREAD);   // 256
 constexpr int BRICK_VOXELS = BX * BY * BZ;                       // 1024
-constexpr int NODE_REC_FLOATS = 16;   // {gx,gy,gz,0, R00..R22, T0,T1,T2} = 64 B, one TMA bulk copy
+constexpr int NODE_REC_FLOATS = 16;   // {gx,gy,gz,0, R00..R22, T0,T1,T2} = 64 B in global memory
+constexpr int NODE_XFORM_OFFSET = 4;  // the 48-byte {R, T} tail is what the fused kernels stage (one TMA bulk copy)
+constexpr int NODE_XFORM_FLOATS = 12;
 constexpr int MAX_BRICK_NODES = 255;  // local anchor ids are bytes, 0xFF = "no anchor"
 
 struct VolumeGeom {
@@ -54,9 +56,16 @@ struct ofx_volume {
     float *node_rec;          // M x NODE_REC_FLOATS
     int node_rec_capacity;
 
-    // anchor cache (device form of WarpField.skin_tsdf's cache, warpfield.py:131-141)
-    int cache_bytes_per_voxel;   // 4 (K<=4) or 8
-    uint8_t *anchor_cache;       // n_voxels * cache_bytes_per_voxel
+    // skin cache (device form of WarpField.skin_tsdf's cache, warpfield.py:131-141), brick-major and
+    // compact: one slot per brick that has candidate nodes.  Voxel j = 4*thread + e of slot s:
+    //   ids      cache_ids[(s*1024 + j) * id_bytes + k]      brick-local node id, 0xFF = not skin-valid
+    //   weights  cache_w[(s*K + k)*1024 + j]                 normalised float32 weight (warpfield.py:121)
+    int cache_bytes_per_voxel;   // id_bytes: 4 (K<=4) or 8
+    uint8_t *cache_ids;
+    float *cache_w;
+    int64_t cache_ids_capacity, cache_w_capacity;   // bytes / floats allocated
+    int *brick_slot;             // n_bricks: slot of a brick (meaningful where brick_cnt > 0)
+    int n_slots;
     int *brick_cnt;              // n_bricks: candidate count, later used-node count
     int *brick_off;              // n_bricks: offset into brick_nodes / cand
     float *brick_radius;         // n_bricks
