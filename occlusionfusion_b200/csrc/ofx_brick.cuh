@@ -15,8 +15,8 @@ struct FrameArgs {
     const float *colour_im;
     Camera cam;
     FastCam fc;                  // the same intrinsics + the error terms of the certified float32 pixel
-    double trunc, rtrunc, obs;   // rtrunc = RN(1/trunc)
-    float obsf;
+    double trunc;
+    FuseArgs fu;
     float ntrunc_up, ntrunc_dn;  // the two float32 neighbours of -trunc (up >= -trunc >= dn)
 };
 
@@ -29,7 +29,8 @@ static inline FrameArgs make_frame_args(const float *depth, const float *colour,
     fa.cam = Camera{intr[0], intr[1], intr[2], intr[3], H, W};
     fa.fc = FastCam{intr[0], intr[1], intr[2], intr[3], 6.2e-8f * fabsf(intr[2]) + 1e-6f,
                     6.2e-8f * fabsf(intr[3]) + 1e-6f, W, H};
-    fa.trunc = trunc; fa.rtrunc = 1.0 / trunc; fa.obs = obs; fa.obsf = (float)obs;
+    fa.trunc = trunc;
+    fa.fu = FuseArgs{trunc, 1.0 / trunc, obs, (float)obs, (double)(float)obs == obs ? 1 : 0};
     const float t = (float)(-trunc);
     if ((double)t >= -trunc) { fa.ntrunc_up = t; fa.ntrunc_dn = ((double)t == -trunc) ? t : nextafterf(t, -INFINITY); }
     else { fa.ntrunc_dn = t; fa.ntrunc_up = nextafterf(t, INFINITY); }
@@ -199,12 +200,14 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
     }
     const float px = __ldg(g.px + lx), py = __ldg(g.py + iy);
 
-    unsigned upd = 0;
-    float dsel[VOX_PER_THREAD], zsel[VOX_PER_THREAD];
-    float ncol[VOX_PER_THREAD];
+    // ---- phase 1: warp + pixel of each voxel (no memory traffic beyond shared memory) ----
+    int pixs[VOX_PER_THREAD];
+    float zsel[VOX_PER_THREAD];
+    unsigned cand = 0;
 #pragma unroll
     for (int e = 0; e < VOX_PER_THREAD; ++e) {
-        if (e >= n_vox) continue;
+        pixs[e] = 0; zsel[e] = 0.f;
+        if (!VEC && e >= n_vox) continue;
         const float pz = __ldg(g.pz + iz0 + e);
         float qx = px, qy = py, qz = pz;
         bool skin_ok = true;                                          // source frame: all valid, tsdf.py:395-398
@@ -222,42 +225,55 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
             const int st = project_fast(qx, qy, qz, fa.fc, u, v);     // tsdf.py:589-593, certified float32
             if (st == 0) continue;
             if (st == 2 && !project(qx, qy, qz, fa.cam, u, v)) continue;   // undecided: the float64 original
-            const int pix = v * fa.cam.W + u;
-            const float d = __ldg(fa.depth + pix);
-            // depth - z >= -trunc in float64 (tsdf.py:608-609).  fl32 is monotone: a float32 difference
-            // above / below the float32 neighbours of -trunc decides; only a tie needs float64
-            const float df = d - qz;
-            if (!(d > 0.0f)) continue;
-            if (!(df > fa.ntrunc_up)) {
-                if (df < fa.ntrunc_dn || !((double)d - (double)qz >= -fa.trunc)) continue;
-            }
-            dsel[e] = d; zsel[e] = qz;
-            ncol[e] = __ldg(fa.colour_im + pix);
-            upd |= 1u << e;
+            pixs[e] = v * fa.cam.W + u;
+            zsel[e] = qz;
+            cand |= 1u << e;
         }
     }
 
     if constexpr (MODE != MODE_DEFORM) {
+        // ---- phase 2: the (up to four) depth gathers in flight together, then the visibility test ----
+        if (!cand) return;
+        float dsel[VOX_PER_THREAD];
+#pragma unroll
+        for (int e = 0; e < VOX_PER_THREAD; ++e) dsel[e] = (cand & (1u << e)) ? __ldg(fa.depth + pixs[e]) : 0.0f;
+        unsigned upd = 0;
+#pragma unroll
+        for (int e = 0; e < VOX_PER_THREAD; ++e) {
+            // depth > 0 and depth - z >= -trunc in float64 (tsdf.py:608-609).  fl32 is monotone: a float32
+            // difference above / below the float32 neighbours of -trunc decides; only a tie needs float64
+            const float d = dsel[e], df = d - zsel[e];
+            bool vis = d > 0.0f && df >= fa.ntrunc_dn;
+            if (vis && !(df > fa.ntrunc_up)) vis = (double)d - (double)zsel[e] >= -fa.trunc;
+            if (vis) upd |= 1u << e;
+        }
         if (!upd) return;
-        float tt[VOX_PER_THREAD], ww[VOX_PER_THREAD], cc[VOX_PER_THREAD];
+
+        // ---- phase 3: volume words + new colours in flight together, fuse, store ----
+        float tt[VOX_PER_THREAD], ww[VOX_PER_THREAD], cc[VOX_PER_THREAD], ncol[VOX_PER_THREAD];
         if (VEC) {
             const float4 t4 = *reinterpret_cast<const float4 *>(tsdf + vox0);
             const float4 w4 = *reinterpret_cast<const float4 *>(weight + vox0);
             const float4 c4 = *reinterpret_cast<const float4 *>(colour + vox0);
+#pragma unroll
+            for (int e = 0; e < VOX_PER_THREAD; ++e) ncol[e] = (upd & (1u << e)) ? __ldg(fa.colour_im + pixs[e]) : 0.0f;
             tt[0] = t4.x; tt[1] = t4.y; tt[2] = t4.z; tt[3] = t4.w;
             ww[0] = w4.x; ww[1] = w4.y; ww[2] = w4.z; ww[3] = w4.w;
             cc[0] = c4.x; cc[1] = c4.y; cc[2] = c4.z; cc[3] = c4.w;
         } else {
 #pragma unroll
             for (int e = 0; e < VOX_PER_THREAD; ++e)
-                if (upd & (1u << e)) { tt[e] = tsdf[vox0 + e]; ww[e] = weight[vox0 + e]; cc[e] = colour[vox0 + e]; }
+                if (upd & (1u << e)) {
+                    tt[e] = tsdf[vox0 + e]; ww[e] = weight[vox0 + e]; cc[e] = colour[vox0 + e];
+                    ncol[e] = __ldg(fa.colour_im + pixs[e]);
+                }
         }
+        float wsum = 0.0f;
 #pragma unroll
         for (int e = 0; e < VOX_PER_THREAD; ++e)
             if (upd & (1u << e)) {
-                fuse_voxel(tt[e], ww[e], cc[e], (double)dsel[e] - (double)zsel[e], ncol[e], fa.trunc, fa.rtrunc, fa.obs,
-                           fa.obsf);
-                c_wsum += (unsigned)ww[e];
+                fuse_voxel(tt[e], ww[e], cc[e], (double)dsel[e] - (double)zsel[e], ncol[e], fa.fu);
+                wsum += ww[e];
             }
         if (VEC) {
             *reinterpret_cast<float4 *>(tsdf + vox0) = make_float4(tt[0], tt[1], tt[2], tt[3]);
@@ -268,6 +284,7 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
             for (int e = 0; e < VOX_PER_THREAD; ++e)
                 if (upd & (1u << e)) { tsdf[vox0 + e] = tt[e]; weight[vox0 + e] = ww[e]; colour[vox0 + e] = cc[e]; }
         }
+        c_wsum += (unsigned)wsum;        // weights are integer-valued counters (obs_weight = 1)
         c_upd += __popc(upd);
     }
 }

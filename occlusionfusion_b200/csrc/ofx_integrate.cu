@@ -165,7 +165,7 @@ brick_cull_kernel(GraphArgs ga, const float4 *__restrict__ brick_box, int n_acti
 //   bar_full   producer -> consumers: descriptor written
 //   bar_data   TMA -> consumers: the transforms have landed (transaction bytes)
 //   bar_empty  consumers -> producer: all eight warps are done with the slot and its records
-constexpr int N_SLOTS = 8;
+constexpr int N_SLOTS = 4;
 constexpr int RING_RECS = 512;                              // >= 2 * MAX_BRICK_NODES: two of the largest bricks
 constexpr int CONSUMER_WARPS = BRICK_THREADS / 32;          // 8
 constexpr int PERSISTENT_THREADS = BRICK_THREADS + 32;      // + 1 producer warp
@@ -250,6 +250,14 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
                 bulk_g2s(rec + i * REC_STRIDE,
                          ga.node_rec + (int64_t)__ldg(ga.brick_nodes + o + i) * NODE_REC_FLOATS + NODE_XFORM_OFFSET,
                          REC_BYTES, &bar_data[slot]);
+            // the brick's skin-cache slot (ids + K weight planes, contiguous) starts its way from DRAM to L2
+            // now, a few bricks before the consumers ask for it
+            if (lane <= K) {
+                if (lane == 0)
+                    bulk_prefetch_l2(ga.cache_ids + (int64_t)cslot * BRICK_VOXELS * ga.id_bytes, BRICK_VOXELS * ga.id_bytes);
+                else
+                    bulk_prefetch_l2(ga.cache_w + ((int64_t)cslot * K + (lane - 1)) * BRICK_VOXELS, BRICK_VOXELS * 4u);
+            }
             int f = 0;
             if (lane == 0) f = atomicAdd(work_counter, 1);
             idx = (int)gridDim.x + __shfl_sync(0xffffffffu, f, 0);

@@ -230,31 +230,44 @@ __device__ __forceinline__ int project_fast(float qx, float qy, float qz, const 
 
 // Running-average update of one voxel (tsdf.py:466, 373-375, 479-493).
 // diff = depth - z (float64), already known to satisfy depth > 0 && diff >= -trunc.
-__device__ __forceinline__ void fuse_voxel(float &tsdf, float &weight, float &colour, double diff,
-                                           float new_colour, double trunc, double rtrunc, double obs, float obsf)
+struct FuseArgs {
+    double trunc, rtrunc, obs;   // rtrunc = RN(1/trunc), computed once on the host
+    float obsf;
+    int obs_is_f32;              // obs == (double)obsf: then f32(f64(w) + obs) == w + obsf (see below)
+};
+
+// byte k of an integer-valued colour word as float: bits 0x4B0000bb are 2^23 + bb
+__device__ __forceinline__ float byte_to_float(uint32_t word, uint32_t selector)
 {
-    // rtrunc = RN(1/trunc), computed once on the host
-    const double dist = diff >= trunc ? 1.0 : fmin(1.0, div_rn(diff, trunc, rtrunc));
+    return __uint_as_float(__byte_perm(word, 0x4B000000u, selector)) - 8388608.0f;
+}
+
+__device__ __forceinline__ void fuse_voxel(float &tsdf, float &weight, float &colour, double diff, float new_colour,
+                                           const FuseArgs &fu)
+{
+    const double dist = diff >= fu.trunc ? 1.0 : fmin(1.0, div_rn(diff, fu.trunc, fu.rtrunc));
     const float w_old = weight;
-    const float w_new = (float)((double)w_old + obs);
+    // f32(f64(w) + obs): when obs is a float32 value the float64 sum is either exact (exponents within
+    // 29 bits) or the small operand is far below half an ulp32 of the large one, so the single float32
+    // addition rounds identically
+    const float w_new = fu.obs_is_f32 ? w_old + fu.obsf : (float)((double)w_old + fu.obs);
     const float prod = w_old * tsdf;
-    const double num = (double)prod + obs * dist, den = (double)w_new;
+    const double num = (double)prod + fu.obs * dist, den = (double)w_new;
     // free space seen again (tsdf = 1, dist = 1): num == den, the quotient is exactly 1
     tsdf = (num == den && den != 0.0) ? 1.0f : (float)div_rn(num, den, __drcp_rn(den));
     weight = w_new;
 
-    const float oc = colour, nc = new_colour;
-    const float ob = floorf(oc / 65536.0f);
-    const float og = floorf((oc - ob * 65536.0f) / 256.0f);
-    const float orr = oc - ob * 65536.0f - og * 256.0f;
-    const float nb = floorf(nc / 65536.0f);
-    const float ng = floorf((nc - nb * 65536.0f) / 256.0f);
-    const float nr = nc - nb * 65536.0f - ng * 256.0f;
+    // colour channels (tsdf.py:479-493).  The packed words are integers below 2^24 with byte-sized
+    // channels, so floor(c/65536) etc. are the bytes of the integer; the blend is the reference's
+    // float32 expression; rintf through the 1.5*2^23 constant (values < 2^22); repacking is exact.
+    const uint32_t oc = (uint32_t)colour, nc = (uint32_t)new_colour;
+    const float ob = byte_to_float(oc, 0x7442u), og = byte_to_float(oc, 0x7441u), orr = byte_to_float(oc, 0x7440u);
+    const float nb = byte_to_float(nc, 0x7442u), ng = byte_to_float(nc, 0x7441u), nr = byte_to_float(nc, 0x7440u);
     const float rw = __frcp_rn(w_new);
-    const float b = fminf(255.0f, rintf(div_rn(w_old * ob + obsf * nb, w_new, rw)));
-    const float g = fminf(255.0f, rintf(div_rn(w_old * og + obsf * ng, w_new, rw)));
-    const float r = fminf(255.0f, rintf(div_rn(w_old * orr + obsf * nr, w_new, rw)));
-    colour = b * 65536.0f + g * 256.0f + r;
+    const float b = fminf(255.0f, (div_rn(w_old * ob + fu.obsf * nb, w_new, rw) + 12582912.0f) - 12582912.0f);
+    const float g = fminf(255.0f, (div_rn(w_old * og + fu.obsf * ng, w_new, rw) + 12582912.0f) - 12582912.0f);
+    const float r = fminf(255.0f, (div_rn(w_old * orr + fu.obsf * nr, w_new, rw) + 12582912.0f) - 12582912.0f);
+    colour = __fmaf_rn(b, 65536.0f, __fmaf_rn(g, 256.0f, r));
 }
 
 // ---- TMA (1-D bulk copy) + mbarrier helpers ------------------------------------------------
@@ -314,6 +327,12 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, u
                      smem_u32(dst_smem)),
                  "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
+}
+
+// asynchronous DRAM -> L2 prefetch of a contiguous range (bytes % 16 == 0, 16-byte aligned)
+__device__ __forceinline__ void bulk_prefetch_l2(const void *src_gmem, uint32_t bytes)
+{
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src_gmem), "r"(bytes) : "memory");
 }
 
 }  // namespace ofx

@@ -60,3 +60,15 @@ print("\nhottest source lines (inlined callers repeat their callees' instruction
 for a in agg[:45]:
     per = f"{a[0] * 32 / nvox:6.1f}/vox" if nvox else ""
     print(f"  {a[0] / tot * 100:5.1f}% {per} {a[1]:6d} smp  {a[2]}:{a[3]}  {a[4]}")
+
+# warp-state sampling: why warps that could not issue were stalled (all instructions summed)
+rows = list(csv.reader(io.StringIO(ncu("--page", "source", "--csv"))))
+hh = rows[1]
+cols = [i for i, n in enumerate(hh) if n.startswith("stall_") and "Not Issued" not in n]
+tot_st = collections.Counter()
+for r in rows[2:]:
+    for i in cols:
+        if i < len(r) and r[i].isdigit():
+            tot_st[hh[i]] += int(r[i])
+ts2 = sum(tot_st.values()) or 1
+print("\nstall reasons (all samples): " + ", ".join(f"{k[6:]} {v / ts2 * 100:.1f}%" for k, v in tot_st.most_common(10)))
