@@ -9,7 +9,8 @@ import numpy as np
 import torch
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "lib", "libofx.so")
+# OFX_LIB: an experimental build of the same library (tools/ab_bench.sh); never a different implementation
+LIB_PATH = os.environ.get("OFX_LIB") or os.path.join(_PKG, "lib", "libofx.so")
 
 OFX_MAX_K = 8
 OFX_N_STATS = 4

@@ -36,9 +36,11 @@ def _stale():
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force=False, verbose=False):
-    if not force and not _stale():
+def build(force=False, verbose=False, out=None, defines=()):
+    """out / defines: build an experimental variant (tools/ab_bench.sh) next to the product library."""
+    if out is None and not force and not _stale():
         return LIB
+    lib_path = out or LIB
     os.makedirs(LIB_DIR, exist_ok=True)
     nvcc = _nvcc()
     env = dict(os.environ)
@@ -49,23 +51,25 @@ def build(force=False, verbose=False):
     objs = []
     logs = []
     for src in SOURCES:
-        obj = os.path.join(LIB_DIR, src.replace(".cu", ".o"))
-        cmd = [nvcc, *ccbin, *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+        obj = os.path.join(LIB_DIR, src.replace(".cu", ".o" if out is None else "." + os.path.basename(out) + ".o"))
+        cmd = [nvcc, *ccbin, *NVCC_FLAGS, *["-D" + d for d in defines], "-c", os.path.join(CSRC, src), "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True, env=env)
         logs.append(f"$ {' '.join(cmd)}\n{r.stdout}{r.stderr}")
         if r.returncode != 0:
             raise RuntimeError("nvcc failed:\n" + logs[-1])
         objs.append(obj)
-    cmd = [nvcc, *ccbin, "-shared", "-o", LIB, *objs]
+    cmd = [nvcc, *ccbin, "-shared", "-o", lib_path, *objs]
     r = subprocess.run(cmd, capture_output=True, text=True, env=env)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n" + r.stdout + r.stderr)
-    with open(os.path.join(LIB_DIR, "build.log"), "w") as f:
+    with open(os.path.join(LIB_DIR, "build.log" if out is None else os.path.basename(out) + ".log"), "w") as f:
         f.write("\n".join(logs))
     if verbose:
         print("\n".join(logs))
-    return LIB
+    return lib_path
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))
+    defs = [a[2:] for a in sys.argv[1:] if a.startswith("-D")]
+    outs = [a.split("=", 1)[1] for a in sys.argv[1:] if a.startswith("--out=")]
+    print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv, out=outs[0] if outs else None, defines=defs))

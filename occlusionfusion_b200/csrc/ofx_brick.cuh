@@ -2,6 +2,9 @@
 // the per-voxel warp (cached anchors -> weights -> linear blend), brick-level frustum culling and
 // the per-thread body (4 consecutive z voxels: warp, project, test, fuse, store).
 #pragma once
+#ifndef OFX_STRAIGHT
+#define OFX_STRAIGHT 1
+#endif
 #include <cmath>
 
 #include "ofx_volume.cuh"
@@ -30,7 +33,9 @@ static inline FrameArgs make_frame_args(const float *depth, const float *colour,
     fa.fc = FastCam{intr[0], intr[1], intr[2], intr[3], 6.2e-8f * fabsf(intr[2]) + 1e-6f,
                     6.2e-8f * fabsf(intr[3]) + 1e-6f, W, H};
     fa.trunc = trunc;
-    fa.fu = FuseArgs{trunc, 1.0 / trunc, obs, (float)obs, (double)(float)obs == obs ? 1 : 0};
+    float tu = (float)trunc;
+    if (!((double)tu > trunc)) tu = nextafterf(tu, INFINITY);
+    fa.fu = FuseArgs{trunc, 1.0 / trunc, obs, (float)obs, (double)(float)obs == obs ? 1 : 0, tu};
     const float t = (float)(-trunc);
     if ((double)t >= -trunc) { fa.ntrunc_up = t; fa.ntrunc_dn = ((double)t == -trunc) ? t : nextafterf(t, -INFINITY); }
     else { fa.ntrunc_dn = t; fa.ntrunc_up = nextafterf(t, INFINITY); }
@@ -178,7 +183,11 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
     uint32_t ids[VOX_PER_THREAD][2];
     float wk[VOX_PER_THREAD][K];
 #pragma unroll
-    for (int e = 0; e < VOX_PER_THREAD; ++e) ids[e][0] = ids[e][1] = 0xFFFFFFFFu;
+    for (int e = 0; e < VOX_PER_THREAD; ++e) {
+        ids[e][0] = ids[e][1] = 0xFFFFFFFFu;
+#pragma unroll
+        for (int k = 0; k < K; ++k) wk[e][k] = 0.0f;
+    }
     if constexpr (MODE != MODE_IDENTITY) {
         if (n_used > 0) {
             const int64_t j0 = (int64_t)slot * BRICK_VOXELS + t * VOX_PER_THREAD;
@@ -213,24 +222,31 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
         bool skin_ok = true;                                          // source frame: all valid, tsdf.py:395-398
         if constexpr (MODE != MODE_IDENTITY) {
             skin_ok = (ids[e][0] & 0xFFu) != 0xFFu;
+#if OFX_STRAIGHT
+            // straight-line: a voxel without anchors blends record 0 with zero weights and is masked below
+            const uint32_t idw[2] = {skin_ok ? ids[e][0] : 0u, skin_ok ? ids[e][1] : 0u};
+            warp_voxel<K>(idw, wk[e], s_rec, px, py, pz, qx, qy, qz);
+#else
             if (skin_ok) warp_voxel<K>(ids[e], wk[e], s_rec, px, py, pz, qx, qy, qz);
+#endif
         }
         if constexpr (MODE == MODE_DEFORM) {
+            if (!skin_ok) { qx = px; qy = py; qz = pz; }              // registration_fusion.py:161,180
             if (out_pts) { out_pts[3 * (vox0 + e)] = qx; out_pts[3 * (vox0 + e) + 1] = qy; out_pts[3 * (vox0 + e) + 2] = qz; }
             if (out_valid) out_valid[vox0 + e] = skin_ok ? 1 : 0;
         } else {
-            if (!skin_ok) continue;                                   // tsdf.py:464
-            ++c_valid;
+#if !OFX_STRAIGHT
+            if (!skin_ok) continue;
+#endif
             int u, v;
-            const int st = project_fast(qx, qy, qz, fa.fc, u, v);     // tsdf.py:589-593, certified float32
-            if (st == 0) continue;
-            if (st == 2 && !project(qx, qy, qz, fa.cam, u, v)) continue;   // undecided: the float64 original
+            int st = project_fast(qx, qy, qz, fa.fc, u, v);           // tsdf.py:589-593, certified float32
+            if (st == 2 && skin_ok) st = project(qx, qy, qz, fa.cam, u, v) ? 1 : 0;   // undecided (~1e-4): the float64 original
+            c_valid += skin_ok ? 1u : 0u;                             // tsdf.py:464
             pixs[e] = v * fa.cam.W + u;
             zsel[e] = qz;
-            cand |= 1u << e;
+            if (skin_ok && st == 1) cand |= 1u << e;
         }
     }
-
     if constexpr (MODE != MODE_DEFORM) {
         // ---- phase 2: the (up to four) depth gathers in flight together, then the visibility test ----
         if (!cand) return;
@@ -272,7 +288,7 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
 #pragma unroll
         for (int e = 0; e < VOX_PER_THREAD; ++e)
             if (upd & (1u << e)) {
-                fuse_voxel(tt[e], ww[e], cc[e], (double)dsel[e] - (double)zsel[e], ncol[e], fa.fu);
+                fuse_voxel(tt[e], ww[e], cc[e], dsel[e], zsel[e], ncol[e], fa.fu);
                 wsum += ww[e];
             }
         if (VEC) {

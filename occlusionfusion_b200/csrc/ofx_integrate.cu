@@ -165,7 +165,16 @@ brick_cull_kernel(GraphArgs ga, const float4 *__restrict__ brick_box, int n_acti
 //   bar_full   producer -> consumers: descriptor written
 //   bar_data   TMA -> consumers: the transforms have landed (transaction bytes)
 //   bar_empty  consumers -> producer: all eight warps are done with the slot and its records
-constexpr int N_SLOTS = 4;
+#ifndef OFX_N_SLOTS
+#define OFX_N_SLOTS 3
+#endif
+#ifndef OFX_MIN_CTAS
+#define OFX_MIN_CTAS 3
+#endif
+#ifndef OFX_PREFETCH_VOLUME
+#define OFX_PREFETCH_VOLUME 0
+#endif
+constexpr int N_SLOTS = OFX_N_SLOTS;
 constexpr int RING_RECS = 512;                              // >= 2 * MAX_BRICK_NODES: two of the largest bricks
 constexpr int CONSUMER_WARPS = BRICK_THREADS / 32;          // 8
 constexpr int PERSISTENT_THREADS = BRICK_THREADS + 32;      // + 1 producer warp
@@ -178,7 +187,7 @@ struct SlotInfo {
 };
 
 template <int K, bool VEC>
-__global__ void __launch_bounds__(PERSISTENT_THREADS, K <= 4 ? 4 : 3)
+__global__ void __launch_bounds__(PERSISTENT_THREADS, K <= 4 ? OFX_MIN_CTAS : 3)
 fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ weight, float *__restrict__ colour,
                         GraphArgs ga, FrameArgs fa, const int *__restrict__ live, const int *__restrict__ n_live_ptr,
                         int *__restrict__ work_counter, unsigned long long *__restrict__ stats)
@@ -258,6 +267,18 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
                 else
                     bulk_prefetch_l2(ga.cache_w + ((int64_t)cslot * K + (lane - 1)) * BRICK_VOXELS, BRICK_VOXELS * 4u);
             }
+#if OFX_PREFETCH_VOLUME
+            if (VEC) {
+                const int lx = bc.lx0 + (lane >> 3), iy = bc.iy0 + (lane & 7);
+                if (lx < g.nx && iy < g.Dy) {
+                    const int64_t row = ((int64_t)lx * g.Dy + iy) * g.Dz + bc.iz0;
+                    const uint32_t bytes = (uint32_t)min(BZ, g.Dz - bc.iz0) * 4u;
+                    bulk_prefetch_l2(tsdf + row, bytes);
+                    bulk_prefetch_l2(weight + row, bytes);
+                    bulk_prefetch_l2(colour + row, bytes);
+                }
+            }
+#endif
             int f = 0;
             if (lane == 0) f = atomicAdd(work_counter, 1);
             idx = (int)gridDim.x + __shfl_sync(0xffffffffu, f, 0);

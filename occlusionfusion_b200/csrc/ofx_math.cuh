@@ -6,6 +6,12 @@
 // op order restated in DESIGN.md ("contract arithmetic").  Reference lines are relative to
 // /root/reference/fusion_with_occlusion/.
 #pragma once
+#ifndef OFX_SLEEP_NS
+#define OFX_SLEEP_NS 2000
+#endif
+#ifndef OFX_KEEP_ONE
+#define OFX_KEEP_ONE 1
+#endif
 #include <cstdint>
 #include <cuda_runtime.h>
 
@@ -217,15 +223,17 @@ __device__ __forceinline__ bool fast_pixel(float q, float f, float c, float eps0
 // 0 = certainly no pixel, 1 = pixel (u, v) certain, 2 = undecided (use project()).
 __device__ __forceinline__ int project_fast(float qx, float qy, float qz, const FastCam &fc, int &u, int &v)
 {
-    if (!(qz > 0.0f)) return 0;
+    // straight-line on purpose: the caller evaluates four voxels back to back and the scheduler
+    // interleaves their dependency chains
     float rz;
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rz) : "f"(qz));
     bool in_u, in_v;
     const bool ok_u = fast_pixel(qx, fc.fx, fc.cx, fc.eps0x, rz, fc.W, u, in_u);
     const bool ok_v = fast_pixel(qy, fc.fy, fc.cy, fc.eps0y, rz, fc.H, v, in_v);
-    // a coordinate that is certainly outside decides the voxel even if the other one is undecided
-    if ((ok_u && !in_u) || (ok_v && !in_v)) return 0;
-    return (ok_u && ok_v) ? 1 : 2;
+    // z <= 0 has no pixel; a coordinate that is certainly outside decides the voxel even if the other
+    // one is undecided
+    const bool dead = !(qz > 0.0f) || (ok_u && !in_u) || (ok_v && !in_v);
+    return dead ? 0 : ((ok_u && ok_v) ? 1 : 2);
 }
 
 // Running-average update of one voxel (tsdf.py:466, 373-375, 479-493).
@@ -234,6 +242,7 @@ struct FuseArgs {
     double trunc, rtrunc, obs;   // rtrunc = RN(1/trunc), computed once on the host
     float obsf;
     int obs_is_f32;              // obs == (double)obsf: then f32(f64(w) + obs) == w + obsf (see below)
+    float trunc_up;              // smallest float32 > trunc
 };
 
 // byte k of an integer-valued colour word as float: bits 0x4B0000bb are 2^23 + bb
@@ -242,19 +251,28 @@ __device__ __forceinline__ float byte_to_float(uint32_t word, uint32_t selector)
     return __uint_as_float(__byte_perm(word, 0x4B000000u, selector)) - 8388608.0f;
 }
 
-__device__ __forceinline__ void fuse_voxel(float &tsdf, float &weight, float &colour, double diff, float new_colour,
+__device__ __forceinline__ void fuse_voxel(float &tsdf, float &weight, float &colour, float d, float z, float new_colour,
                                            const FuseArgs &fu)
 {
-    const double dist = diff >= fu.trunc ? 1.0 : fmin(1.0, div_rn(diff, fu.trunc, fu.rtrunc));
     const float w_old = weight;
     // f32(f64(w) + obs): when obs is a float32 value the float64 sum is either exact (exponents within
     // 29 bits) or the small operand is far below half an ulp32 of the large one, so the single float32
     // addition rounds identically
     const float w_new = fu.obs_is_f32 ? w_old + fu.obsf : (float)((double)w_old + fu.obs);
-    const float prod = w_old * tsdf;
-    const double num = (double)prod + fu.obs * dist, den = (double)w_new;
-    // free space seen again (tsdf = 1, dist = 1): num == den, the quotient is exactly 1
-    tsdf = (num == den && den != 0.0) ? 1.0f : (float)div_rn(num, den, __drcp_rn(den));
+    // Free space seen again -- the bulk of all updates: dist = 1 and tsdf = 1.  fl32(d - z) above the
+    // float32 successor of trunc proves d - z >= trunc (rounding is monotone), i.e. dist = 1; then
+    // num = w + obs (exact in float64) and the quotient is exactly 1 iff fl32(w + obs) was exact
+    // (Fast2Sum, |w| >= |obs|), otherwise the float64 expression is evaluated.
+    const float sum_err = fu.obsf - (w_new - w_old);
+    const bool keep_one = OFX_KEEP_ONE && fu.obs_is_f32 && (d - z) > fu.trunc_up && tsdf == 1.0f && w_old >= fabsf(fu.obsf) && sum_err == 0.0f &&
+                          w_new != 0.0f;
+    if (!keep_one) {
+        const double diff = (double)d - (double)z;                      // tsdf.py:608, exact
+        const double dist = diff >= fu.trunc ? 1.0 : fmin(1.0, div_rn(diff, fu.trunc, fu.rtrunc));
+        const float prod = w_old * tsdf;
+        const double num = (double)prod + fu.obs * dist, den = (double)w_new;
+        tsdf = (num == den && den != 0.0) ? 1.0f : (float)div_rn(num, den, __drcp_rn(den));
+    }
     weight = w_new;
 
     // colour channels (tsdf.py:479-493).  The packed words are integers below 2^24 with byte-sized
@@ -316,7 +334,7 @@ __device__ __forceinline__ void mbar_wait_sleep(uint64_t *bar, uint32_t parity)
             : "r"(smem_u32(bar)), "r"(parity)
             : "memory");
         if (done) break;
-        __nanosleep(256);
+        __nanosleep(OFX_SLEEP_NS);
     }
 }
 // global -> shared bulk copy through the TMA unit (SASS: UBLKCP); bytes % 16 == 0, both
