@@ -2,9 +2,6 @@
 // the per-voxel warp (cached anchors -> weights -> linear blend), brick-level frustum culling and
 // the per-thread body (4 consecutive z voxels: warp, project, test, fuse, store).
 #pragma once
-#ifndef OFX_STRAIGHT
-#define OFX_STRAIGHT 1
-#endif
 #include <cmath>
 
 #include "ofx_volume.cuh"
@@ -49,9 +46,7 @@ struct GraphArgs {
     const int *cnt;
     const int *brick_nodes;
     const int *brick_slot;   // cache slot of a brick
-    const uint8_t *cache_ids;
-    const float *cache_w;
-    int id_bytes;            // 4 or 8
+    const uint8_t *cache;    // skin cache, slot_bytes_of(Kp) per slot (layout: ofx_volume.cuh)
     float cutoff, denom;
 };
 
@@ -63,8 +58,8 @@ constexpr uint32_t REC_BYTES = NODE_XFORM_FLOATS * 4u;
 
 // q = sum_k w_k (R_k p + T_k) with the cached anchors and weights of one voxel (warpfield.py:225-226).
 // (The reference skips w == 0, warpfield.py:219: cached voxels have w >= exp(-8.0001) / (K + 1e-6) > 0.)
-template <int K>
-__device__ __forceinline__ void warp_voxel(const uint32_t (&ids)[2], const float (&w)[K], const float *__restrict__ s_rec,
+template <int K, int KP>
+__device__ __forceinline__ void warp_voxel(const uint32_t (&ids)[2], const float (&w)[KP], const float *__restrict__ s_rec,
                                            float px, float py, float pz, float &qx, float &qy, float &qz)
 {
     float ax = 0.f, ay = 0.f, az = 0.f;
@@ -167,8 +162,8 @@ template <int K, bool VEC, int MODE>
 __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__restrict__ tsdf,
                                                   float *__restrict__ weight, float *__restrict__ colour,
                                                   const GraphArgs &ga, const FrameArgs &fa,
-                                                  const float *__restrict__ s_rec, const BrickCoord &bc, int n_used,
-                                                  int slot, int t, float *__restrict__ out_pts,
+                                                  const float *__restrict__ s_rec, const uint8_t *__restrict__ s_slot,
+                                                  const BrickCoord &bc, int n_used, int t, float *__restrict__ out_pts,
                                                   uint8_t *__restrict__ out_valid, unsigned &c_upd, unsigned &c_valid,
                                                   unsigned &c_wsum)
 {
@@ -179,34 +174,11 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
     const int64_t vox0 = ((int64_t)lx * g.Dy + iy) * g.Dz + iz0;
     const int n_vox = min(VOX_PER_THREAD, g.Dz - iz0);
 
-    // skin-cache words of this thread's four voxels: ids (one or two 16-byte loads) + K weight float4s
-    uint32_t ids[VOX_PER_THREAD][2];
-    float wk[VOX_PER_THREAD][K];
-#pragma unroll
-    for (int e = 0; e < VOX_PER_THREAD; ++e) {
-        ids[e][0] = ids[e][1] = 0xFFFFFFFFu;
-#pragma unroll
-        for (int k = 0; k < K; ++k) wk[e][k] = 0.0f;
-    }
-    if constexpr (MODE != MODE_IDENTITY) {
-        if (n_used > 0) {
-            const int64_t j0 = (int64_t)slot * BRICK_VOXELS + t * VOX_PER_THREAD;
-            if constexpr (K <= 4) {
-                const uint4 q = __ldg(reinterpret_cast<const uint4 *>(ga.cache_ids + j0 * 4));
-                ids[0][0] = q.x; ids[1][0] = q.y; ids[2][0] = q.z; ids[3][0] = q.w;
-            } else {
-                const uint4 *c = reinterpret_cast<const uint4 *>(ga.cache_ids + j0 * 8);
-                const uint4 q0 = __ldg(c), q1 = __ldg(c + 1);
-                ids[0][0] = q0.x; ids[0][1] = q0.y; ids[1][0] = q0.z; ids[1][1] = q0.w;
-                ids[2][0] = q1.x; ids[2][1] = q1.y; ids[3][0] = q1.z; ids[3][1] = q1.w;
-            }
-#pragma unroll
-            for (int k = 0; k < K; ++k) {
-                const float4 w4 = __ldg(reinterpret_cast<const float4 *>(ga.cache_w + ((int64_t)slot * K + k) * BRICK_VOXELS) + t);
-                wk[0][k] = w4.x; wk[1][k] = w4.y; wk[2][k] = w4.z; wk[3][k] = w4.w;
-            }
-        }
-    }
+    // the brick's skin-cache slot sits in shared memory (one TMA bulk copy): per voxel one ids word and
+    // one weight float4 per group of four anchors, read just in time (conflict-free: lane stride 4 / 16 B)
+    constexpr int KP = K <= 4 ? 4 : 8;
+    const uint32_t *s_ids = reinterpret_cast<const uint32_t *>(s_slot) + t;
+    const float4 *s_w = reinterpret_cast<const float4 *>(s_slot + BRICK_VOXELS * KP) + t;
     const float px = __ldg(g.px + lx), py = __ldg(g.py + iy);
 
     // ---- phase 1: warp + pixel of each voxel (no memory traffic beyond shared memory) ----
@@ -221,23 +193,30 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
         float qx = px, qy = py, qz = pz;
         bool skin_ok = true;                                          // source frame: all valid, tsdf.py:395-398
         if constexpr (MODE != MODE_IDENTITY) {
-            skin_ok = (ids[e][0] & 0xFFu) != 0xFFu;
-#if OFX_STRAIGHT
+            uint32_t idw[2] = {0u, 0u};
+            float wv[KP];
+            if (n_used > 0) {
+#pragma unroll
+                for (int gq = 0; gq < KP / 4; ++gq) {
+                    idw[gq] = s_ids[(gq * 4 + e) * BRICK_THREADS];
+                    const float4 w4 = s_w[(gq * 4 + e) * BRICK_THREADS];
+                    wv[4 * gq] = w4.x; wv[4 * gq + 1] = w4.y; wv[4 * gq + 2] = w4.z; wv[4 * gq + 3] = w4.w;
+                }
+            } else {
+                idw[0] = 0xFFFFFFFFu;
+#pragma unroll
+                for (int k = 0; k < KP; ++k) wv[k] = 0.0f;
+            }
+            skin_ok = (idw[0] & 0xFFu) != 0xFFu;
             // straight-line: a voxel without anchors blends record 0 with zero weights and is masked below
-            const uint32_t idw[2] = {skin_ok ? ids[e][0] : 0u, skin_ok ? ids[e][1] : 0u};
-            warp_voxel<K>(idw, wk[e], s_rec, px, py, pz, qx, qy, qz);
-#else
-            if (skin_ok) warp_voxel<K>(ids[e], wk[e], s_rec, px, py, pz, qx, qy, qz);
-#endif
+            if (!skin_ok) idw[0] = idw[1] = 0u;
+            warp_voxel<K, KP>(idw, wv, s_rec, px, py, pz, qx, qy, qz);
         }
         if constexpr (MODE == MODE_DEFORM) {
             if (!skin_ok) { qx = px; qy = py; qz = pz; }              // registration_fusion.py:161,180
             if (out_pts) { out_pts[3 * (vox0 + e)] = qx; out_pts[3 * (vox0 + e) + 1] = qy; out_pts[3 * (vox0 + e) + 2] = qz; }
             if (out_valid) out_valid[vox0 + e] = skin_ok ? 1 : 0;
         } else {
-#if !OFX_STRAIGHT
-            if (!skin_ok) continue;
-#endif
             int u, v;
             int st = project_fast(qx, qy, qz, fa.fc, u, v);           // tsdf.py:589-593, certified float32
             if (st == 2 && skin_ok) st = project(qx, qy, qz, fa.cam, u, v) ? 1 : 0;   // undecided (~1e-4): the float64 original

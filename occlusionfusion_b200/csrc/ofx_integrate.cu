@@ -25,13 +25,18 @@ namespace ofx {
 int sm_count();
 
 // ---- generic one-CTA-per-brick kernel (identity warp, deform materialisation) --------------------
+// dynamic shared memory (non-identity modes): [skin-cache slot | node transforms]
 template <int K, bool VEC, int MODE>
 __global__ void __launch_bounds__(BRICK_THREADS)
 fused_brick_kernel(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ weight, float *__restrict__ colour,
                    GraphArgs ga, FrameArgs fa, unsigned long long *__restrict__ stats, float *__restrict__ out_pts,
                    uint8_t *__restrict__ out_valid)
 {
-    __shared__ __align__(128) float s_rec[(MODE == MODE_IDENTITY ? 1 : MAX_BRICK_NODES) * REC_STRIDE];
+    constexpr int KP = K <= 4 ? 4 : 8;
+    constexpr uint32_t SLOT_BYTES = slot_bytes_of(KP);
+    extern __shared__ __align__(128) unsigned char s_dyn[];
+    unsigned char *s_slot = s_dyn;
+    float *s_rec = reinterpret_cast<float *>(s_dyn + SLOT_BYTES);
     __shared__ __align__(8) uint64_t s_bar;
     __shared__ unsigned long long s_stat[3];
     __shared__ int s_cull;
@@ -47,7 +52,11 @@ fused_brick_kernel(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ w
     __syncthreads();
     if constexpr (MODE != MODE_IDENTITY) {
         if (n_used > 0) {
-            if (threadIdx.x == 0) mbar_arrive_expect_tx(&s_bar, (uint32_t)n_used * REC_BYTES);
+            if (threadIdx.x == 0) {
+                mbar_arrive_expect_tx(&s_bar, (uint32_t)n_used * REC_BYTES + SLOT_BYTES);
+                bulk_g2s(s_slot, ga.cache + (int64_t)ga.brick_slot[b] * SLOT_BYTES, SLOT_BYTES, &s_bar);
+            }
+            __syncthreads();
             if (threadIdx.x < 32) {
                 const int o = ga.off[b];
                 for (int i = threadIdx.x; i < n_used; i += 32)
@@ -66,9 +75,8 @@ fused_brick_kernel(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ w
         __syncthreads();
         if (s_cull) return;
     }
-    const int slot = (MODE != MODE_IDENTITY && n_used > 0) ? ga.brick_slot[b] : 0;
     unsigned c_upd = 0, c_valid = 0, c_wsum = 0;
-    brick_thread_work<K, VEC, MODE>(g, tsdf, weight, colour, ga, fa, s_rec, bc, n_used, slot, threadIdx.x, out_pts,
+    brick_thread_work<K, VEC, MODE>(g, tsdf, weight, colour, ga, fa, s_rec, s_slot, bc, n_used, threadIdx.x, out_pts,
                                     out_valid, c_upd, c_valid, c_wsum);
     if constexpr (MODE != MODE_DEFORM) {
         c_upd = __reduce_add_sync(0xffffffffu, c_upd);
@@ -162,20 +170,20 @@ brick_cull_kernel(GraphArgs ga, const float4 *__restrict__ brick_box, int n_acti
 // The producer draws live bricks (first = blockIdx.x, then an atomic counter), allocates room for the
 // brick's node transforms in a ring of RING_RECS records, gathers them with the TMA unit (one 48-byte
 // cp.async.bulk per node) and publishes a descriptor.  Three mbarriers per descriptor slot:
-//   bar_full   producer -> consumers: descriptor written
 //   bar_data   TMA -> consumers: the transforms have landed (transaction bytes)
-//   bar_empty  consumers -> producer: all eight warps are done with the slot and its records
+//   named barrier 1 + slot   consumers -> producer: all eight warps are done with the slot and its records
+//                            (bar.arrive / bar.sync: the producer blocks in hardware, it does not poll)
 #ifndef OFX_N_SLOTS
-#define OFX_N_SLOTS 3
+#define OFX_N_SLOTS 2
 #endif
 #ifndef OFX_MIN_CTAS
-#define OFX_MIN_CTAS 3
+#define OFX_MIN_CTAS 4
 #endif
 #ifndef OFX_PREFETCH_VOLUME
 #define OFX_PREFETCH_VOLUME 0
 #endif
 constexpr int N_SLOTS = OFX_N_SLOTS;
-constexpr int RING_RECS = 512;                              // >= 2 * MAX_BRICK_NODES: two of the largest bricks
+constexpr int RING_RECS = 256;                              // > MAX_BRICK_NODES: the largest brick fits an empty ring
 constexpr int CONSUMER_WARPS = BRICK_THREADS / 32;          // 8
 constexpr int PERSISTENT_THREADS = BRICK_THREADS + 32;      // + 1 producer warp
 
@@ -187,21 +195,23 @@ struct SlotInfo {
 };
 
 template <int K, bool VEC>
-__global__ void __launch_bounds__(PERSISTENT_THREADS, K <= 4 ? OFX_MIN_CTAS : 3)
+__global__ void __launch_bounds__(PERSISTENT_THREADS, K <= 4 ? OFX_MIN_CTAS : 2)
 fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ weight, float *__restrict__ colour,
                         GraphArgs ga, FrameArgs fa, const int *__restrict__ live, const int *__restrict__ n_live_ptr,
                         int *__restrict__ work_counter, unsigned long long *__restrict__ stats)
 {
-    __shared__ __align__(128) float s_rec[RING_RECS * REC_STRIDE];
-    __shared__ __align__(8) uint64_t bar_data[N_SLOTS], bar_full[N_SLOTS], bar_empty[N_SLOTS];
+    // dynamic shared memory: [N_SLOTS skin-cache slots | ring of node transforms]
+    constexpr int KP = K <= 4 ? 4 : 8;
+    constexpr uint32_t SLOT_BYTES = slot_bytes_of(KP);
+    extern __shared__ __align__(128) unsigned char s_dyn[];
+    float *s_rec = reinterpret_cast<float *>(s_dyn + N_SLOTS * SLOT_BYTES);
+    __shared__ __align__(8) uint64_t bar_data[N_SLOTS];
     __shared__ SlotInfo s_info[N_SLOTS];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
         for (int s = 0; s < N_SLOTS; ++s) {
             mbar_init(&bar_data[s], 1);
-            mbar_init(&bar_full[s], 1);
-            mbar_init(&bar_empty[s], CONSUMER_WARPS);
         }
     }
     __syncthreads();
@@ -234,7 +244,7 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
                     } else if (tail - head >= n_used) { start = head; head += n_used; }
                     if (start >= 0) break;
                 }
-                mbar_wait_sleep(&bar_empty[rel % N_SLOTS], (uint32_t)(rel / N_SLOTS) & 1u);   // oldest brick done
+                named_bar_sync(1 + rel % N_SLOTS, PERSISTENT_THREADS);                          // oldest brick done
                 ++rel;
                 if (rel < it) {
                     const int nt = s_info[rel % N_SLOTS].rec_off;
@@ -243,15 +253,16 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
                 }
             }
             if (!more) {
-                if (lane == 0) { s_info[slot].n_used = -1; mbar_arrive(&bar_full[slot]); }
+                if (lane == 0) { s_info[slot].n_used = -1; mbar_arrive(&bar_data[slot]); }
                 break;
             }
             const BrickCoord bc = brick_coord(g, b);
             if (lane == 0) {
                 s_info[slot].lx0 = bc.lx0; s_info[slot].iy0 = bc.iy0; s_info[slot].iz0 = bc.iz0;
                 s_info[slot].n_used = n_used; s_info[slot].rec_off = start; s_info[slot].cache_slot = cslot;
-                mbar_arrive_expect_tx(&bar_data[slot], (uint32_t)n_used * REC_BYTES);
-                mbar_arrive(&bar_full[slot]);          // release: descriptor visible; the data has its own barrier
+                mbar_arrive_expect_tx(&bar_data[slot], (uint32_t)n_used * REC_BYTES + SLOT_BYTES);
+                // the brick's skin-cache slot (ids + weights of its 1024 voxels): one bulk copy
+                bulk_g2s(s_dyn + slot * SLOT_BYTES, ga.cache + (int64_t)cslot * SLOT_BYTES, SLOT_BYTES, &bar_data[slot]);
             }
             __syncwarp();
             float *rec = s_rec + start * REC_STRIDE;
@@ -259,14 +270,6 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
                 bulk_g2s(rec + i * REC_STRIDE,
                          ga.node_rec + (int64_t)__ldg(ga.brick_nodes + o + i) * NODE_REC_FLOATS + NODE_XFORM_OFFSET,
                          REC_BYTES, &bar_data[slot]);
-            // the brick's skin-cache slot (ids + K weight planes, contiguous) starts its way from DRAM to L2
-            // now, a few bricks before the consumers ask for it
-            if (lane <= K) {
-                if (lane == 0)
-                    bulk_prefetch_l2(ga.cache_ids + (int64_t)cslot * BRICK_VOXELS * ga.id_bytes, BRICK_VOXELS * ga.id_bytes);
-                else
-                    bulk_prefetch_l2(ga.cache_w + ((int64_t)cslot * K + (lane - 1)) * BRICK_VOXELS, BRICK_VOXELS * 4u);
-            }
 #if OFX_PREFETCH_VOLUME
             if (VEC) {
                 const int lx = bc.lx0 + (lane >> 3), iy = bc.iy0 + (lane & 7);
@@ -292,18 +295,17 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
     for (int it = 0;; ++it) {
         const int slot = it % N_SLOTS;
         const uint32_t ph = (uint32_t)(it / N_SLOTS) & 1u;
-        mbar_wait(&bar_full[slot], ph);
+        mbar_wait(&bar_data[slot], ph);            // descriptor written and the TMA bytes of this brick have landed
         const SlotInfo info = s_info[slot];
         if (info.n_used < 0) break;
-        mbar_wait(&bar_data[slot], ph);            // the TMA bytes of this brick have landed
         const BrickCoord bc{info.lx0, info.iy0, info.iz0};
         unsigned w32 = 0;
-        brick_thread_work<K, VEC, MODE_WARPED>(g, tsdf, weight, colour, ga, fa, s_rec + info.rec_off * REC_STRIDE, bc,
-                                               info.n_used, info.cache_slot, threadIdx.x, nullptr, nullptr, c_upd,
-                                               c_valid, w32);
+        brick_thread_work<K, VEC, MODE_WARPED>(g, tsdf, weight, colour, ga, fa, s_rec + info.rec_off * REC_STRIDE,
+                                               s_dyn + slot * SLOT_BYTES, bc, info.n_used, threadIdx.x, nullptr, nullptr,
+                                               c_upd, c_valid, w32);
         c_wsum += w32;
         __syncwarp();
-        if (lane == 0) mbar_arrive(&bar_empty[slot]);
+        named_bar_arrive(1 + slot, PERSISTENT_THREADS);
     }
     // counters: once per CTA lifetime
     c_upd = __reduce_add_sync(0xffffffffu, c_upd);
@@ -329,8 +331,8 @@ static bool volume_vec_ok(const ofx_volume *v)
 
 static GraphArgs graph_args(const ofx_volume *v)
 {
-    return GraphArgs{v->node_rec, v->active, v->brick_off, v->brick_cnt, v->brick_nodes, v->brick_slot, v->cache_ids,
-                     v->cache_w, v->cache_bytes_per_voxel, v->cutoff, v->denom};
+    return GraphArgs{v->node_rec, v->active, v->brick_off, v->brick_cnt, v->brick_nodes, v->brick_slot, v->cache,
+                     v->cutoff, v->denom};
 }
 
 template <int K, int MODE>
@@ -338,12 +340,16 @@ static int launch_brick(ofx_volume *v, int grid, const GraphArgs &ga, const Fram
                         float *out_pts, uint8_t *out_valid, cudaStream_t s)
 {
     if (grid <= 0) return 0;
-    if (volume_vec_ok(v))
-        fused_brick_kernel<K, true, MODE><<<grid, BRICK_THREADS, 0, s>>>(v->geom, v->desc.tsdf, v->desc.weight,
-                                                                         v->desc.colour, ga, fa, stats, out_pts, out_valid);
-    else
-        fused_brick_kernel<K, false, MODE><<<grid, BRICK_THREADS, 0, s>>>(v->geom, v->desc.tsdf, v->desc.weight,
-                                                                          v->desc.colour, ga, fa, stats, out_pts, out_valid);
+    const size_t smem = MODE == MODE_IDENTITY ? 16 : (size_t)slot_bytes_of(K <= 4 ? 4 : 8) + MAX_BRICK_NODES * REC_BYTES;
+    if (volume_vec_ok(v)) {
+        OFX_CUDA(cudaFuncSetAttribute(fused_brick_kernel<K, true, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        fused_brick_kernel<K, true, MODE><<<grid, BRICK_THREADS, smem, s>>>(v->geom, v->desc.tsdf, v->desc.weight,
+                                                                            v->desc.colour, ga, fa, stats, out_pts, out_valid);
+    } else {
+        OFX_CUDA(cudaFuncSetAttribute(fused_brick_kernel<K, false, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        fused_brick_kernel<K, false, MODE><<<grid, BRICK_THREADS, smem, s>>>(v->geom, v->desc.tsdf, v->desc.weight,
+                                                                             v->desc.colour, ga, fa, stats, out_pts, out_valid);
+    }
     OFX_LAUNCH_CHECK();
     return 0;
 }
@@ -352,8 +358,9 @@ template <int K, bool VEC>
 static int launch_persistent_t(ofx_volume *v, const FrameArgs &fa, unsigned long long *stats, cudaStream_t s)
 {
     static int blocks_per_sm = 0;      // per instantiation
-    const size_t smem = 0;
+    const size_t smem = (size_t)N_SLOTS * slot_bytes_of(K <= 4 ? 4 : 8) + RING_RECS * REC_BYTES;
     if (blocks_per_sm == 0) {
+        OFX_CUDA(cudaFuncSetAttribute(fused_warped_persistent<K, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         OFX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, fused_warped_persistent<K, VEC>,
                                                                PERSISTENT_THREADS, smem));
         if (blocks_per_sm < 1) blocks_per_sm = 1;

@@ -179,7 +179,9 @@ struct Camera {
 
 // cam2pix + frustum test (tsdf.py:351-364, 589-593): float64, multiply before divide,
 // round half to even.  false when z <= 0 or the pixel falls outside the image.
-__device__ __forceinline__ bool project(float qx, float qy, float qz, const Camera &cam, int &u, int &v)
+// Out of line on purpose: the fused kernels call it for ~1e-4 of the voxels, and inlining lets the
+// compiler hoist its float64 constants into registers that the hot loop then has to spill.
+static __device__ __noinline__ bool project(float qx, float qy, float qz, const Camera &cam, int &u, int &v)
 {
     if (!(qz > 0.0f)) return false;
     const double z = (double)qz;
@@ -318,6 +320,16 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
         "}\n" ::"r"(smem_u32(bar)),
         "r"(parity)
         : "memory");
+}
+// named barriers (bar.arrive / bar.sync): consumers signal without blocking, the producer blocks in
+// hardware without taking issue slots.  `threads` = arriving + waiting threads, a multiple of 32.
+__device__ __forceinline__ void named_bar_arrive(int id, int threads)
+{
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+__device__ __forceinline__ void named_bar_sync(int id, int threads)
+{
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
 // the same wait for a warp that expects to wait long (the producer): sleep between polls
 __device__ __forceinline__ void mbar_wait_sleep(uint64_t *bar, uint32_t parity)

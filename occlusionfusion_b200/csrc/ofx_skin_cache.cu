@@ -185,8 +185,7 @@ __global__ void __launch_bounds__(BRICK_THREADS) skin_brick_kernel(VolumeGeom g,
                                                                    int *__restrict__ cnt, const int *__restrict__ cand,
                                                                    int *__restrict__ brick_nodes,
                                                                    const int *__restrict__ brick_slot,
-                                                                   uint8_t *__restrict__ cache_ids,
-                                                                   float *__restrict__ cache_w,
+                                                                   uint8_t *__restrict__ cache,
                                                                    int *__restrict__ error_flag)
 {
     extern __shared__ __align__(16) unsigned char s_raw[];
@@ -286,43 +285,37 @@ __global__ void __launch_bounds__(BRICK_THREADS) skin_brick_kernel(VolumeGeom g,
         if (n_used > MAX_BRICK_NODES) atomicExch(error_flag, n_used);
     }
 
-    // byte ids (0xFF = no anchor) and normalised weights -> the brick's cache slot; threads outside
-    // the volume write "invalid" so that the fused kernel can always load whole 16-byte words
-    constexpr int ID_BYTES = K <= 4 ? 4 : 8;
+    // byte ids (0xFF = no anchor) and normalised weights -> the brick's cache slot (layout: ofx_volume.cuh);
+    // threads outside the volume write "invalid"
+    constexpr int KP = K <= 4 ? 4 : 8;
     const float rdenom = __frcp_rn(denom);
-    uint32_t words[VOX_PER_THREAD][2];
-    float wq[K][VOX_PER_THREAD];
+    uint8_t *sl = cache + slot * slot_bytes_of(KP);
 #pragma unroll
     for (int e = 0; e < VOX_PER_THREAD; ++e) {
-        words[e][0] = words[e][1] = 0xFFFFFFFFu;
-        float w[K];
+        uint32_t words[2] = {0xFFFFFFFFu, 0xFFFFFFFFu};
+        float w[KP];
 #pragma unroll
-        for (int k = 0; k < K; ++k) w[k] = 0.0f;
+        for (int k = 0; k < KP; ++k) w[k] = 0.0f;
         if (ok[e]) {
-            words[e][0] = words[e][1] = 0u;
+            words[0] = words[1] = 0u;
 #pragma unroll
-            for (int k = 0; k < ID_BYTES; ++k) {
+            for (int k = 0; k < KP; ++k) {
                 uint32_t id = 0xFFu;
                 if (k < K) id = (uint32_t)min((int)s_rank[bi[e][k < K ? k : 0]], 254);
-                words[e][k >> 2] |= id << (8 * (k & 3));
+                words[k >> 2] |= id << (8 * (k & 3));
             }
-            skin_weights_valid<K>(bd[e], denom, rdenom, w);             // warpfield.py:104-121
+            float wv[K];
+            skin_weights_valid<K>(bd[e], denom, rdenom, wv);            // warpfield.py:104-121
+#pragma unroll
+            for (int k = 0; k < K; ++k) w[k] = wv[k];
         }
 #pragma unroll
-        for (int k = 0; k < K; ++k) wq[k][e] = w[k];
+        for (int gq = 0; gq < KP / 4; ++gq) {
+            const int cell = (gq * 4 + e) * BRICK_THREADS + threadIdx.x;
+            reinterpret_cast<uint32_t *>(sl)[cell] = words[gq];
+            reinterpret_cast<float4 *>(sl + BRICK_VOXELS * KP)[cell] = make_float4(w[4 * gq], w[4 * gq + 1], w[4 * gq + 2], w[4 * gq + 3]);
+        }
     }
-    const int64_t j0 = slot * BRICK_VOXELS + threadIdx.x * VOX_PER_THREAD;
-    if constexpr (ID_BYTES == 4) {
-        *reinterpret_cast<uint4 *>(cache_ids + j0 * 4) = make_uint4(words[0][0], words[1][0], words[2][0], words[3][0]);
-    } else {
-        uint4 *c = reinterpret_cast<uint4 *>(cache_ids + j0 * 8);
-        c[0] = make_uint4(words[0][0], words[0][1], words[1][0], words[1][1]);
-        c[1] = make_uint4(words[2][0], words[2][1], words[3][0], words[3][1]);
-    }
-#pragma unroll
-    for (int k = 0; k < K; ++k)
-        *reinterpret_cast<float4 *>(cache_w + (slot * K + k) * BRICK_VOXELS + threadIdx.x * VOX_PER_THREAD) =
-            make_float4(wq[k][0], wq[k][1], wq[k][2], wq[k][3]);
     (void)any_valid;
 }
 
@@ -338,8 +331,7 @@ static int launch_skin_brick(ofx_volume *v, int max_cnt, cudaStream_t s)
     OFX_CUDA(cudaFuncSetAttribute(skin_brick_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     skin_brick_kernel<K><<<v->n_bricks, BRICK_THREADS, smem, s>>>(v->geom, v->node_rec, v->cutoff, v->denom,
                                                                   v->brick_off, v->brick_cnt, v->cand, v->brick_nodes,
-                                                                  v->brick_slot, v->cache_ids, v->cache_w,
-                                                                  v->scratch + 2);
+                                                                  v->brick_slot, v->cache, v->scratch + 2);
     OFX_LAUNCH_CHECK();
     return 0;
 }
@@ -359,7 +351,7 @@ extern "C" int ofx_set_graph(ofx_volume *v, const float *nodes, int32_t M, doubl
     v->cutoff = (float)(4.0 * node_coverage);                        // warpfield.py:109
     v->denom = (float)(2.0 * (node_coverage * node_coverage));       // warpfield.py:114
 
-    v->cache_bytes_per_voxel = K <= 4 ? 4 : 8;
+    v->cache_kp = K <= 4 ? 4 : 8;
 
     const int nb = v->n_bricks;
     OFX_CUDA(cudaMemsetAsync(v->scratch, 0, 16 * sizeof(int), s));
@@ -377,19 +369,12 @@ extern "C" int ofx_set_graph(ofx_volume *v, const float *nodes, int32_t M, doubl
     const int64_t total = tm[0];
     const int max_cnt = tm[1];
     v->n_slots = tm[6];
-    const int64_t need_ids = (int64_t)v->n_slots * BRICK_VOXELS * v->cache_bytes_per_voxel;
-    const int64_t need_w = (int64_t)v->n_slots * BRICK_VOXELS * K;
-    if (need_ids > v->cache_ids_capacity) {
-        if (v->cache_ids) OFX_CUDA(cudaFree(v->cache_ids));
-        v->cache_ids = nullptr; v->cache_ids_capacity = 0;
-        OFX_CUDA(cudaMalloc(&v->cache_ids, (size_t)(need_ids + need_ids / 8)));
-        v->cache_ids_capacity = need_ids + need_ids / 8;
-    }
-    if (need_w > v->cache_w_capacity) {
-        if (v->cache_w) OFX_CUDA(cudaFree(v->cache_w));
-        v->cache_w = nullptr; v->cache_w_capacity = 0;
-        OFX_CUDA(cudaMalloc(&v->cache_w, (size_t)(need_w + need_w / 8) * sizeof(float)));
-        v->cache_w_capacity = need_w + need_w / 8;
+    const int64_t need = (int64_t)v->n_slots * slot_bytes_of(v->cache_kp);
+    if (need > v->cache_capacity) {
+        if (v->cache) OFX_CUDA(cudaFree(v->cache));
+        v->cache = nullptr; v->cache_capacity = 0;
+        OFX_CUDA(cudaMalloc(&v->cache, (size_t)(need + need / 8)));
+        v->cache_capacity = need + need / 8;
     }
     if (total > v->list_capacity) {
         if (v->cand) OFX_CUDA(cudaFree(v->cand));

@@ -130,7 +130,7 @@ extern "C" int ofx_volume_create(ofx_volume **out, const ofx_volume_desc *d)
 extern "C" int ofx_volume_destroy(ofx_volume *v)
 {
     if (!v) return 0;
-    cudaFree(v->tables); cudaFree(v->node_rec); cudaFree(v->cache_ids); cudaFree(v->cache_w); cudaFree(v->brick_slot); cudaFree(v->brick_cnt);
+    cudaFree(v->tables); cudaFree(v->node_rec); cudaFree(v->cache); cudaFree(v->brick_slot); cudaFree(v->brick_cnt);
     cudaFree(v->brick_off); cudaFree(v->brick_radius); cudaFree(v->cand); cudaFree(v->brick_nodes);
     cudaFree(v->active); cudaFree(v->scratch); cudaFree(v->stats_scratch);
     cudaFree(v->live); cudaFree(v->brick_box); cudaFree(v->depth_tiles);

@@ -17,6 +17,7 @@ constexpr int BRICK_VOXELS = BX * BY * BZ;                       // 1024
 constexpr int NODE_REC_FLOATS = 16;   // {gx,gy,gz,0, R00..R22, T0,T1,T2} = 64 B in global memory
 constexpr int NODE_XFORM_OFFSET = 4;  // the 48-byte {R, T} tail is what the fused kernels stage (one TMA bulk copy)
 constexpr int NODE_XFORM_FLOATS = 12;
+__host__ __device__ constexpr int slot_bytes_of(int kp) { return BRICK_VOXELS * 5 * kp; }
 constexpr int MAX_BRICK_NODES = 255;  // local anchor ids are bytes, 0xFF = "no anchor"
 
 struct VolumeGeom {
@@ -57,13 +58,14 @@ struct ofx_volume {
     int node_rec_capacity;
 
     // skin cache (device form of WarpField.skin_tsdf's cache, warpfield.py:131-141), brick-major and
-    // compact: one slot per brick that has candidate nodes.  Voxel j = 4*thread + e of slot s:
-    //   ids      cache_ids[(s*1024 + j) * id_bytes + k]      brick-local node id, 0xFF = not skin-valid
-    //   weights  cache_w[(s*K + k)*1024 + j]                 normalised float32 weight (warpfield.py:121)
-    int cache_bytes_per_voxel;   // id_bytes: 4 (K<=4) or 8
-    uint8_t *cache_ids;
-    float *cache_w;
-    int64_t cache_ids_capacity, cache_w_capacity;   // bytes / floats allocated
+    // compact: one slot of slot_bytes = 1024 * 5 * Kp bytes (Kp = 4 for K <= 4, else 8) per brick that
+    // has candidate nodes, laid out for ONE bulk copy into shared memory and conflict-free reads
+    // (thread t, voxel e of the thread, anchor group g = k / 4):
+    //   ids      u32   at ((g*4 + e)*256 + t) * 4              four brick-local node ids, 0xFF = not skin-valid
+    //   weights  f32x4 at 1024*Kp + ((g*4 + e)*256 + t) * 16   normalised weights (warpfield.py:121), 0 beyond K
+    int cache_kp;                // Kp
+    uint8_t *cache;
+    int64_t cache_capacity;      // bytes allocated
     int *brick_slot;             // n_bricks: slot of a brick (meaningful where brick_cnt > 0)
     int n_slots;
     int *brick_cnt;              // n_bricks: candidate count, later used-node count
