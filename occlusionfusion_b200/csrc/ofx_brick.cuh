@@ -158,7 +158,7 @@ __device__ __forceinline__ bool brick_outside_frustum(const VolumeGeom &g, const
 // ---- per-thread body ---------------------------------------------------------------------------------
 // Thread t of a brick owns voxels (lx0 + t/64, iy0 + (t/8)%8, iz0 + 4*(t%8) .. +3).  Counters are
 // accumulated into c_upd / c_valid / c_wsum (the caller reduces them).
-template <int K, bool VEC, int MODE>
+template <int K, bool VEC, int MODE, bool OBS32>
 __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__restrict__ tsdf,
                                                   float *__restrict__ weight, float *__restrict__ colour,
                                                   const GraphArgs &ga, const FrameArgs &fa,
@@ -239,7 +239,7 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
             // difference above / below the float32 neighbours of -trunc decides; only a tie needs float64
             const float d = dsel[e], df = d - zsel[e];
             bool vis = d > 0.0f && df >= fa.ntrunc_dn;
-            if (vis && !(df > fa.ntrunc_up)) vis = (double)d - (double)zsel[e] >= -fa.trunc;
+            if (vis && !(df > fa.ntrunc_up)) vis = visible_exact(d, zsel[e], fa.trunc);
             if (vis) upd |= 1u << e;
         }
         if (!upd) return;
@@ -267,7 +267,7 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
 #pragma unroll
         for (int e = 0; e < VOX_PER_THREAD; ++e)
             if (upd & (1u << e)) {
-                fuse_voxel(tt[e], ww[e], cc[e], dsel[e], zsel[e], ncol[e], fa.fu);
+                fuse_voxel<OBS32>(tt[e], ww[e], cc[e], dsel[e], zsel[e], ncol[e], fa.fu);
                 wsum += ww[e];
             }
         if (VEC) {

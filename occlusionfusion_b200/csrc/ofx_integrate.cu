@@ -26,7 +26,7 @@ int sm_count();
 
 // ---- generic one-CTA-per-brick kernel (identity warp, deform materialisation) --------------------
 // dynamic shared memory (non-identity modes): [skin-cache slot | node transforms]
-template <int K, bool VEC, int MODE>
+template <int K, bool VEC, int MODE, bool OBS32>
 __global__ void __launch_bounds__(BRICK_THREADS)
 fused_brick_kernel(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ weight, float *__restrict__ colour,
                    GraphArgs ga, FrameArgs fa, unsigned long long *__restrict__ stats, float *__restrict__ out_pts,
@@ -76,7 +76,7 @@ fused_brick_kernel(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ w
         if (s_cull) return;
     }
     unsigned c_upd = 0, c_valid = 0, c_wsum = 0;
-    brick_thread_work<K, VEC, MODE>(g, tsdf, weight, colour, ga, fa, s_rec, s_slot, bc, n_used, threadIdx.x, out_pts,
+    brick_thread_work<K, VEC, MODE, OBS32>(g, tsdf, weight, colour, ga, fa, s_rec, s_slot, bc, n_used, threadIdx.x, out_pts,
                                     out_valid, c_upd, c_valid, c_wsum);
     if constexpr (MODE != MODE_DEFORM) {
         c_upd = __reduce_add_sync(0xffffffffu, c_upd);
@@ -194,7 +194,7 @@ struct SlotInfo {
     int cache_slot;
 };
 
-template <int K, bool VEC>
+template <int K, bool VEC, bool OBS32>
 __global__ void __launch_bounds__(PERSISTENT_THREADS, K <= 4 ? OFX_MIN_CTAS : 2)
 fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ weight, float *__restrict__ colour,
                         GraphArgs ga, FrameArgs fa, const int *__restrict__ live, const int *__restrict__ n_live_ptr,
@@ -207,12 +207,12 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
     float *s_rec = reinterpret_cast<float *>(s_dyn + N_SLOTS * SLOT_BYTES);
     __shared__ __align__(8) uint64_t bar_data[N_SLOTS];
     __shared__ SlotInfo s_info[N_SLOTS];
+    __shared__ unsigned s_cnt[4];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
-        for (int s = 0; s < N_SLOTS; ++s) {
-            mbar_init(&bar_data[s], 1);
-        }
+        for (int s = 0; s < N_SLOTS; ++s) mbar_init(&bar_data[s], 1);
+        s_cnt[0] = s_cnt[1] = s_cnt[2] = s_cnt[3] = 0u;
     }
     __syncthreads();
 
@@ -290,8 +290,8 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
     }
 
     // ===== consumer warps =====
-    unsigned c_upd = 0, c_valid = 0;
-    unsigned long long c_wsum = 0;
+    // counters: per brick a warp reduction into shared memory (keeps them out of the registers that
+    // live across the brick loop), flushed once when the CTA's consumers are done
     for (int it = 0;; ++it) {
         const int slot = it % N_SLOTS;
         const uint32_t ph = (uint32_t)(it / N_SLOTS) & 1u;
@@ -299,23 +299,32 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
         const SlotInfo info = s_info[slot];
         if (info.n_used < 0) break;
         const BrickCoord bc{info.lx0, info.iy0, info.iz0};
-        unsigned w32 = 0;
-        brick_thread_work<K, VEC, MODE_WARPED>(g, tsdf, weight, colour, ga, fa, s_rec + info.rec_off * REC_STRIDE,
-                                               s_dyn + slot * SLOT_BYTES, bc, info.n_used, threadIdx.x, nullptr, nullptr,
-                                               c_upd, c_valid, w32);
-        c_wsum += w32;
+        unsigned c_upd = 0, c_valid = 0, c_wsum = 0;
+        brick_thread_work<K, VEC, MODE_WARPED, OBS32>(g, tsdf, weight, colour, ga, fa, s_rec + info.rec_off * REC_STRIDE,
+                                                      s_dyn + slot * SLOT_BYTES, bc, info.n_used, threadIdx.x, nullptr,
+                                                      nullptr, c_upd, c_valid, c_wsum);
         __syncwarp();
         named_bar_arrive(1 + slot, PERSISTENT_THREADS);
+        c_upd = __reduce_add_sync(0xffffffffu, c_upd);
+        c_valid = __reduce_add_sync(0xffffffffu, c_valid);
+        c_wsum = __reduce_add_sync(0xffffffffu, c_wsum);
+        if (lane == 0) {
+            // 32-bit shared-memory atomics are native (64-bit ones are CAS loops); a CTA sees far fewer
+            // than 2^32 voxels per launch, the weight sum keeps a carry word
+            if (c_upd) atomicAdd(&s_cnt[0], c_upd);
+            if (c_valid) atomicAdd(&s_cnt[1], c_valid);
+            if (c_wsum) {
+                const unsigned old = atomicAdd(&s_cnt[2], c_wsum);
+                if (old + c_wsum < old) atomicAdd(&s_cnt[3], 1u);
+            }
+        }
     }
-    // counters: once per CTA lifetime
-    c_upd = __reduce_add_sync(0xffffffffu, c_upd);
-    c_valid = __reduce_add_sync(0xffffffffu, c_valid);
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) c_wsum += __shfl_xor_sync(0xffffffffu, c_wsum, o);
-    if (lane == 0) {
-        if (c_upd) atomicAdd(stats + OFX_STAT_UPDATED, (unsigned long long)c_upd);
-        if (c_valid) atomicAdd(stats + OFX_STAT_SKIN_VALID, (unsigned long long)c_valid);
-        if (c_wsum) atomicAdd(stats + OFX_STAT_WEIGHT_SUM, c_wsum);
+    named_bar_sync(1 + N_SLOTS, BRICK_THREADS);    // consumers only
+    if (threadIdx.x == 0) {
+        if (s_cnt[0]) atomicAdd(stats + OFX_STAT_UPDATED, (unsigned long long)s_cnt[0]);
+        if (s_cnt[1]) atomicAdd(stats + OFX_STAT_SKIN_VALID, (unsigned long long)s_cnt[1]);
+        const unsigned long long ws = ((unsigned long long)s_cnt[3] << 32) | s_cnt[2];
+        if (ws) atomicAdd(stats + OFX_STAT_WEIGHT_SUM, ws);
     }
 }
 
@@ -342,26 +351,26 @@ static int launch_brick(ofx_volume *v, int grid, const GraphArgs &ga, const Fram
     if (grid <= 0) return 0;
     const size_t smem = MODE == MODE_IDENTITY ? 16 : (size_t)slot_bytes_of(K <= 4 ? 4 : 8) + MAX_BRICK_NODES * REC_BYTES;
     if (volume_vec_ok(v)) {
-        OFX_CUDA(cudaFuncSetAttribute(fused_brick_kernel<K, true, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        fused_brick_kernel<K, true, MODE><<<grid, BRICK_THREADS, smem, s>>>(v->geom, v->desc.tsdf, v->desc.weight,
+        OFX_CUDA(cudaFuncSetAttribute(fused_brick_kernel<K, true, MODE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        fused_brick_kernel<K, true, MODE, false><<<grid, BRICK_THREADS, smem, s>>>(v->geom, v->desc.tsdf, v->desc.weight,
                                                                             v->desc.colour, ga, fa, stats, out_pts, out_valid);
     } else {
-        OFX_CUDA(cudaFuncSetAttribute(fused_brick_kernel<K, false, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        fused_brick_kernel<K, false, MODE><<<grid, BRICK_THREADS, smem, s>>>(v->geom, v->desc.tsdf, v->desc.weight,
+        OFX_CUDA(cudaFuncSetAttribute(fused_brick_kernel<K, false, MODE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        fused_brick_kernel<K, false, MODE, false><<<grid, BRICK_THREADS, smem, s>>>(v->geom, v->desc.tsdf, v->desc.weight,
                                                                              v->desc.colour, ga, fa, stats, out_pts, out_valid);
     }
     OFX_LAUNCH_CHECK();
     return 0;
 }
 
-template <int K, bool VEC>
+template <int K, bool VEC, bool OBS32>
 static int launch_persistent_t(ofx_volume *v, const FrameArgs &fa, unsigned long long *stats, cudaStream_t s)
 {
     static int blocks_per_sm = 0;      // per instantiation
     const size_t smem = (size_t)N_SLOTS * slot_bytes_of(K <= 4 ? 4 : 8) + RING_RECS * REC_BYTES;
     if (blocks_per_sm == 0) {
-        OFX_CUDA(cudaFuncSetAttribute(fused_warped_persistent<K, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        OFX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, fused_warped_persistent<K, VEC>,
+        OFX_CUDA(cudaFuncSetAttribute(fused_warped_persistent<K, VEC, OBS32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        OFX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, fused_warped_persistent<K, VEC, OBS32>,
                                                                PERSISTENT_THREADS, smem));
         if (blocks_per_sm < 1) blocks_per_sm = 1;
     }
@@ -374,7 +383,7 @@ static int launch_persistent_t(ofx_volume *v, const FrameArgs &fa, unsigned long
     OFX_LAUNCH_CHECK();
     const int cap = sm_count() * blocks_per_sm;       // persistent grid: a multiple of the SM count
     const int grid = v->n_active < cap ? v->n_active : cap;   // CTAs beyond the live count retire at once
-    fused_warped_persistent<K, VEC><<<grid, PERSISTENT_THREADS, smem, s>>>(v->geom, v->desc.tsdf, v->desc.weight,
+    fused_warped_persistent<K, VEC, OBS32><<<grid, PERSISTENT_THREADS, smem, s>>>(v->geom, v->desc.tsdf, v->desc.weight,
                                                                           v->desc.colour, ga, fa, v->live, n_live, work,
                                                                           stats);
     OFX_LAUNCH_CHECK();
@@ -384,7 +393,10 @@ static int launch_persistent_t(ofx_volume *v, const FrameArgs &fa, unsigned long
 template <int K>
 static int launch_persistent(ofx_volume *v, const FrameArgs &fa, unsigned long long *stats, cudaStream_t s)
 {
-    return volume_vec_ok(v) ? launch_persistent_t<K, true>(v, fa, stats, s) : launch_persistent_t<K, false>(v, fa, stats, s);
+    // the float32-observation-weight build is the hot one; the general one shares everything else
+    if (fa.fu.obs_is_f32)
+        return volume_vec_ok(v) ? launch_persistent_t<K, true, true>(v, fa, stats, s) : launch_persistent_t<K, false, true>(v, fa, stats, s);
+    return volume_vec_ok(v) ? launch_persistent_t<K, true, false>(v, fa, stats, s) : launch_persistent_t<K, false, false>(v, fa, stats, s);
 }
 
 extern "C" int ofx_integrate(ofx_volume *v, const float *depth, const float *colour_packed, int32_t H, int32_t W,

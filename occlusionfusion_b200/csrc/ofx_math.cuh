@@ -179,9 +179,7 @@ struct Camera {
 
 // cam2pix + frustum test (tsdf.py:351-364, 589-593): float64, multiply before divide,
 // round half to even.  false when z <= 0 or the pixel falls outside the image.
-// Out of line on purpose: the fused kernels call it for ~1e-4 of the voxels, and inlining lets the
-// compiler hoist its float64 constants into registers that the hot loop then has to spill.
-static __device__ __noinline__ bool project(float qx, float qy, float qz, const Camera &cam, int &u, int &v)
+__device__ __forceinline__ bool project(float qx, float qy, float qz, const Camera &cam, int &u, int &v)
 {
     if (!(qz > 0.0f)) return false;
     const double z = (double)qz;
@@ -238,6 +236,12 @@ __device__ __forceinline__ int project_fast(float qx, float qy, float qz, const 
     return dead ? 0 : ((ok_u && ok_v) ? 1 : 2);
 }
 
+// depth - z >= -trunc in float64 (tsdf.py:608-609), for the rare float32 ties
+__device__ __forceinline__ bool visible_exact(float d, float z, double trunc)
+{
+    return (double)d - (double)z >= -trunc;
+}
+
 // Running-average update of one voxel (tsdf.py:466, 373-375, 479-493).
 // diff = depth - z (float64), already known to satisfy depth > 0 && diff >= -trunc.
 struct FuseArgs {
@@ -253,6 +257,9 @@ __device__ __forceinline__ float byte_to_float(uint32_t word, uint32_t selector)
     return __uint_as_float(__byte_perm(word, 0x4B000000u, selector)) - 8388608.0f;
 }
 
+// OBS32: obs_weight is a float32 value (fu.obs_is_f32; the reference's default 1.0 is) -- a compile-time
+// switch so that the float64 weight sum of the general case does not ride along in the hot loop.
+template <bool OBS32>
 __device__ __forceinline__ void fuse_voxel(float &tsdf, float &weight, float &colour, float d, float z, float new_colour,
                                            const FuseArgs &fu)
 {
@@ -260,13 +267,15 @@ __device__ __forceinline__ void fuse_voxel(float &tsdf, float &weight, float &co
     // f32(f64(w) + obs): when obs is a float32 value the float64 sum is either exact (exponents within
     // 29 bits) or the small operand is far below half an ulp32 of the large one, so the single float32
     // addition rounds identically
-    const float w_new = fu.obs_is_f32 ? w_old + fu.obsf : (float)((double)w_old + fu.obs);
+    float w_new;
+    if constexpr (OBS32) w_new = w_old + fu.obsf;
+    else w_new = (float)((double)w_old + fu.obs);
     // Free space seen again -- the bulk of all updates: dist = 1 and tsdf = 1.  fl32(d - z) above the
     // float32 successor of trunc proves d - z >= trunc (rounding is monotone), i.e. dist = 1; then
     // num = w + obs (exact in float64) and the quotient is exactly 1 iff fl32(w + obs) was exact
     // (Fast2Sum, |w| >= |obs|), otherwise the float64 expression is evaluated.
     const float sum_err = fu.obsf - (w_new - w_old);
-    const bool keep_one = OFX_KEEP_ONE && fu.obs_is_f32 && (d - z) > fu.trunc_up && tsdf == 1.0f && w_old >= fabsf(fu.obsf) && sum_err == 0.0f &&
+    const bool keep_one = OFX_KEEP_ONE && OBS32 && (d - z) > fu.trunc_up && tsdf == 1.0f && w_old >= fabsf(fu.obsf) && sum_err == 0.0f &&
                           w_new != 0.0f;
     if (!keep_one) {
         const double diff = (double)d - (double)z;                      // tsdf.py:608, exact
