@@ -2,6 +2,9 @@
 // the per-voxel warp (cached anchors -> weights -> linear blend), brick-level frustum culling and
 // the per-thread body (4 consecutive z voxels: warp, project, test, fuse, store).
 #pragma once
+#ifndef OFX_SPEC_LOADS
+#define OFX_SPEC_LOADS 0
+#endif
 #include <cmath>
 
 #include "ofx_volume.cuh"
@@ -158,36 +161,39 @@ __device__ __forceinline__ bool brick_outside_frustum(const VolumeGeom &g, const
 // ---- per-thread body ---------------------------------------------------------------------------------
 // Thread t of a brick owns voxels (lx0 + t/64, iy0 + (t/8)%8, iz0 + 4*(t%8) .. +3).  Counters are
 // accumulated into c_upd / c_valid / c_wsum (the caller reduces them).
-template <int K, bool VEC, int MODE, bool OBS32>
+// `release` runs once per thread, warp-convergent, as soon as the staged node transforms and skin-cache
+// slot are no longer needed (after phase 1): the persistent kernel hands the stage back to its producer there.
+template <int K, bool VEC, int MODE, bool OBS32, typename Release>
 __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__restrict__ tsdf,
                                                   float *__restrict__ weight, float *__restrict__ colour,
                                                   const GraphArgs &ga, const FrameArgs &fa,
                                                   const float *__restrict__ s_rec, const uint8_t *__restrict__ s_slot,
                                                   const BrickCoord &bc, int n_used, int t, float *__restrict__ out_pts,
                                                   uint8_t *__restrict__ out_valid, unsigned &c_upd, unsigned &c_valid,
-                                                  unsigned &c_wsum)
+                                                  unsigned &c_wsum, Release release)
 {
     const int tz = t & 7, ty = (t >> 3) & 7, tx = t >> 6;
     const int lx = bc.lx0 + tx, iy = bc.iy0 + ty, iz0 = bc.iz0 + tz * VOX_PER_THREAD;
     const bool row_live = lx < g.nx && iy < g.Dy && iz0 < g.Dz;
-    if (!row_live) return;
     const int64_t vox0 = ((int64_t)lx * g.Dy + iy) * g.Dz + iz0;
-    const int n_vox = min(VOX_PER_THREAD, g.Dz - iz0);
+    const int n_vox = row_live ? min(VOX_PER_THREAD, g.Dz - iz0) : 0;
 
     // the brick's skin-cache slot sits in shared memory (one TMA bulk copy): per voxel one ids word and
     // one weight float4 per group of four anchors, read just in time (conflict-free: lane stride 4 / 16 B)
     constexpr int KP = K <= 4 ? 4 : 8;
     const uint32_t *s_ids = reinterpret_cast<const uint32_t *>(s_slot) + t;
     const float4 *s_w = reinterpret_cast<const float4 *>(s_slot + BRICK_VOXELS * KP) + t;
-    const float px = __ldg(g.px + lx), py = __ldg(g.py + iy);
+    const float px = __ldg(g.px + (row_live ? lx : 0)), py = __ldg(g.py + (row_live ? iy : 0));
 
     // ---- phase 1: warp + pixel of each voxel (no memory traffic beyond shared memory) ----
     int pixs[VOX_PER_THREAD];
     float zsel[VOX_PER_THREAD];
     unsigned cand = 0;
 #pragma unroll
+    for (int e = 0; e < VOX_PER_THREAD; ++e) { pixs[e] = 0; zsel[e] = 0.f; }
+    if (row_live)
+#pragma unroll
     for (int e = 0; e < VOX_PER_THREAD; ++e) {
-        pixs[e] = 0; zsel[e] = 0.f;
         if (!VEC && e >= n_vox) continue;
         const float pz = __ldg(g.pz + iz0 + e);
         float qx = px, qy = py, qz = pz;
@@ -226,12 +232,29 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
             if (skin_ok && st == 1) cand |= 1u << e;
         }
     }
+    __syncwarp();
+    release();
     if constexpr (MODE != MODE_DEFORM) {
-        // ---- phase 2: the (up to four) depth gathers in flight together, then the visibility test ----
+        // ---- phase 2: every load of the thread in flight together: the (up to four) depth and colour
+        // gathers and, speculatively, the thread's three volume words (a thread with a voxel in the image
+        // mostly updates; waiting for the depth test first would expose the DRAM latency a second time)
         if (!cand) return;
-        float dsel[VOX_PER_THREAD];
+        float dsel[VOX_PER_THREAD], ncol[VOX_PER_THREAD];
+        float tt[VOX_PER_THREAD], ww[VOX_PER_THREAD], cc[VOX_PER_THREAD];
 #pragma unroll
         for (int e = 0; e < VOX_PER_THREAD; ++e) dsel[e] = (cand & (1u << e)) ? __ldg(fa.depth + pixs[e]) : 0.0f;
+#if OFX_SPEC_LOADS
+        if (VEC) {
+            const float4 t4 = *reinterpret_cast<const float4 *>(tsdf + vox0);
+            const float4 w4 = *reinterpret_cast<const float4 *>(weight + vox0);
+            const float4 c4 = *reinterpret_cast<const float4 *>(colour + vox0);
+#pragma unroll
+            for (int e = 0; e < VOX_PER_THREAD; ++e) ncol[e] = (cand & (1u << e)) ? __ldg(fa.colour_im + pixs[e]) : 0.0f;
+            tt[0] = t4.x; tt[1] = t4.y; tt[2] = t4.z; tt[3] = t4.w;
+            ww[0] = w4.x; ww[1] = w4.y; ww[2] = w4.z; ww[3] = w4.w;
+            cc[0] = c4.x; cc[1] = c4.y; cc[2] = c4.z; cc[3] = c4.w;
+        }
+#endif
         unsigned upd = 0;
 #pragma unroll
         for (int e = 0; e < VOX_PER_THREAD; ++e) {
@@ -244,24 +267,25 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
         }
         if (!upd) return;
 
-        // ---- phase 3: volume words + new colours in flight together, fuse, store ----
-        float tt[VOX_PER_THREAD], ww[VOX_PER_THREAD], cc[VOX_PER_THREAD], ncol[VOX_PER_THREAD];
-        if (VEC) {
-            const float4 t4 = *reinterpret_cast<const float4 *>(tsdf + vox0);
-            const float4 w4 = *reinterpret_cast<const float4 *>(weight + vox0);
-            const float4 c4 = *reinterpret_cast<const float4 *>(colour + vox0);
+        // ---- phase 3: fuse, store ----
+        if (!(VEC && OFX_SPEC_LOADS)) {
+            if (VEC) {
+                const float4 t4 = *reinterpret_cast<const float4 *>(tsdf + vox0);
+                const float4 w4 = *reinterpret_cast<const float4 *>(weight + vox0);
+                const float4 c4 = *reinterpret_cast<const float4 *>(colour + vox0);
 #pragma unroll
-            for (int e = 0; e < VOX_PER_THREAD; ++e) ncol[e] = (upd & (1u << e)) ? __ldg(fa.colour_im + pixs[e]) : 0.0f;
-            tt[0] = t4.x; tt[1] = t4.y; tt[2] = t4.z; tt[3] = t4.w;
-            ww[0] = w4.x; ww[1] = w4.y; ww[2] = w4.z; ww[3] = w4.w;
-            cc[0] = c4.x; cc[1] = c4.y; cc[2] = c4.z; cc[3] = c4.w;
-        } else {
+                for (int e = 0; e < VOX_PER_THREAD; ++e) ncol[e] = (upd & (1u << e)) ? __ldg(fa.colour_im + pixs[e]) : 0.0f;
+                tt[0] = t4.x; tt[1] = t4.y; tt[2] = t4.z; tt[3] = t4.w;
+                ww[0] = w4.x; ww[1] = w4.y; ww[2] = w4.z; ww[3] = w4.w;
+                cc[0] = c4.x; cc[1] = c4.y; cc[2] = c4.z; cc[3] = c4.w;
+            } else {
 #pragma unroll
-            for (int e = 0; e < VOX_PER_THREAD; ++e)
-                if (upd & (1u << e)) {
-                    tt[e] = tsdf[vox0 + e]; ww[e] = weight[vox0 + e]; cc[e] = colour[vox0 + e];
-                    ncol[e] = __ldg(fa.colour_im + pixs[e]);
-                }
+                for (int e = 0; e < VOX_PER_THREAD; ++e)
+                    if (upd & (1u << e)) {
+                        tt[e] = tsdf[vox0 + e]; ww[e] = weight[vox0 + e]; cc[e] = colour[vox0 + e];
+                        ncol[e] = __ldg(fa.colour_im + pixs[e]);
+                    }
+            }
         }
         float wsum = 0.0f;
 #pragma unroll

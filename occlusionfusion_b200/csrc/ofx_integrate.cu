@@ -77,7 +77,7 @@ fused_brick_kernel(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ w
     }
     unsigned c_upd = 0, c_valid = 0, c_wsum = 0;
     brick_thread_work<K, VEC, MODE, OBS32>(g, tsdf, weight, colour, ga, fa, s_rec, s_slot, bc, n_used, threadIdx.x, out_pts,
-                                    out_valid, c_upd, c_valid, c_wsum);
+                                           out_valid, c_upd, c_valid, c_wsum, [] {});
     if constexpr (MODE != MODE_DEFORM) {
         c_upd = __reduce_add_sync(0xffffffffu, c_upd);
         c_valid = __reduce_add_sync(0xffffffffu, c_valid);
@@ -107,7 +107,7 @@ constexpr int CULL_THREADS = 256;
 constexpr int CULL_BRICKS_PER_CTA = CULL_THREADS / CULL_LANES;
 
 __global__ void __launch_bounds__(CULL_THREADS)
-brick_cull_kernel(GraphArgs ga, const float4 *__restrict__ brick_box, int n_active, Camera cam, int *__restrict__ live,
+brick_cull_kernel(VolumeGeom g, GraphArgs ga, const float4 *__restrict__ brick_box, int n_active, Camera cam, int *__restrict__ live,
                   int *__restrict__ n_live, unsigned long long *__restrict__ stats)
 {
     __shared__ int s_mask[CULL_THREADS / 32];
@@ -161,7 +161,11 @@ brick_cull_kernel(GraphArgs ga, const float4 *__restrict__ brick_box, int n_acti
         const int w = threadIdx.x >> 5;
         for (int k = 0; k < w; ++k) rank += __popc((unsigned)s_mask[k]);
         rank += __popc((unsigned)s_mask[w] & ((1u << (threadIdx.x & 31)) - 1u));
-        live[s_base + rank] = b;
+        // everything the fused kernel's producer needs about the brick, in one 32-byte record
+        const BrickCoord bc = brick_coord(g, b);
+        int4 *d = reinterpret_cast<int4 *>(live) + 2 * (s_base + rank);
+        d[0] = make_int4(bc.lx0, bc.iy0, bc.iz0, n_used);
+        d[1] = make_int4(o, __ldg(ga.brick_slot + b), b, 0);
     }
 }
 
@@ -179,8 +183,25 @@ brick_cull_kernel(GraphArgs ga, const float4 *__restrict__ brick_box, int n_acti
 #ifndef OFX_MIN_CTAS
 #define OFX_MIN_CTAS 4
 #endif
+#ifndef OFX_CONSUMER_SLEEP
+#define OFX_CONSUMER_SLEEP 0
+#endif
 #ifndef OFX_PREFETCH_VOLUME
 #define OFX_PREFETCH_VOLUME 0
+#endif
+#ifndef OFX_TIMING
+#define OFX_TIMING 0
+#endif
+#if OFX_TIMING
+// investigation build only: where the persistent kernel's warps wait (ns, summed over warps)
+__device__ unsigned long long g_dbg[8];
+__device__ unsigned long long g_cta[1024][4];   // per CTA: kernel entry, first data, end, bricks
+__device__ __forceinline__ unsigned long long gtime()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
 #endif
 constexpr int N_SLOTS = OFX_N_SLOTS;
 constexpr int RING_RECS = 256;                              // > MAX_BRICK_NODES: the largest brick fits an empty ring
@@ -191,7 +212,6 @@ struct SlotInfo {
     int lx0, iy0, iz0;
     int n_used;      // -1 = no more bricks
     int rec_off;     // first record of the brick in the ring
-    int cache_slot;
 };
 
 template <int K, bool VEC, bool OBS32>
@@ -218,6 +238,9 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
 
     if (warp == CONSUMER_WARPS) {
         // ===== producer warp (all lanes keep the same bookkeeping; lane 0 talks to the barriers) =====
+#if OFX_TIMING
+        unsigned long long dbg_a = 0, dbg_b = 0, dbg_n = 0;
+#endif
         const int n_live = *n_live_ptr;
         int idx = blockIdx.x;
         int rel = 0;                  // iterations [0, rel) have been released by the consumers
@@ -225,13 +248,23 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
         bool wrapped = false;         // in use: [tail, head) when !wrapped, [tail, end) + [0, head) when wrapped
         for (int it = 0;; ++it) {
             const int slot = it % N_SLOTS;
-            int b = 0, n_used = 0, o = 0, cslot = 0;
+            // everything that does not depend on the hand-back happens before waiting for it: the brick's
+            // descriptor (one 32-byte record written by the cull kernel), the first 32 node ids of its list,
+            // the source addresses, and an L2 prefetch of its cache slot
+            int n_used = 0, o = 0;
+            BrickCoord bc{0, 0, 0};
+            const uint8_t *slot_src = nullptr;
+            const float *rec_src = nullptr;
             const bool more = idx < n_live;
             if (more) {
-                b = __ldg(live + idx);
-                n_used = __ldg(ga.cnt + b);
-                o = __ldg(ga.off + b);
-                cslot = __ldg(ga.brick_slot + b);
+                const int4 *d = reinterpret_cast<const int4 *>(live) + 2 * idx;
+                const int4 d0 = __ldg(d), d1 = __ldg(d + 1);
+                bc = BrickCoord{d0.x, d0.y, d0.z};
+                n_used = d0.w; o = d1.x;
+                slot_src = ga.cache + (int64_t)d1.y * SLOT_BYTES;
+                if (lane < n_used)
+                    rec_src = ga.node_rec + (int64_t)__ldg(ga.brick_nodes + o + lane) * NODE_REC_FLOATS + NODE_XFORM_OFFSET;
+                if (lane < 5 * KP / 4) bulk_prefetch_l2(slot_src + lane * 4096, 4096u);
             }
             // room: a free descriptor slot and n_used contiguous records
             int start = -1;
@@ -244,7 +277,13 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
                     } else if (tail - head >= n_used) { start = head; head += n_used; }
                     if (start >= 0) break;
                 }
+#if OFX_TIMING
+                const unsigned long long t0 = gtime();
+#endif
                 named_bar_sync(1 + rel % N_SLOTS, PERSISTENT_THREADS);                          // oldest brick done
+#if OFX_TIMING
+                dbg_a += gtime() - t0; ++dbg_n;
+#endif
                 ++rel;
                 if (rel < it) {
                     const int nt = s_info[rel % N_SLOTS].rec_off;
@@ -256,20 +295,20 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
                 if (lane == 0) { s_info[slot].n_used = -1; mbar_arrive(&bar_data[slot]); }
                 break;
             }
-            const BrickCoord bc = brick_coord(g, b);
             if (lane == 0) {
                 s_info[slot].lx0 = bc.lx0; s_info[slot].iy0 = bc.iy0; s_info[slot].iz0 = bc.iz0;
-                s_info[slot].n_used = n_used; s_info[slot].rec_off = start; s_info[slot].cache_slot = cslot;
+                s_info[slot].n_used = n_used; s_info[slot].rec_off = start;
                 mbar_arrive_expect_tx(&bar_data[slot], (uint32_t)n_used * REC_BYTES + SLOT_BYTES);
                 // the brick's skin-cache slot (ids + weights of its 1024 voxels): one bulk copy
-                bulk_g2s(s_dyn + slot * SLOT_BYTES, ga.cache + (int64_t)cslot * SLOT_BYTES, SLOT_BYTES, &bar_data[slot]);
+                bulk_g2s(s_dyn + slot * SLOT_BYTES, slot_src, SLOT_BYTES, &bar_data[slot]);
             }
             __syncwarp();
             float *rec = s_rec + start * REC_STRIDE;
-            for (int i = lane; i < n_used; i += 32)
+            if (lane < n_used) bulk_g2s(rec + lane * REC_STRIDE, rec_src, REC_BYTES, &bar_data[slot]);
+            for (int i = lane + 32; i < n_used; i += 32)
                 bulk_g2s(rec + i * REC_STRIDE,
-                         ga.node_rec + (int64_t)__ldg(ga.brick_nodes + o + i) * NODE_REC_FLOATS + NODE_XFORM_OFFSET,
-                         REC_BYTES, &bar_data[slot]);
+                         ga.node_rec + (int64_t)__ldg(ga.brick_nodes + o + i) * NODE_REC_FLOATS + NODE_XFORM_OFFSET, REC_BYTES,
+                         &bar_data[slot]);
 #if OFX_PREFETCH_VOLUME
             if (VEC) {
                 const int lx = bc.lx0 + (lane >> 3), iy = bc.iy0 + (lane & 7);
@@ -282,29 +321,54 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
                 }
             }
 #endif
+#if OFX_TIMING
+            {
+                const unsigned long long t2 = gtime();
+                mbar_wait(&bar_data[slot], (uint32_t)(it / N_SLOTS) & 1u);
+                dbg_b += gtime() - t2;
+            }
+#endif
             int f = 0;
             if (lane == 0) f = atomicAdd(work_counter, 1);
             idx = (int)gridDim.x + __shfl_sync(0xffffffffu, f, 0);
         }
+#if OFX_TIMING
+        if (lane == 0) { atomicAdd(&g_dbg[0], dbg_a); atomicAdd(&g_dbg[1], dbg_n); atomicAdd(&g_dbg[5], dbg_b); }
+#endif
         return;
     }
 
     // ===== consumer warps =====
     // counters: per brick a warp reduction into shared memory (keeps them out of the registers that
     // live across the brick loop), flushed once when the CTA's consumers are done
+#if OFX_TIMING
+    unsigned long long dbg_a = 0, dbg_b = 0, dbg_n = 0;
+    if (threadIdx.x == 0) g_cta[blockIdx.x][0] = gtime();
+#endif
     for (int it = 0;; ++it) {
         const int slot = it % N_SLOTS;
         const uint32_t ph = (uint32_t)(it / N_SLOTS) & 1u;
+#if OFX_TIMING
+        const unsigned long long t0 = gtime();
+#endif
         mbar_wait(&bar_data[slot], ph);            // descriptor written and the TMA bytes of this brick have landed
+#if OFX_TIMING
+        const unsigned long long t1 = gtime();
+        dbg_a += t1 - t0; ++dbg_n;
+        if (it == 0 && threadIdx.x == 0) g_cta[blockIdx.x][1] = t1;
+#endif
         const SlotInfo info = s_info[slot];
         if (info.n_used < 0) break;
         const BrickCoord bc{info.lx0, info.iy0, info.iz0};
         unsigned c_upd = 0, c_valid = 0, c_wsum = 0;
         brick_thread_work<K, VEC, MODE_WARPED, OBS32>(g, tsdf, weight, colour, ga, fa, s_rec + info.rec_off * REC_STRIDE,
                                                       s_dyn + slot * SLOT_BYTES, bc, info.n_used, threadIdx.x, nullptr,
-                                                      nullptr, c_upd, c_valid, c_wsum);
+                                                      nullptr, c_upd, c_valid, c_wsum,
+                                                      [slot] { named_bar_arrive(1 + slot, PERSISTENT_THREADS); });
         __syncwarp();
-        named_bar_arrive(1 + slot, PERSISTENT_THREADS);
+#if OFX_TIMING
+        dbg_b += gtime() - t1;
+#endif
         c_upd = __reduce_add_sync(0xffffffffu, c_upd);
         c_valid = __reduce_add_sync(0xffffffffu, c_valid);
         c_wsum = __reduce_add_sync(0xffffffffu, c_wsum);
@@ -319,6 +383,10 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
             }
         }
     }
+#if OFX_TIMING
+    if (lane == 0) { atomicAdd(&g_dbg[2], dbg_a); atomicAdd(&g_dbg[3], dbg_n); atomicAdd(&g_dbg[4], dbg_b); }
+    if (threadIdx.x == 0) { g_cta[blockIdx.x][2] = gtime(); g_cta[blockIdx.x][3] = dbg_n - 1; }
+#endif
     named_bar_sync(1 + N_SLOTS, BRICK_THREADS);    // consumers only
     if (threadIdx.x == 0) {
         if (s_cnt[0]) atomicAdd(stats + OFX_STAT_UPDATED, (unsigned long long)s_cnt[0]);
@@ -379,7 +447,7 @@ static int launch_persistent_t(ofx_volume *v, const FrameArgs &fa, unsigned long
     OFX_CUDA(cudaMemsetAsync(n_live, 0, 2 * sizeof(int), s));
     const GraphArgs ga = graph_args(v);
     brick_cull_kernel<<<(v->n_active + CULL_BRICKS_PER_CTA - 1) / CULL_BRICKS_PER_CTA, CULL_THREADS, 0, s>>>(
-        ga, v->brick_box, v->n_active, fa.cam, v->live, n_live, stats);
+        v->geom, ga, v->brick_box, v->n_active, fa.cam, v->live, n_live, stats);
     OFX_LAUNCH_CHECK();
     const int cap = sm_count() * blocks_per_sm;       // persistent grid: a multiple of the SM count
     const int grid = v->n_active < cap ? v->n_active : cap;   // CTAs beyond the live count retire at once
@@ -425,6 +493,22 @@ extern "C" int ofx_integrate(ofx_volume *v, const float *depth, const float *col
     default: return launch_persistent<8>(v, fa, st, s);
     }
 }
+
+#if OFX_TIMING
+extern "C" int ofx_debug_timing(unsigned long long *out_host, int reset)
+{
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out_host, ofx::g_dbg, sizeof(unsigned long long) * 8);
+    if (reset) { unsigned long long z[8] = {0}; cudaMemcpyToSymbol(ofx::g_dbg, z, sizeof(z)); }
+    return 0;
+}
+extern "C" int ofx_debug_cta(unsigned long long *out_host)
+{
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out_host, ofx::g_cta, sizeof(unsigned long long) * 1024 * 4);
+    return 0;
+}
+#endif
 
 extern "C" int ofx_volume_deform(ofx_volume *v, float *out_pts, uint8_t *valid, void *stream)
 {

@@ -117,7 +117,7 @@ extern "C" int ofx_volume_create(ofx_volume **out, const ofx_volume_desc *d)
     OFX_CUDA(cudaMalloc(&v->brick_off, nb * sizeof(int)));
     OFX_CUDA(cudaMalloc(&v->brick_radius, nb * sizeof(float)));
     OFX_CUDA(cudaMalloc(&v->active, nb * sizeof(int)));
-    OFX_CUDA(cudaMalloc(&v->live, nb * sizeof(int)));
+    OFX_CUDA(cudaMalloc(&v->live, nb * LIVE_DESC_INTS * sizeof(int)));
     OFX_CUDA(cudaMalloc(&v->brick_slot, nb * sizeof(int)));
     OFX_CUDA(cudaMalloc(&v->brick_box, nb * sizeof(float4)));
     OFX_CUDA(cudaMalloc(&v->scratch, 16 * sizeof(int)));      // [0..5] set_graph results, [8] n_live, [9] brick work counter

@@ -15,6 +15,7 @@ constexpr int VOX_PER_THREAD = 4;
 constexpr int BRICK_THREADS = BX * BY * (BZ / VOX_PER_THREAD);   // 256
 constexpr int BRICK_VOXELS = BX * BY * BZ;                       // 1024
 constexpr int NODE_REC_FLOATS = 16;   // {gx,gy,gz,0, R00..R22, T0,T1,T2} = 64 B in global memory
+constexpr int LIVE_DESC_INTS = 8;      // live-brick descriptor: {lx0, iy0, iz0, n_used | list offset, cache slot, brick, 0}
 constexpr int NODE_XFORM_OFFSET = 4;  // the 48-byte {R, T} tail is what the fused kernels stage (one TMA bulk copy)
 constexpr int NODE_XFORM_FLOATS = 12;
 __host__ __device__ constexpr int slot_bytes_of(int kp) { return BRICK_VOXELS * 5 * kp; }
@@ -77,7 +78,7 @@ struct ofx_volume {
     int *active;                 // bricks with at least one skin-valid voxel
     int n_active;
     float4 *brick_box;           // n_bricks: brick centre (world) + bounding radius h, written by ofx_set_graph
-    int *live;                   // per frame: active bricks that survive the frustum / depth cull (n_bricks capacity)
+    int *live;                   // per frame: descriptors (LIVE_DESC_INTS ints) of the active bricks that survive the cull
     float *depth_tiles;          // per frame: max depth of each DEPTH_TILE x DEPTH_TILE pixel tile
     int depth_tiles_capacity;
     int *scratch;                // small device scratch: [0]=total [1]=max [2]=error [8]=n_live [9]=work counter
