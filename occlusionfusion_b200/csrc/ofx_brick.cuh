@@ -62,20 +62,19 @@ constexpr uint32_t REC_BYTES = NODE_XFORM_FLOATS * 4u;
 // q = sum_k w_k (R_k p + T_k) with the cached anchors and weights of one voxel (warpfield.py:225-226).
 // (The reference skips w == 0, warpfield.py:219: cached voxels have w >= exp(-8.0001) / (K + 1e-6) > 0.)
 template <int K, int KP>
-__device__ __forceinline__ void warp_voxel(const uint32_t (&ids)[2], const float (&w)[KP], const float *__restrict__ s_rec,
-                                           float px, float py, float pz, float &qx, float &qy, float &qz)
+__device__ __forceinline__ void warp_voxel(const uint32_t (&ids)[2], const float (&w)[KP], uint32_t rec_base, float px,
+                                           float py, float pz, float &qx, float &qy, float &qz)
 {
+    // rec_base: 32-bit shared-memory address of the brick's first record; one PRMT (byte k of the ids
+    // word) and one IMAD per anchor, then three 16-byte loads at immediate offsets
     float ax = 0.f, ay = 0.f, az = 0.f;
 #pragma unroll
     for (int k = 0; k < K; ++k) {
-        const uint32_t id = (ids[k >> 2] >> (8 * (k & 3))) & 0xFFu;
-        const float *rec = s_rec + id * REC_STRIDE;
+        const uint32_t addr = __byte_perm(ids[k >> 2], 0u, 0x4440u + (k & 3)) * REC_BYTES + rec_base;
         float r12[12];
-        const float4 a = *reinterpret_cast<const float4 *>(rec);
-        const float4 b = *reinterpret_cast<const float4 *>(rec + 4);
-        const float4 c = *reinterpret_cast<const float4 *>(rec + 8);
-        r12[0] = a.x; r12[1] = a.y; r12[2] = a.z; r12[3] = a.w; r12[4] = b.x; r12[5] = b.y; r12[6] = b.z; r12[7] = b.w;
-        r12[8] = c.x; r12[9] = c.y; r12[10] = c.z; r12[11] = c.w;
+        asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r12[0]), "=f"(r12[1]), "=f"(r12[2]), "=f"(r12[3]) : "r"(addr));
+        asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+16];" : "=f"(r12[4]), "=f"(r12[5]), "=f"(r12[6]), "=f"(r12[7]) : "r"(addr));
+        asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+32];" : "=f"(r12[8]), "=f"(r12[9]), "=f"(r12[10]), "=f"(r12[11]) : "r"(addr));
         lbs_accumulate(r12, w[k], px, py, pz, ax, ay, az);
     }
     qx = ax; qy = ay; qz = az;
@@ -184,6 +183,7 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
     const uint32_t *s_ids = reinterpret_cast<const uint32_t *>(s_slot) + t;
     const float4 *s_w = reinterpret_cast<const float4 *>(s_slot + BRICK_VOXELS * KP) + t;
     const float px = __ldg(g.px + (row_live ? lx : 0)), py = __ldg(g.py + (row_live ? iy : 0));
+    const uint32_t rec_base = smem_u32(s_rec);
 
     // ---- phase 1: warp + pixel of each voxel (no memory traffic beyond shared memory) ----
     int pixs[VOX_PER_THREAD];
@@ -201,7 +201,7 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
         if constexpr (MODE != MODE_IDENTITY) {
             uint32_t idw[2] = {0u, 0u};
             float wv[KP];
-            if (n_used > 0) {
+            if (MODE == MODE_WARPED || n_used > 0) {               // live bricks of the per-frame path always have nodes
 #pragma unroll
                 for (int gq = 0; gq < KP / 4; ++gq) {
                     idw[gq] = s_ids[(gq * 4 + e) * BRICK_THREADS];
@@ -216,7 +216,7 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
             skin_ok = (idw[0] & 0xFFu) != 0xFFu;
             // straight-line: a voxel without anchors blends record 0 with zero weights and is masked below
             if (!skin_ok) idw[0] = idw[1] = 0u;
-            warp_voxel<K, KP>(idw, wv, s_rec, px, py, pz, qx, qy, qz);
+            warp_voxel<K, KP>(idw, wv, rec_base, px, py, pz, qx, qy, qz);
         }
         if constexpr (MODE == MODE_DEFORM) {
             if (!skin_ok) { qx = px; qy = py; qz = pz; }              // registration_fusion.py:161,180
