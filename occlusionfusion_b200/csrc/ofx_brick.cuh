@@ -2,9 +2,6 @@
 // the per-voxel warp (cached anchors -> weights -> linear blend), brick-level frustum culling and
 // the per-thread body (4 consecutive z voxels: warp, project, test, fuse, store).
 #pragma once
-#ifndef OFX_SPEC_LOADS
-#define OFX_SPEC_LOADS 0
-#endif
 #include <cmath>
 
 #include "ofx_volume.cuh"
@@ -235,26 +232,11 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
     __syncwarp();
     release();
     if constexpr (MODE != MODE_DEFORM) {
-        // ---- phase 2: every load of the thread in flight together: the (up to four) depth and colour
-        // gathers and, speculatively, the thread's three volume words (a thread with a voxel in the image
-        // mostly updates; waiting for the depth test first would expose the DRAM latency a second time)
+        // ---- phase 2: the (up to four) depth gathers in flight together, then the visibility test ----
         if (!cand) return;
-        float dsel[VOX_PER_THREAD], ncol[VOX_PER_THREAD];
-        float tt[VOX_PER_THREAD], ww[VOX_PER_THREAD], cc[VOX_PER_THREAD];
+        float dsel[VOX_PER_THREAD];
 #pragma unroll
         for (int e = 0; e < VOX_PER_THREAD; ++e) dsel[e] = (cand & (1u << e)) ? __ldg(fa.depth + pixs[e]) : 0.0f;
-#if OFX_SPEC_LOADS
-        if (VEC) {
-            const float4 t4 = *reinterpret_cast<const float4 *>(tsdf + vox0);
-            const float4 w4 = *reinterpret_cast<const float4 *>(weight + vox0);
-            const float4 c4 = *reinterpret_cast<const float4 *>(colour + vox0);
-#pragma unroll
-            for (int e = 0; e < VOX_PER_THREAD; ++e) ncol[e] = (cand & (1u << e)) ? __ldg(fa.colour_im + pixs[e]) : 0.0f;
-            tt[0] = t4.x; tt[1] = t4.y; tt[2] = t4.z; tt[3] = t4.w;
-            ww[0] = w4.x; ww[1] = w4.y; ww[2] = w4.z; ww[3] = w4.w;
-            cc[0] = c4.x; cc[1] = c4.y; cc[2] = c4.z; cc[3] = c4.w;
-        }
-#endif
         unsigned upd = 0;
 #pragma unroll
         for (int e = 0; e < VOX_PER_THREAD; ++e) {
@@ -267,25 +249,25 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
         }
         if (!upd) return;
 
-        // ---- phase 3: fuse, store ----
-        if (!(VEC && OFX_SPEC_LOADS)) {
-            if (VEC) {
-                const float4 t4 = *reinterpret_cast<const float4 *>(tsdf + vox0);
-                const float4 w4 = *reinterpret_cast<const float4 *>(weight + vox0);
-                const float4 c4 = *reinterpret_cast<const float4 *>(colour + vox0);
+        // ---- phase 3: volume words + new colours in flight together, fuse, store.  Only threads with an
+        // update touch the volume (speculative loads before the depth test were measured: no gain) ----
+        float tt[VOX_PER_THREAD], ww[VOX_PER_THREAD], cc[VOX_PER_THREAD], ncol[VOX_PER_THREAD];
+        if (VEC) {
+            const float4 t4 = *reinterpret_cast<const float4 *>(tsdf + vox0);
+            const float4 w4 = *reinterpret_cast<const float4 *>(weight + vox0);
+            const float4 c4 = *reinterpret_cast<const float4 *>(colour + vox0);
 #pragma unroll
-                for (int e = 0; e < VOX_PER_THREAD; ++e) ncol[e] = (upd & (1u << e)) ? __ldg(fa.colour_im + pixs[e]) : 0.0f;
-                tt[0] = t4.x; tt[1] = t4.y; tt[2] = t4.z; tt[3] = t4.w;
-                ww[0] = w4.x; ww[1] = w4.y; ww[2] = w4.z; ww[3] = w4.w;
-                cc[0] = c4.x; cc[1] = c4.y; cc[2] = c4.z; cc[3] = c4.w;
-            } else {
+            for (int e = 0; e < VOX_PER_THREAD; ++e) ncol[e] = (upd & (1u << e)) ? __ldg(fa.colour_im + pixs[e]) : 0.0f;
+            tt[0] = t4.x; tt[1] = t4.y; tt[2] = t4.z; tt[3] = t4.w;
+            ww[0] = w4.x; ww[1] = w4.y; ww[2] = w4.z; ww[3] = w4.w;
+            cc[0] = c4.x; cc[1] = c4.y; cc[2] = c4.z; cc[3] = c4.w;
+        } else {
 #pragma unroll
-                for (int e = 0; e < VOX_PER_THREAD; ++e)
-                    if (upd & (1u << e)) {
-                        tt[e] = tsdf[vox0 + e]; ww[e] = weight[vox0 + e]; cc[e] = colour[vox0 + e];
-                        ncol[e] = __ldg(fa.colour_im + pixs[e]);
-                    }
-            }
+            for (int e = 0; e < VOX_PER_THREAD; ++e)
+                if (upd & (1u << e)) {
+                    tt[e] = tsdf[vox0 + e]; ww[e] = weight[vox0 + e]; cc[e] = colour[vox0 + e];
+                    ncol[e] = __ldg(fa.colour_im + pixs[e]);
+                }
         }
         float wsum = 0.0f;
 #pragma unroll

@@ -183,12 +183,6 @@ brick_cull_kernel(VolumeGeom g, GraphArgs ga, const float4 *__restrict__ brick_b
 #ifndef OFX_MIN_CTAS
 #define OFX_MIN_CTAS 4
 #endif
-#ifndef OFX_CONSUMER_SLEEP
-#define OFX_CONSUMER_SLEEP 0
-#endif
-#ifndef OFX_PREFETCH_VOLUME
-#define OFX_PREFETCH_VOLUME 0
-#endif
 #ifndef OFX_TIMING
 #define OFX_TIMING 0
 #endif
@@ -309,18 +303,6 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
                 bulk_g2s(rec + i * REC_STRIDE,
                          ga.node_rec + (int64_t)__ldg(ga.brick_nodes + o + i) * NODE_REC_FLOATS + NODE_XFORM_OFFSET, REC_BYTES,
                          &bar_data[slot]);
-#if OFX_PREFETCH_VOLUME
-            if (VEC) {
-                const int lx = bc.lx0 + (lane >> 3), iy = bc.iy0 + (lane & 7);
-                if (lx < g.nx && iy < g.Dy) {
-                    const int64_t row = ((int64_t)lx * g.Dy + iy) * g.Dz + bc.iz0;
-                    const uint32_t bytes = (uint32_t)min(BZ, g.Dz - bc.iz0) * 4u;
-                    bulk_prefetch_l2(tsdf + row, bytes);
-                    bulk_prefetch_l2(weight + row, bytes);
-                    bulk_prefetch_l2(colour + row, bytes);
-                }
-            }
-#endif
 #if OFX_TIMING
             {
                 const unsigned long long t2 = gtime();

@@ -7,7 +7,7 @@
 // /root/reference/fusion_with_occlusion/.
 #pragma once
 #ifndef OFX_SLEEP_NS
-#define OFX_SLEEP_NS 2000
+#define OFX_SLEEP_NS 100
 #endif
 #ifndef OFX_WAIT_HINT_NS
 #define OFX_WAIT_HINT_NS 2000

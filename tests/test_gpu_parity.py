@@ -164,6 +164,32 @@ def test_synthetic_dense_and_obs_weight(oracle):
     assert stats[1][1] <= stats[1][0]["skin_valid"] <= w.dims[0] * w.dims[1] * w.dims[2]
 
 
+def test_obs_weight_not_float32(oracle):
+    """obs_weight = 0.3 is not a float32 value: the general float64 weight sum (tsdf.py:373) runs instead
+    of the float32 fast path; the source frame takes the generic kernel, warped frames the persistent one."""
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload("tiny")
+    vol, ov, wf, stats = _run_pair(w, oracle, n_frames=4, obs_weight=0.3)
+    _assert_bit_equal(vol, ov)
+    for st, n in stats:
+        assert st["updated"] == n
+
+
+def test_medium_dense_certified_paths(oracle):
+    """393 k voxels, all skin-valid, three warped frames: large enough that the certified float32 pixel
+    (about 1e-4 of the voxels are undecided and take the float64 original), the float32 visibility test
+    and the free-space fast path of the running average all see their rare branches; bit-identical."""
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload("c1-dense", dim=[64, 64, 96], voxel=0.0125, n_nodes=125, H=240, W=320)
+    vol, ov, wf, stats = _run_pair(w, oracle, n_frames=4)
+    _assert_bit_equal(vol, ov)
+    for st, n in stats:
+        assert st["updated"] == n
+    assert stats[1][1] > 100000
+    t, c, wt = vol.get_volume()
+    assert wt.max() == 4.0 and (t < 1.0).any()          # repeated observations and a real surface band
+
+
 @pytest.mark.parametrize("dims", [[13, 17, 19], [8, 8, 33], [5, 3, 4]])
 def test_ragged_dims_scalar_path(dims, oracle):
     """Dz not a multiple of 4 -> unaligned rows -> scalar load/store path; bricks partly empty."""
