@@ -43,6 +43,16 @@ def parse():
     return ap.parse_args()
 
 
+def ncu_traffic(workload):
+    """DRAM bytes (read + write) of ONE launch of the fused kernel on this workload, from the committed
+    `ncu --set full` capture (profiles/ncu_traffic.json: written by hand from the .ncu-rep, per round)."""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    try:
+        return json.load(open(p)).get(workload)
+    except Exception:
+        return None
+
+
 def hbm_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -314,7 +324,7 @@ def bench_workload(name, args, rank, world, device, with_e2e=True):
     local_upd = float(stats_acc[_capi.STAT_UPDATED]) / K
     res = dict(workload=w, ms_per_step=step_ms, kernel_ms=kern_ms, updated=upd, skin_valid=valid, bricks=bricks,
                value=upd / (step_ms * 1e-3), wall_ms_per_step=t_wall * 1e3 / K, clocks=clocks,
-               local_updated=local_upd, launches_per_step=2, graph=graph is not None)
+               local_updated=local_upd, launches_per_step=3, graph=graph is not None)   # node transforms, brick cull, fused kernel
     # roofline of the fused kernel on this rank's shard (rank 0 reports its own shard)
     alg_bytes = 24.0 * local_upd + 8.0 * H * W + 60.0 * w.M
     res["alg_bytes"] = alg_bytes
@@ -437,8 +447,13 @@ def main():
             "e2e": main_res["e2e"], "gpu_launches": main_res["launches_per_step"] * args.steps,
             "clocks": main_res["clocks"],
             "roofline": {"bound": "hbm", "achieved": main_res["achieved_gbs"], "peak": peak, "unit": "GB/s",
-                         "frac": main_res["achieved_gbs"] / peak, "traffic": None, "peak_source": peak_src,
-                         "kernel": "fused_brick_kernel<K,VEC,WARPED>", "kernel_ms": main_res["kernel_ms_local"],
+                         "frac": main_res["achieved_gbs"] / peak,
+                         "traffic": (ncu_traffic(w.name) or {}).get("dram_bytes_per_launch") if world == 1 else None,
+                         "traffic_source": (ncu_traffic(w.name) or {}).get("source") if world == 1 else None,
+                         "peak_source": peak_src,
+                         "kernel": "fused_warped_persistent<K,VEC,OBS32> (+ brick_cull_kernel and two 16-byte memsets: "
+                                   "CUDA events around ofx_integrate)",
+                         "kernel_ms": main_res["kernel_ms_local"],
                          "algorithmic_bytes_per_launch": main_res["alg_bytes"],
                          "bytes_formula": "24*N_updated(this GPU) + 8*W*H + 60*M"},
             "cpu_baseline": cb, "also": also,
