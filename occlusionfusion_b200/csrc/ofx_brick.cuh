@@ -3,6 +3,7 @@
 // the per-thread body (4 consecutive z voxels: warp, project, test, fuse, store).
 #pragma once
 #include <cmath>
+#include <type_traits>
 
 #include "ofx_volume.cuh"
 
@@ -63,16 +64,73 @@ __device__ __forceinline__ void warp_voxel(const uint32_t (&ids)[2], const float
                                            float py, float pz, float &qx, float &qy, float &qz)
 {
     // rec_base: 32-bit shared-memory address of the brick's first record; one PRMT (byte k of the ids
-    // word) and one IMAD per anchor, then three 16-byte loads at immediate offsets
+    // word) and one IMAD per anchor, then three 16-byte loads at immediate offsets.  The loads are
+    // `asm volatile`: the bytes are written by the TMA unit / by build_row_table, invisibly to the
+    // compiler, which must neither reuse a value from the previous brick nor move a load above them.
     float ax = 0.f, ay = 0.f, az = 0.f;
 #pragma unroll
     for (int k = 0; k < K; ++k) {
         const uint32_t addr = __byte_perm(ids[k >> 2], 0u, 0x4440u + (k & 3)) * REC_BYTES + rec_base;
         float r12[12];
-        asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r12[0]), "=f"(r12[1]), "=f"(r12[2]), "=f"(r12[3]) : "r"(addr));
-        asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+16];" : "=f"(r12[4]), "=f"(r12[5]), "=f"(r12[6]), "=f"(r12[7]) : "r"(addr));
-        asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+32];" : "=f"(r12[8]), "=f"(r12[9]), "=f"(r12[10]), "=f"(r12[11]) : "r"(addr));
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r12[0]), "=f"(r12[1]), "=f"(r12[2]), "=f"(r12[3]) : "r"(addr));
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+16];" : "=f"(r12[4]), "=f"(r12[5]), "=f"(r12[6]), "=f"(r12[7]) : "r"(addr));
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+32];" : "=f"(r12[8]), "=f"(r12[9]), "=f"(r12[10]), "=f"(r12[11]) : "r"(addr));
         lbs_accumulate(r12, w[k], px, py, pz, ax, ay, az);
+    }
+    qx = ax; qy = ay; qz = az;
+}
+
+// ---- per-warp row tables ---------------------------------------------------------------------------
+// The reference evaluates R p + T as fma(R_2, p_z, fma(R_1, p_y, fma(R_0, p_x, T))) per component
+// (ofx_math.cuh: lbs_accumulate).  The inner two FMAs depend only on the node and on the voxel ROW
+// (x, y); a warp owns four rows of a brick, eight lanes per row.  So each warp first tabulates, for its
+// rows and the brick's nodes, B = fma(R_1, p_y, fma(R_0, p_x, T)) together with the z column of R, and
+// the per-voxel work becomes q_k = fma(R_2, p_z, B): the same operations in the same order (bit-identical),
+// half the FMAs and half the shared-memory bytes per anchor (24 instead of 48) -- shared-memory wavefronts
+// are what bounds the kernel (profiles/: l1tex data pipe at 90 %).
+//   tab   float4 [4 rows][ROW_TAB_CAP]   {B_x, B_y, B_z, R_02}
+//   col   float2 [ROW_TAB_CAP]           {R_12, R_22}
+// Bricks with more than ROW_TAB_CAP nodes take the record path (warp_voxel).
+constexpr int ROW_TAB_CAP = 32;
+constexpr int ROW_TAB_BYTES = 4 * ROW_TAB_CAP * 16 + ROW_TAB_CAP * 8;      // per warp
+
+__device__ __forceinline__ void build_row_table(uint32_t rec_base, int n_used, float px, float py, uint32_t tab_base, int lane)
+{
+    const int r = lane >> 3;
+    for (int n = lane & 7; n < n_used; n += 8) {
+        const uint32_t addr = (uint32_t)n * REC_BYTES + rec_base;
+        float a[12];
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(a[0]), "=f"(a[1]), "=f"(a[2]), "=f"(a[3]) : "r"(addr));
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+16];" : "=f"(a[4]), "=f"(a[5]), "=f"(a[6]), "=f"(a[7]) : "r"(addr));
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+32];" : "=f"(a[8]), "=f"(a[9]), "=f"(a[10]), "=f"(a[11]) : "r"(addr));
+        const float bx = __fmaf_rn(a[1], py, __fmaf_rn(a[0], px, a[9]));
+        const float by = __fmaf_rn(a[4], py, __fmaf_rn(a[3], px, a[10]));
+        const float bz = __fmaf_rn(a[7], py, __fmaf_rn(a[6], px, a[11]));
+        const uint32_t ent = tab_base + (uint32_t)(r * ROW_TAB_CAP + n) * 16u;
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(ent), "f"(bx), "f"(by), "f"(bz), "f"(a[2]) : "memory");
+        if (r == 0)
+            asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(tab_base + 4u * ROW_TAB_CAP * 16u + (uint32_t)n * 8u), "f"(a[5]),
+                         "f"(a[8])
+                         : "memory");
+    }
+    __syncwarp();
+}
+
+// q = sum_k w_k fma(R_2k, p_z, B_k) through the warp's row table; row_base = table row of this lane
+template <int K, int KP>
+__device__ __forceinline__ void warp_voxel_tab(const uint32_t (&ids)[2], const float (&w)[KP], uint32_t row_base,
+                                               uint32_t col_base, float pz, float &qx, float &qy, float &qz)
+{
+    float ax = 0.f, ay = 0.f, az = 0.f;
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        const uint32_t id = __byte_perm(ids[k >> 2], 0u, 0x4440u + (k & 3));
+        float bx, by, bz, r02, r12, r22;
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(bx), "=f"(by), "=f"(bz), "=f"(r02) : "r"(id * 16u + row_base));
+        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(r12), "=f"(r22) : "r"(id * 8u + col_base));
+        ax = __fmaf_rn(w[k], __fmaf_rn(r02, pz, bx), ax);
+        ay = __fmaf_rn(w[k], __fmaf_rn(r12, pz, by), ay);
+        az = __fmaf_rn(w[k], __fmaf_rn(r22, pz, bz), az);
     }
     qx = ax; qy = ay; qz = az;
 }
@@ -164,7 +222,8 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
                                                   float *__restrict__ weight, float *__restrict__ colour,
                                                   const GraphArgs &ga, const FrameArgs &fa,
                                                   const float *__restrict__ s_rec, const uint8_t *__restrict__ s_slot,
-                                                  const BrickCoord &bc, int n_used, int t, float *__restrict__ out_pts,
+                                                  uint8_t *s_tab, const BrickCoord &bc, int n_used, int t,
+                                                  float *__restrict__ out_pts,
                                                   uint8_t *__restrict__ out_valid, unsigned &c_upd, unsigned &c_valid,
                                                   unsigned &c_wsum, Release release)
 {
@@ -179,7 +238,8 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
     constexpr int KP = K <= 4 ? 4 : 8;
     const uint32_t *s_ids = reinterpret_cast<const uint32_t *>(s_slot) + t;
     const float4 *s_w = reinterpret_cast<const float4 *>(s_slot + BRICK_VOXELS * KP) + t;
-    const float px = __ldg(g.px + (row_live ? lx : 0)), py = __ldg(g.py + (row_live ? iy : 0));
+    // (x, y of the row even for lanes whose z lies beyond the volume: they help build the row table)
+    const float px = __ldg(g.px + min(lx, g.nx - 1)), py = __ldg(g.py + min(iy, g.Dy - 1));
     const uint32_t rec_base = smem_u32(s_rec);
 
     // ---- phase 1: warp + pixel of each voxel (no memory traffic beyond shared memory) ----
@@ -188,6 +248,14 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
     unsigned cand = 0;
 #pragma unroll
     for (int e = 0; e < VOX_PER_THREAD; ++e) { pixs[e] = 0; zsel[e] = 0.f; }
+    // s_tab != nullptr (persistent kernel): row tables when the brick's node list fits (brick-uniform)
+    const bool use_tab = MODE != MODE_IDENTITY && s_tab != nullptr && n_used <= ROW_TAB_CAP;
+    const uint32_t tab_base = use_tab ? smem_u32(s_tab) : 0u;
+    if (use_tab) build_row_table(rec_base, n_used, px, py, tab_base, t & 31);
+    const uint32_t row_base = tab_base + (uint32_t)((t & 31) >> 3) * (ROW_TAB_CAP * 16u);
+    const uint32_t col_base = tab_base + 4u * ROW_TAB_CAP * 16u;
+    auto phase1 = [&](auto tab_tag) {
+    constexpr bool TAB = decltype(tab_tag)::value;
     if (row_live)
 #pragma unroll
     for (int e = 0; e < VOX_PER_THREAD; ++e) {
@@ -213,7 +281,8 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
             skin_ok = (idw[0] & 0xFFu) != 0xFFu;
             // straight-line: a voxel without anchors blends record 0 with zero weights and is masked below
             if (!skin_ok) idw[0] = idw[1] = 0u;
-            warp_voxel<K, KP>(idw, wv, rec_base, px, py, pz, qx, qy, qz);
+            if constexpr (TAB) warp_voxel_tab<K, KP>(idw, wv, row_base, col_base, pz, qx, qy, qz);
+            else warp_voxel<K, KP>(idw, wv, rec_base, px, py, pz, qx, qy, qz);
         }
         if constexpr (MODE == MODE_DEFORM) {
             if (!skin_ok) { qx = px; qy = py; qz = pz; }              // registration_fusion.py:161,180
@@ -229,6 +298,8 @@ __device__ __forceinline__ void brick_thread_work(const VolumeGeom &g, float *__
             if (skin_ok && st == 1) cand |= 1u << e;
         }
     }
+    };
+    if (use_tab) phase1(std::true_type{}); else phase1(std::false_type{});
     __syncwarp();
     release();
     if constexpr (MODE != MODE_DEFORM) {

@@ -76,7 +76,7 @@ fused_brick_kernel(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ w
         if (s_cull) return;
     }
     unsigned c_upd = 0, c_valid = 0, c_wsum = 0;
-    brick_thread_work<K, VEC, MODE, OBS32>(g, tsdf, weight, colour, ga, fa, s_rec, s_slot, bc, n_used, threadIdx.x, out_pts,
+    brick_thread_work<K, VEC, MODE, OBS32>(g, tsdf, weight, colour, ga, fa, s_rec, s_slot, nullptr, bc, n_used, threadIdx.x, out_pts,
                                            out_valid, c_upd, c_valid, c_wsum, [] {});
     if constexpr (MODE != MODE_DEFORM) {
         c_upd = __reduce_add_sync(0xffffffffu, c_upd);
@@ -178,7 +178,7 @@ brick_cull_kernel(VolumeGeom g, GraphArgs ga, const float4 *__restrict__ brick_b
 //   named barrier 1 + slot   consumers -> producer: all eight warps are done with the slot and its records
 //                            (bar.arrive / bar.sync: the producer blocks in hardware, it does not poll)
 #ifndef OFX_N_SLOTS
-#define OFX_N_SLOTS 2
+#define OFX_N_SLOTS 1
 #endif
 #ifndef OFX_MIN_CTAS
 #define OFX_MIN_CTAS 4
@@ -209,7 +209,7 @@ struct SlotInfo {
 };
 
 template <int K, bool VEC, bool OBS32>
-__global__ void __launch_bounds__(PERSISTENT_THREADS, K <= 4 ? OFX_MIN_CTAS : 2)
+__global__ void __launch_bounds__(PERSISTENT_THREADS, K <= 4 ? OFX_MIN_CTAS : 3)
 fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ weight, float *__restrict__ colour,
                         GraphArgs ga, FrameArgs fa, const int *__restrict__ live, const int *__restrict__ n_live_ptr,
                         int *__restrict__ work_counter, unsigned long long *__restrict__ stats)
@@ -219,6 +219,7 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
     constexpr uint32_t SLOT_BYTES = slot_bytes_of(KP);
     extern __shared__ __align__(128) unsigned char s_dyn[];
     float *s_rec = reinterpret_cast<float *>(s_dyn + N_SLOTS * SLOT_BYTES);
+    uint8_t *s_tab = s_dyn + N_SLOTS * SLOT_BYTES + RING_RECS * REC_BYTES + (threadIdx.x >> 5) * ROW_TAB_BYTES;   // consumer warps
     __shared__ __align__(8) uint64_t bar_data[N_SLOTS];
     __shared__ SlotInfo s_info[N_SLOTS];
     __shared__ unsigned s_cnt[4];
@@ -344,8 +345,8 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
         const BrickCoord bc{info.lx0, info.iy0, info.iz0};
         unsigned c_upd = 0, c_valid = 0, c_wsum = 0;
         brick_thread_work<K, VEC, MODE_WARPED, OBS32>(g, tsdf, weight, colour, ga, fa, s_rec + info.rec_off * REC_STRIDE,
-                                                      s_dyn + slot * SLOT_BYTES, bc, info.n_used, threadIdx.x, nullptr,
-                                                      nullptr, c_upd, c_valid, c_wsum,
+                                                      s_dyn + slot * SLOT_BYTES, s_tab, bc, info.n_used, threadIdx.x,
+                                                      nullptr, nullptr, c_upd, c_valid, c_wsum,
                                                       [slot] { named_bar_arrive(1 + slot, PERSISTENT_THREADS); });
         __syncwarp();
 #if OFX_TIMING
@@ -417,7 +418,7 @@ template <int K, bool VEC, bool OBS32>
 static int launch_persistent_t(ofx_volume *v, const FrameArgs &fa, unsigned long long *stats, cudaStream_t s)
 {
     static int blocks_per_sm = 0;      // per instantiation
-    const size_t smem = (size_t)N_SLOTS * slot_bytes_of(K <= 4 ? 4 : 8) + RING_RECS * REC_BYTES;
+    const size_t smem = (size_t)N_SLOTS * slot_bytes_of(K <= 4 ? 4 : 8) + RING_RECS * REC_BYTES + CONSUMER_WARPS * ROW_TAB_BYTES;
     if (blocks_per_sm == 0) {
         OFX_CUDA(cudaFuncSetAttribute(fused_warped_persistent<K, VEC, OBS32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         OFX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, fused_warped_persistent<K, VEC, OBS32>,
