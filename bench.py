@@ -352,6 +352,10 @@ def bench_e2e(w, vol, wf, sf, frames, ests, args, rank, world, device):
     n_frames = len(ests)
     K, Wm = args.steps, max(3, args.warmup)
     H, W = w.H, w.W
+    # the camera frames wait in page-locked host memory (numpy views of pinned tensors): the H2D copy of
+    # RGB + Z inside the timed region is a DMA straight from them
+    if rank == 0:
+        frames = [torch.from_numpy(f).pin_memory().numpy() if f is not None else None for f in frames]
     fid = [getattr(vol, "frame_id", 0)]
     wf.frame_id = fid[0]                 # the warp field follows the volume's frame counter (warpfield.py:399)
 

@@ -9,9 +9,6 @@
 #ifndef OFX_SLEEP_NS
 #define OFX_SLEEP_NS 100
 #endif
-#ifndef OFX_WAIT_HINT_NS
-#define OFX_WAIT_HINT_NS 2000
-#endif
 #ifndef OFX_KEEP_ONE
 #define OFX_KEEP_ONE 1
 #endif
@@ -321,18 +318,18 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar)
 }
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
 {
-    // the suspend-time hint lets the hardware park the warp for up to that many ns per attempt instead
-    // of returning at once: a spinning warp otherwise issues at IPC ~1 and takes slots from working warps
+    // plain try_wait loop.  (A suspend-time hint compiles to NANOSLEEP.SYNCS plus a reload of the
+    // parity from local memory per poll -- measured: no faster, and the reloads cost L1 wavefronts.)
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
         "WAIT_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
         "@p bra DONE_%=;\n"
         "bra WAIT_%=;\n"
         "DONE_%=:\n"
         "}\n" ::"r"(smem_u32(bar)),
-        "r"(parity), "r"(OFX_WAIT_HINT_NS)
+        "r"(parity)
         : "memory");
 }
 // named barriers (bar.arrive / bar.sync): consumers signal without blocking, the producer blocks in

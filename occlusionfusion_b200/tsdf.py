@@ -163,14 +163,20 @@ class TSDFVolume:
             self._frame_dev[3].copy_(im_t[-1])
         else:
             src = im_t if im_t is not None else torch.from_numpy(np.asarray(im, dtype=np.float32))
-            if self._h2d_done is not None:
-                self._h2d_done.synchronize()     # the previous frame's DMA must have left the staging buffer
-            self._frame_host[:3].copy_(src[:3])
-            self._frame_host[3].copy_(src[-1])
-            self._frame_dev.copy_(self._frame_host, non_blocking=True)
-            if self._h2d_done is None:
-                self._h2d_done = torch.cuda.Event()
-            self._h2d_done.record(torch.cuda.current_stream(self.device))
+            if src.is_pinned():
+                # the caller's frame already lives in page-locked memory: DMA the four channels straight
+                # from it (the caller must not overwrite the frame before this integrate has finished)
+                self._frame_dev[:3].copy_(src[:3], non_blocking=True)
+                self._frame_dev[3].copy_(src[-1], non_blocking=True)
+            else:
+                if self._h2d_done is not None:
+                    self._h2d_done.synchronize()     # the previous frame's DMA must have left the staging buffer
+                self._frame_host[:3].copy_(src[:3])
+                self._frame_host[3].copy_(src[-1])
+                self._frame_dev.copy_(self._frame_host, non_blocking=True)
+                if self._h2d_done is None:
+                    self._h2d_done = torch.cuda.Event()
+                self._h2d_done.record(torch.cuda.current_stream(self.device))
         self.h2d_bytes_last_frame = self._frame_dev.numel() * 4
         _capi.check(self._lib.ofx_pack_frame(_capi.ptr(self._frame_dev), 4, H, W, _capi.ptr(self._color_im_dev),
                                              _capi.ptr(self._depth_im_dev), _capi.stream_ptr(self.device)))

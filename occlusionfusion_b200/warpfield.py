@@ -53,6 +53,7 @@ class WarpField:
             self.savepath = None
         self._graph_key = None          # (id of node array, M, K, coverage) last uploaded
         self._transforms_dirty = True
+        self._RT_host = None            # pinned staging [R | T] for the per-frame upload
         self._R_dev = self._T_dev = None
 
     @property
@@ -75,10 +76,24 @@ class WarpField:
                     if hasattr(self, a):
                         delattr(self, a)
             if self._transforms_dirty:
-                self._R_dev = _capi.to_device(np.asarray(self.rotations).astype(np.float32), torch.float32, self.device)
-                self._T_dev = _capi.to_device(np.asarray(self.translations).astype(np.float32), torch.float32, self.device)
-                assert self._R_dev.shape[0] == nodes.shape[0] == self._T_dev.shape[0], \
+                M = nodes.shape[0]
+                R = np.asarray(self.rotations)
+                T = np.asarray(self.translations)
+                assert R.shape[0] == M == T.shape[0], \
                     f"Nodes mismatch between transformation data:{self.rotations.shape} and graph nodes:{nodes.shape}"
+                # one pinned staging buffer [R (9M) | T (3M)], one asynchronous upload
+                if self._RT_host is None or self._RT_host.numel() != 12 * M:
+                    self._RT_host = torch.empty(12 * M, dtype=torch.float32, pin_memory=True)
+                    self._RT_dev = torch.empty(12 * M, dtype=torch.float32, device=self.device)
+                    self._RT_done = torch.cuda.Event()
+                else:
+                    self._RT_done.synchronize()      # the previous upload has left the staging buffer
+                h = self._RT_host.numpy()
+                h[:9 * M] = R.reshape(-1)            # casts to float32 like the reference's device upload
+                h[9 * M:] = T.reshape(-1)
+                self._RT_dev.copy_(self._RT_host, non_blocking=True)
+                self._RT_done.record(torch.cuda.current_stream(self.device))
+                self._R_dev, self._T_dev = self._RT_dev[:9 * M], self._RT_dev[9 * M:]
                 _capi.check(self._lib.ofx_set_transforms(self.tsdf._h, _capi.ptr(self._R_dev), _capi.ptr(self._T_dev),
                                                          _capi.stream_ptr(self.device)))
                 self._transforms_dirty = False
