@@ -75,7 +75,7 @@ int64_t ofx_volume_num_voxels(const ofx_volume *v); /* local voxels: nx_local*Dy
 
 /* Graph nodes (canonical positions g, EDGraph.nodes) -- call again after node insertion
  * (WarpField.update_graph, warpfield.py:487-582 -> :532-533 rebuild tree + re-skin).
- * Rebuilds the per-voxel anchor cache (the device form of WarpField.skin_tsdf's cache,
+ * Rebuilds the per-voxel skin cache (anchor ids + normalised weights; the device form of WarpField.skin_tsdf's cache,
  * warpfield.py:131-141).  K = graph_neighbours (warpfield.py:60), 1..OFX_MAX_K, K <= M. */
 int ofx_set_graph(ofx_volume *v, const float *nodes, int32_t M, double node_coverage, int32_t K,
                   void *stream);

@@ -1,21 +1,21 @@
 // ofx_integrate.cu -- the fused hot kernels of libofx.so (sm_100a):
-//     per voxel: anchors (cached ids) -> skinning weights -> linear-blend warp -> projection ->
-//     visibility test -> running-average TSDF / weight / colour update, in one pass.
+//     per voxel: cached anchors + weights -> linear-blend warp -> projection -> visibility test ->
+//     running-average TSDF / weight / colour update, in one pass.
 // Replaces, per frame, WarpField.deform_tsdf (warpfield.py:369-380: skin_tsdf + deform) and
 // TSDFVolume.integrate (tsdf.py:378-494) -- in the reference five full-volume host arrays and
-// two device round trips; here 24 B of HBM traffic per UPDATED voxel plus K (padded to 4 or 8)
-// bytes of anchor cache per voxel of a visited brick, and nothing for the rest of the volume.
+// two device round trips; here 24 B of HBM traffic per UPDATED voxel plus 20 B of skin cache per
+// voxel of a visited brick (K <= 4), and nothing for the rest of the volume.
 //
 // Work unit: a brick of 4 x 8 x 32 voxels handled by 256 threads, each thread owning four
 // consecutive voxels along z = one float4 of each of the three volumes (coalesced 128 B rows).
 //
+//   brick_cull_kernel        per frame: active bricks -> live list (exact frustum cull)
 //   fused_warped_persistent  (warped frames, the per-frame hot path)
-//       persistent CTAs (a multiple of the SM count) walk the list of active bricks.  A
-//       producer warp gathers the next brick's node records (64 B each: position, rotation,
-//       translation) into shared memory with the TMA unit (cp.async.bulk, one copy per node)
-//       through a two-stage mbarrier pipeline and decides the brick-level frustum cull, while
-//       eight consumer warps process the current brick; counters stay in registers until the
-//       CTA retires.
+//       persistent CTAs (a multiple of the SM count) walk the live list.  A producer warp stages
+//       the next brick's skin-cache slot (one 20 KB bulk copy) and node transforms (one 48-byte
+//       bulk copy per node) in shared memory with the TMA unit; eight consumer warps tabulate the
+//       row-invariant part of R p + T, process the brick in three phases (ofx_brick.cuh) and hand
+//       the stage back through a named barrier.
 //   fused_brick_kernel       (source frame = identity warp; deform_tsdf materialisation)
 //       one CTA per brick, same per-thread body.
 #include "ofx_brick.cuh"
