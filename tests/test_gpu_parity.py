@@ -208,6 +208,47 @@ def test_other_k(K, oracle):
     assert stats[1][1] > 0
 
 
+def test_sequence_with_node_insertion(oracle):
+    """BASELINE config 3 in small: a frame sequence with per-frame graph-node updates and node insertion
+    (EDGraph.update appends nodes, warpfield.py:532-533 re-skins every voxel): after each insertion the
+    device node table and skin cache are rebuilt and the following frames stay bit-identical to the
+    oracle driven with the same node table."""
+    from occlusionfusion_b200 import WarpField
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload("tiny")
+    vol = _mk_volume(w)
+    ov = oracle.OracleVolume(w.dims, w.origin, w.voxel_size, w.intr, w.trunc)
+    M0 = w.M - 30                                        # start with a subset, insert the rest in three goes
+    nodes = w.nodes[:M0].copy()
+    wf = WarpField(_graph(nodes, w.coverage), vol, None)
+    wf.graph_neighbours = w.K
+    vol.warpfield = wf
+    ov.set_graph(nodes, w.coverage, w.K)
+    n_upd = []
+    for f in range(8):
+        im = w.frame(f)
+        if f > 0:
+            if f in (3, 5, 6):                           # node insertion: old nodes keep their indices
+                nodes = w.nodes[: len(nodes) + 10].copy()
+                wf.graph.nodes = nodes
+                wf.rotations = np.tile(np.eye(3, dtype=np.float32), (len(nodes), 1, 1))
+                wf.translations = np.zeros((len(nodes), 3), np.float32)
+                wf.deformed_nodes = nodes.copy()
+                ov.set_graph(nodes, w.coverage, w.K)
+            est = w.estimate(f, nodes)
+            wf.update_transformations(est)
+            ov.set_transforms(est["node_rotations"], wf.translations)
+        vol.integrate({"im": im, "id": f})
+        n = ov.integrate(im, f == 0)
+        assert vol.last_stats()["updated"] == n, f
+        n_upd.append(n)
+    _assert_bit_equal(vol, ov)
+    assert min(n_upd[1:]) > 1000
+    a, wt, v = wf.skin_tsdf()
+    oa, owt, ovl = ov.skin_tsdf()
+    assert np.array_equal(a, oa) and np.array_equal(wt, owt) and np.array_equal(v, ovl)
+
+
 @pytest.mark.parametrize("x_block", [None, 4])
 def test_sharded_equals_whole(x_block, oracle):
     """Two shards (contiguous slabs, and 4-plane blocks dealt round-robin) reproduce the whole volume."""
