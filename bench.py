@@ -39,6 +39,7 @@ def parse():
     ap.add_argument("--also", default="c2,c1", help="extra workloads reported under 'also' (N=1 only); '' = none")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of a CUDA graph replay")
+    ap.add_argument("--no-pipeline", action="store_true", help="N > 1: broadcast -> kernel -> all-gather strictly in sequence")
     ap.add_argument("--cpu-planes", type=int, default=0, help="x-planes in the CPU sample (0 = auto)")
     return ap.parse_args()
 
@@ -184,13 +185,18 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
-def workload_config(w, n_gpus):
+def workload_config(w, n_gpus, pipelined=False):
     return {"workload": f"{w.name}: {w.dims[0]}x{w.dims[1]}x{w.dims[2]} voxels @ {w.voxel_size * 1e3:.2f} mm, "
                         f"{w.W}x{w.H} synthetic depth+colour, {w.M} nodes, K={w.K}, scene={w.scene}, warped frames, "
                         f"steady state (graph unchanged)",
             "sharding": f"x-plane blocks of 4 dealt round-robin over {n_gpus} GPU(s)" if n_gpus > 1 else "single GPU",
-            "l2": "volume state > L2 and a 256 MiB buffer is written between timed steps",
-            "launch": "per-frame launch sequence replayed as one CUDA graph (falls back to eager launches)"}
+            "l2": ("per-GPU working set per frame (volume words + skin cache, >= 300 MB) exceeds the 126 MB L2; "
+                   "no flush between pipelined steps") if pipelined else
+                  "volume state > L2 and a 256 MiB buffer is written between timed steps",
+            "launch": ("two packets / two streams: broadcast of frame t+1 and counter all-gather of frame t overlap the "
+                       "kernels; the K steps are one CUDA graph (falls back to eager launches), timed first-to-last with CUDA "
+                       "events, max over ranks") if pipelined else
+                      "per-frame launch sequence replayed as one CUDA graph (falls back to eager launches)"}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -276,41 +282,92 @@ def bench_workload(name, args, rank, world, device, with_e2e=True):
         stats_acc += core(*kevs[i])
     barrier()
 
-    # the per-frame launch sequence is short and launch-bound: replay it as one CUDA graph
+    pipelined = world > 1 and not args.no_pipeline
     graph = None
-    if not args.no_graph:
-        try:
-            g_ = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g_):
-                core()
-            graph = g_
-            prep(0); graph.replay()
-            barrier()
-        except Exception as e:            # noqa: BLE001
-            print(f"[bench] CUDA graph capture unavailable ({type(e).__name__}: {e}); timing eager launches", file=sys.stderr)
-            graph = None
-            barrier()
+    if pipelined:
+        # ---- pass B (N > 1): two packets, two streams -- frame t+1's broadcast and frame t's counter
+        # all-gather overlap the kernels (sharded.py: pipeline_*).  Timed first-to-last on the compute
+        # stream; no L2 flush: a GPU's per-frame working set (volume words + skin cache, > 300 MB at
+        # N = 8) exceeds the 126 MB L2.
+        sampler = ClockSampler(device.index or 0)
+        for i in range(3):                                     # warm the second packet / stream / NCCL channels
+            sf.pipeline_begin(H, W, packets[0] if rank == 0 else None)
+            sf.pipeline_step(packets[1] if rank == 0 else None)
+            sf.pipeline_step(last=True)
+            sf.pipeline_end()
+        def run_pipeline():
+            sf.pipeline_begin(H, W, packets[0] if rank == 0 else None)
+            for i in range(K):
+                nxt = packets[(i + 1) % n_frames] if rank == 0 else None
+                sf.pipeline_step(nxt, last=(i == K - 1))
+            sf.pipeline_end()
 
-    # pass B: the timed K steps
-    evs = [(mk(), mk()) for _ in range(K)]
-    sampler = ClockSampler(device.index or 0)
-    if rank == 0:
-        sampler.start()
-    barrier()
-    t_wall0 = time.perf_counter()
-    for i in range(K):
-        prep(i)
-        evs[i][0].record(stream)
+        # the K-step launch sequence (both streams, NCCL included) as one CUDA graph: at N = 8 a step is
+        # ~0.1 ms on the device, less than Python needs to enqueue its ~10 launches
+        if not args.no_graph:
+            try:
+                g_ = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g_):
+                    run_pipeline()
+                graph = g_
+                graph.replay()
+                barrier()
+            except Exception as e:            # noqa: BLE001
+                print(f"[bench] CUDA graph capture unavailable ({type(e).__name__}: {e}); timing eager launches", file=sys.stderr)
+                graph = None
+                barrier()
+        if rank == 0:
+            sampler.start()
+        barrier()
+        e0, e1 = mk(), mk()
+        t_wall0 = time.perf_counter()
+        e0.record(stream)
         if graph is not None:
             graph.replay()
         else:
-            core()
-        evs[i][1].record(stream)
-    barrier()
-    t_wall = time.perf_counter() - t_wall0
-    clocks = sampler.stop() if rank == 0 else None
+            run_pipeline()
+        e1.record(stream)
+        barrier()
+        t_wall = time.perf_counter() - t_wall0
+        clocks = sampler.stop() if rank == 0 else None
+        step_ms_total = e0.elapsed_time(e1)
+        evs = [(None, None)] * K
+    else:
+        # the per-frame launch sequence is short and launch-bound: replay it as one CUDA graph
+        if not args.no_graph:
+            try:
+                g_ = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g_):
+                    core()
+                graph = g_
+                prep(0); graph.replay()
+                barrier()
+            except Exception as e:            # noqa: BLE001
+                print(f"[bench] CUDA graph capture unavailable ({type(e).__name__}: {e}); timing eager launches", file=sys.stderr)
+                graph = None
+                barrier()
+
+        # pass B: the timed K steps
+        evs = [(mk(), mk()) for _ in range(K)]
+        sampler = ClockSampler(device.index or 0)
+        if rank == 0:
+            sampler.start()
+        barrier()
+        t_wall0 = time.perf_counter()
+        for i in range(K):
+            prep(i)
+            evs[i][0].record(stream)
+            if graph is not None:
+                graph.replay()
+            else:
+                core()
+            evs[i][1].record(stream)
+        barrier()
+        t_wall = time.perf_counter() - t_wall0
+        clocks = sampler.stop() if rank == 0 else None
+        step_ms_total = sum(a.elapsed_time(b) for a, b in evs)
     evs = [(a_, b_, c_, d_) for (a_, b_), (c_, d_) in zip(evs, kevs)]
-    step_ms = sum(a.elapsed_time(b) for a, b, _, _ in evs)
+    step_ms = step_ms_total
     kern_ms = sum(c.elapsed_time(d) for _, _, c, d in evs)
     tot = torch.tensor([step_ms, kern_ms], dtype=torch.float64, device=device)
     cnt = stats_acc.clone()
@@ -324,7 +381,7 @@ def bench_workload(name, args, rank, world, device, with_e2e=True):
     local_upd = float(stats_acc[_capi.STAT_UPDATED]) / K
     res = dict(workload=w, ms_per_step=step_ms, kernel_ms=kern_ms, updated=upd, skin_valid=valid, bricks=bricks,
                value=upd / (step_ms * 1e-3), wall_ms_per_step=t_wall * 1e3 / K, clocks=clocks,
-               local_updated=local_upd, launches_per_step=3, graph=graph is not None)   # node transforms, brick cull, fused kernel
+               local_updated=local_upd, launches_per_step=3, graph=graph is not None, pipelined=pipelined)   # node transforms, brick cull, fused kernel
     # roofline of the fused kernel on this rank's shard (rank 0 reports its own shard)
     alg_bytes = 24.0 * local_upd + 8.0 * H * W + 60.0 * w.M
     res["alg_bytes"] = alg_bytes
@@ -443,7 +500,7 @@ def main():
             "metric": METRIC, "value": main_res["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": main_res["ms_per_step"], "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32 (f64 projection/TSDF average)", "data": "synthetic",
-            "config": workload_config(w, world),
+            "config": workload_config(w, world, main_res.get("pipelined", False)),
             "voxels": int(np.prod(w.dims)), "updated_per_frame": main_res["updated"],
             "skin_valid_per_frame": main_res["skin_valid"], "bricks_per_frame": main_res["bricks"],
             "voxels_visited_per_s": float(np.prod(w.dims)) / (main_res["ms_per_step"] * 1e-3),

@@ -131,6 +131,69 @@ class ShardedFusion:
         dist.all_gather_into_tensor(out, stats.contiguous().view(-1), group=self.group)
         return out.view(self.world, N_STATS)
 
+    # -- per frame, pipelined ----------------------------------------------------------------------
+    # Two packets, two streams (SURVEY.md 8e "scaling risk"): while the shard integrates frame t the
+    # next frame's packet is already being broadcast, and the counters of frame t are gathered behind
+    # its kernel.  Order on the communication stream:
+    #     bcast(t+1) | wait kernel(t) | all-gather(t) | bcast(t+2) | ...
+    # so bcast(t+2) overwrites packet t%2 only after kernel(t) has read it, and overlaps kernel(t+1).
+    # Rank 0 hands over frame t+1 (a device-resident packet, e.g. what fill_packet staged) when it
+    # submits frame t: one frame of look-ahead.
+    def pipeline_setup(self, H, W):
+        """Allocates the second packet, the communication stream and the events (once; not capturable)."""
+        self._ensure_packet(H, W)
+        dev = self.device
+        if getattr(self, "_pbuf", None) is not None and self._pbuf[0] is self.buf:
+            return
+        self._pbuf = [self.buf, self.packet.alloc(dev)]
+        self._pviews = [self.views, self.packet.views(self._pbuf[1])]
+        self._pstats = [torch.zeros(N_STATS, dtype=torch.int64, device=dev) for _ in range(2)]
+        self._pgath = [torch.zeros(self.world * N_STATS, dtype=torch.int64, device=dev) for _ in range(2)]
+        self._comm = torch.cuda.Stream(device=dev)
+        self._ev_bcast = [torch.cuda.Event() for _ in range(2)]
+        self._ev_done = [torch.cuda.Event() for _ in range(2)]
+
+    def pipeline_begin(self, H, W, first_packet=None):
+        self.pipeline_setup(H, W)
+        dev = self.device
+        self._comm.wait_stream(torch.cuda.current_stream(dev))
+        self._pipe_t = 0
+        self._bcast(0, first_packet)
+
+    def _bcast(self, t, packet):
+        j = t % 2
+        with torch.cuda.stream(self._comm):
+            if self.rank == 0 and packet is not None and packet.data_ptr() != self._pbuf[j].data_ptr():
+                self._pbuf[j].copy_(packet, non_blocking=True)
+            if self.world > 1:
+                dist.broadcast(self._pbuf[j], src=0, group=self.group)
+            self._ev_bcast[j].record(self._comm)
+
+    def pipeline_step(self, next_packet=None, last=False, obs_weight=1.0):
+        """Integrate frame t (its packet was broadcast by the previous call) while frame t+1's packet
+        (`next_packet` on rank 0; ignored when `last`) is broadcast.  Returns the (world, N_STATS) counter
+        tensor of frame t; it is valid once the communication stream has run (pipeline_end() or an event)."""
+        t, j = self._pipe_t, self._pipe_t % 2
+        comp = torch.cuda.current_stream(self.device)
+        if not last:
+            self._bcast(t + 1, next_packet)
+        comp.wait_event(self._ev_bcast[j])
+        v = self._pviews[j]
+        self.be.set_transforms(v["R"], v["T"])
+        st = self.be.integrate(v["depth"], v["colour"], False, obs_weight, stats=self._pstats[j])
+        self._ev_done[j].record(comp)
+        with torch.cuda.stream(self._comm):
+            self._comm.wait_event(self._ev_done[j])
+            if self.world > 1:
+                dist.all_gather_into_tensor(self._pgath[j], st, group=self.group)
+            else:
+                self._pgath[j].copy_(st)
+        self._pipe_t += 1
+        return self._pgath[j].view(self.world, N_STATS)
+
+    def pipeline_end(self):
+        torch.cuda.current_stream(self.device).wait_stream(self._comm)
+
     # -- output (not per frame) ------------------------------------------------------------------
     def gather_volume(self):
         """Full (Dx,Dy,Dz) volumes on rank 0 (None elsewhere): undoes the dealt-block plane mapping."""
@@ -177,12 +240,13 @@ class CudaShard:
         self.vol.update(im, getattr(self.vol, "frame_id", -self.vol.fopt.skip_rate) + self.vol.fopt.skip_rate)
         return self.vol._color_im_dev, self.vol._depth_im_dev
 
-    def integrate(self, depth, colour, identity_warp, obs_weight):
+    def integrate(self, depth, colour, identity_warp, obs_weight, stats=None):
         c = self._capi
         H, W = depth.shape
+        st = self.stats if stats is None else stats
         c.check(self.lib.ofx_integrate(self.vol._h, c.ptr(depth), c.ptr(colour), H, W, self.vol._intr4, float(obs_weight),
-                                       int(identity_warp), c.ptr(self.stats), self._s()))
-        return self.stats
+                                       int(identity_warp), c.ptr(st), self._s()))
+        return st
 
     def get_volume(self):
         return self.vol.get_volume()
