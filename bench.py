@@ -476,7 +476,11 @@ def main():
     torch.cuda.set_device(device)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=device)
+        try:        # NCCL's kernels on a high-priority stream: they are tiny and must not queue behind the fused kernel
+            opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)
+            dist.init_process_group("nccl", device_id=device, pg_options=opts)
+        except Exception:      # noqa: BLE001
+            dist.init_process_group("nccl", device_id=device)
     from occlusionfusion_b200.synthetic import Workload
 
     main_res = bench_workload(args.workload, args, rank, world, device)

@@ -122,6 +122,14 @@ int ofx_check_visibility(const float *points, int64_t n, const float *depth, int
                          const float *intr_host, double trunc_margin, uint8_t *valid,
                          double *depth_diff, void *stream);
 
+/* ---- multi-GPU plumbing ------------------------------------------------------------------------ */
+/* Copies `bytes` (a multiple of 16, both pointers 16-byte aligned) from `src` to `dst` with `ctas`
+ * thread blocks.  `src` may be a PEER pointer (another GPU's buffer mapped into this process through
+ * NVLink / NVSwitch, e.g. torch symmetric memory): every rank pulls the per-frame packet
+ * [R | T | colour | depth] from the rank that received the camera frame.  New in this library (the
+ * reference has no multi-device path); replaces the NCCL broadcast on the per-frame path. */
+int ofx_peer_copy(void *dst, const void *src, int64_t bytes, int32_t ctas, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

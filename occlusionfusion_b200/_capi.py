@@ -21,7 +21,7 @@ SYMBOLS = [
     "ofx_abi_version", "ofx_last_error", "ofx_volume_create", "ofx_volume_destroy", "ofx_volume_reset",
     "ofx_volume_num_voxels", "ofx_set_graph", "ofx_set_transforms", "ofx_integrate",
     "ofx_volume_world_points", "ofx_volume_skin", "ofx_volume_deform", "ofx_pack_frame", "ofx_skin",
-    "ofx_warp_points", "ofx_check_visibility",
+    "ofx_warp_points", "ofx_check_visibility", "ofx_peer_copy",
 ]
 
 
@@ -66,6 +66,7 @@ def load():
     lib.ofx_pack_frame.argtypes = [vp, i32, i32, i32, vp, vp, vp]
     lib.ofx_skin.argtypes = [vp, i64, vp, i32, f64, i32, vp, vp, vp, vp]
     lib.ofx_warp_points.argtypes = [vp, i64, vp, vp, vp, i32, vp, vp, vp, vp]
+    lib.ofx_peer_copy.argtypes = [vp, vp, i64, i32, vp]
     lib.ofx_check_visibility.argtypes = [vp, i64, vp, i32, i32, C.POINTER(C.c_float), f64, vp, vp, vp]
     for name in SYMBOLS:
         getattr(lib, name)      # AttributeError here = the .so is older than include/ofx.h

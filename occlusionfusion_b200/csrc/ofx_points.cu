@@ -209,3 +209,29 @@ extern "C" int ofx_check_visibility(const float *points, int64_t n, const float 
     OFX_LAUNCH_CHECK();
     return 0;
 }
+
+// ---- peer pull copy (multi-GPU frame packet) ---------------------------------------------------------
+namespace ofx {
+__global__ void __launch_bounds__(256) peer_copy_kernel(uint4 *__restrict__ dst, const uint4 *__restrict__ src, int64_t n16)
+{
+    // four independent 16-byte loads in flight per thread: NVLink round trips are ~2 us
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i + 3 * stride < n16; i += 4 * stride) {
+        const uint4 a = src[i], b = src[i + stride], c = src[i + 2 * stride], d = src[i + 3 * stride];
+        dst[i] = a; dst[i + stride] = b; dst[i + 2 * stride] = c; dst[i + 3 * stride] = d;
+    }
+    for (; i < n16; i += stride) dst[i] = src[i];
+}
+}  // namespace ofx
+
+extern "C" int ofx_peer_copy(void *dst, const void *src, int64_t bytes, int32_t ctas, void *stream)
+{
+    OFX_REQUIRE(dst && src && bytes >= 0 && bytes % 16 == 0, "ofx_peer_copy: bad arguments");
+    OFX_REQUIRE((((uintptr_t)dst | (uintptr_t)src) & 15) == 0, "ofx_peer_copy: pointers must be 16-byte aligned");
+    if (bytes == 0) return 0;
+    if (ctas < 1) ctas = 32;
+    ofx::peer_copy_kernel<<<ctas, 256, 0, (cudaStream_t)stream>>>((uint4 *)dst, (const uint4 *)src, bytes / 16);
+    OFX_LAUNCH_CHECK();
+    return 0;
+}

@@ -299,9 +299,9 @@ def test_pipelined_driver_equals_sequential(oracle):
             sf.pipeline_begin(w.H, w.W, packets[0])
             outs = [sf.pipeline_step(packets[i + 1] if i + 1 < len(packets) else None, last=(i + 1 == len(packets)))
                     for i in range(len(packets))]
-            sf.pipeline_end()
+            final = sf.pipeline_end()
             torch.cuda.synchronize()
-            got = [outs[-2].clone(), outs[-1].clone()]        # the two counter buffers hold the last two frames
+            got = [outs[-1].clone(), final.clone()]           # a step returns the counters of the frame before it
         vols.append(vol.get_volume())
         counters.append([g.cpu().numpy() for g in got])
     for a, b in zip(vols[0], vols[1]):
