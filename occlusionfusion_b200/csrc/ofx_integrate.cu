@@ -107,21 +107,26 @@ constexpr int CULL_THREADS = 256;
 constexpr int CULL_BRICKS_PER_CTA = CULL_THREADS / CULL_LANES;
 
 __global__ void __launch_bounds__(CULL_THREADS)
-brick_cull_kernel(VolumeGeom g, GraphArgs ga, const float4 *__restrict__ brick_box, int n_active, Camera cam, int *__restrict__ live,
+brick_cull_kernel(GraphArgs ga, const int4 *__restrict__ active_desc, int n_active, Camera cam, int *__restrict__ live,
                   int *__restrict__ n_live, unsigned long long *__restrict__ stats)
 {
     __shared__ int s_mask[CULL_THREADS / 32];
     __shared__ int s_base;
     const int slot = threadIdx.x / CULL_LANES, sub = threadIdx.x % CULL_LANES;
     const int idx = blockIdx.x * CULL_BRICKS_PER_CTA + slot;
-    int b = -1, n_used = 0, o = 0;
+    // the frame's counters start from zero here (nothing else writes them before the fused kernel)
+    if (blockIdx.x == 0 && threadIdx.x < OFX_N_STATS) stats[threadIdx.x] = 0ull;
+    int n_used = 0, o = 0;
+    int4 d0 = make_int4(0, 0, 0, 0), d1 = make_int4(0, 0, -1, 0);
     float4 box = make_float4(0.f, 0.f, 0.f, 0.f);
     if (idx < n_active) {
-        b = __ldg(ga.active + idx);
-        n_used = __ldg(ga.cnt + b);
-        o = __ldg(ga.off + b);
-        box = __ldg(brick_box + b);
+        const int4 *d = active_desc + ACTIVE_DESC_VEC * idx;
+        d0 = __ldg(d); d1 = __ldg(d + 1);
+        const int4 bx = __ldg(d + 2);
+        box = make_float4(__int_as_float(bx.x), __int_as_float(bx.y), __int_as_float(bx.z), __int_as_float(bx.w));
+        n_used = d0.w; o = d1.x;
     }
+    const int b = d1.z;
     float u_lo = 3.0e38f, u_hi = -3.0e38f, v_lo = 3.0e38f, v_hi = -3.0e38f;
     int unbounded = 0;
     for (int i = sub; i < n_used; i += CULL_LANES) {
@@ -153,7 +158,6 @@ brick_cull_kernel(VolumeGeom g, GraphArgs ga, const float4 *__restrict__ brick_b
         int tot = 0;
         for (int w = 0; w < CULL_THREADS / 32; ++w) tot += __popc((unsigned)s_mask[w]);
         s_base = tot ? atomicAdd(n_live, tot) : 0;
-        if (tot) atomicAdd(stats + OFX_STAT_BRICKS, (unsigned long long)tot);
     }
     __syncthreads();
     if (keep && sub == 0) {
@@ -162,10 +166,9 @@ brick_cull_kernel(VolumeGeom g, GraphArgs ga, const float4 *__restrict__ brick_b
         for (int k = 0; k < w; ++k) rank += __popc((unsigned)s_mask[k]);
         rank += __popc((unsigned)s_mask[w] & ((1u << (threadIdx.x & 31)) - 1u));
         // everything the fused kernel's producer needs about the brick, in one 32-byte record
-        const BrickCoord bc = brick_coord(g, b);
         int4 *d = reinterpret_cast<int4 *>(live) + 2 * (s_base + rank);
-        d[0] = make_int4(bc.lx0, bc.iy0, bc.iz0, n_used);
-        d[1] = make_int4(o, __ldg(ga.brick_slot + b), b, 0);
+        d[0] = d0;
+        d[1] = d1;
     }
 }
 
@@ -211,8 +214,8 @@ struct SlotInfo {
 template <int K, bool VEC, bool OBS32>
 __global__ void __launch_bounds__(PERSISTENT_THREADS, K <= 4 ? OFX_MIN_CTAS : 3)
 fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ weight, float *__restrict__ colour,
-                        GraphArgs ga, FrameArgs fa, const int *__restrict__ live, const int *__restrict__ n_live_ptr,
-                        int *__restrict__ work_counter, unsigned long long *__restrict__ stats)
+                        GraphArgs ga, FrameArgs fa, const int *__restrict__ live, int *counters,
+                        unsigned long long *__restrict__ stats)
 {
     // dynamic shared memory: [N_SLOTS skin-cache slots | ring of node transforms]
     constexpr int KP = K <= 4 ? 4 : 8;
@@ -236,7 +239,7 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
 #if OFX_TIMING
         unsigned long long dbg_a = 0, dbg_b = 0, dbg_n = 0;
 #endif
-        const int n_live = *n_live_ptr;
+        const int n_live = *reinterpret_cast<volatile int *>(counters);          // counters: {n_live, work, retired CTAs}
         int idx = blockIdx.x;
         int rel = 0;                  // iterations [0, rel) have been released by the consumers
         int head = 0, tail = 0;       // ring: next free record / first record of the oldest unreleased brick
@@ -312,7 +315,7 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
             }
 #endif
             int f = 0;
-            if (lane == 0) f = atomicAdd(work_counter, 1);
+            if (lane == 0) f = atomicAdd(counters + 1, 1);
             idx = (int)gridDim.x + __shfl_sync(0xffffffffu, f, 0);
         }
 #if OFX_TIMING
@@ -376,6 +379,14 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
         if (s_cnt[1]) atomicAdd(stats + OFX_STAT_SKIN_VALID, (unsigned long long)s_cnt[1]);
         const unsigned long long ws = ((unsigned long long)s_cnt[3] << 32) | s_cnt[2];
         if (ws) atomicAdd(stats + OFX_STAT_WEIGHT_SUM, ws);
+        // the last CTA to retire leaves the launch counters at zero for the next frame's cull (every
+        // producer has read n_live and drawn its last work item before its consumers get here)
+        const int n_live = *reinterpret_cast<volatile int *>(counters);
+        __threadfence();
+        if (atomicAdd(counters + 2, 1) == (int)gridDim.x - 1) {
+            atomicAdd(stats + OFX_STAT_BRICKS, (unsigned long long)n_live);
+            counters[0] = 0; counters[1] = 0; counters[2] = 0;
+        }
     }
 }
 
@@ -425,19 +436,23 @@ static int launch_persistent_t(ofx_volume *v, const FrameArgs &fa, unsigned long
                                                                PERSISTENT_THREADS, smem));
         if (blocks_per_sm < 1) blocks_per_sm = 1;
     }
-    if (v->n_active <= 0) return 0;
-    int *n_live = v->scratch + 8, *work = v->scratch + 9;
-    OFX_CUDA(cudaMemsetAsync(n_live, 0, 2 * sizeof(int), s));
+    if (v->n_active <= 0) {
+        OFX_CUDA(cudaMemsetAsync(stats, 0, OFX_N_STATS * sizeof(uint64_t), s));
+        return 0;
+    }
+    int *counters = v->scratch + 8;    // {n_live, work, retired CTAs}: zero between launches (the fused kernel resets them)
+    if (v->counters_dirty) OFX_CUDA(cudaMemsetAsync(counters, 0, 3 * sizeof(int), s));
+    v->counters_dirty = true;
     const GraphArgs ga = graph_args(v);
     brick_cull_kernel<<<(v->n_active + CULL_BRICKS_PER_CTA - 1) / CULL_BRICKS_PER_CTA, CULL_THREADS, 0, s>>>(
-        v->geom, ga, v->brick_box, v->n_active, fa.cam, v->live, n_live, stats);
+        ga, v->active_desc, v->n_active, fa.cam, v->live, counters, stats);
     OFX_LAUNCH_CHECK();
     const int cap = sm_count() * blocks_per_sm;       // persistent grid: a multiple of the SM count
     const int grid = v->n_active < cap ? v->n_active : cap;   // CTAs beyond the live count retire at once
     fused_warped_persistent<K, VEC, OBS32><<<grid, PERSISTENT_THREADS, smem, s>>>(v->geom, v->desc.tsdf, v->desc.weight,
-                                                                          v->desc.colour, ga, fa, v->live, n_live, work,
-                                                                          stats);
+                                                                          v->desc.colour, ga, fa, v->live, counters, stats);
     OFX_LAUNCH_CHECK();
+    v->counters_dirty = false;
     return 0;
 }
 
@@ -457,9 +472,9 @@ extern "C" int ofx_integrate(ofx_volume *v, const float *depth, const float *col
     OFX_REQUIRE(v && depth && colour_packed && intr_host && H > 0 && W > 0, "ofx_integrate: bad arguments");
     cudaStream_t s = (cudaStream_t)stream;
     unsigned long long *st = reinterpret_cast<unsigned long long *>(stats ? stats : v->stats_scratch);
-    OFX_CUDA(cudaMemsetAsync(st, 0, OFX_N_STATS * sizeof(uint64_t), s));
     const FrameArgs fa = make_frame_args(depth, colour_packed, intr_host, H, W, v->desc.trunc_margin, obs_weight);
     if (identity_warp) {
+        OFX_CUDA(cudaMemsetAsync(st, 0, OFX_N_STATS * sizeof(uint64_t), s));
         GraphArgs ga{};
         return launch_brick<4, MODE_IDENTITY>(v, v->n_bricks, ga, fa, st, nullptr, nullptr, s);
     }

@@ -319,6 +319,22 @@ __global__ void __launch_bounds__(BRICK_THREADS) skin_brick_kernel(VolumeGeom g,
     (void)any_valid;
 }
 
+// One record per active brick with everything the per-frame cull needs, contiguous in the order of the
+// active list: {lx0, iy0, iz0, n_used | list offset, cache slot, brick, 0 | centre + bounding radius}.
+__global__ void active_desc_kernel(VolumeGeom g, const int *__restrict__ active, int n_active, const int *__restrict__ cnt,
+                                   const int *__restrict__ off, const int *__restrict__ brick_slot,
+                                   const float4 *__restrict__ brick_box, int4 *__restrict__ desc)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_active) return;
+    const int b = active[i];
+    const BrickCoord bc = brick_coord(g, b);
+    const float4 box = brick_box[b];
+    desc[ACTIVE_DESC_VEC * i] = make_int4(bc.lx0, bc.iy0, bc.iz0, cnt[b]);
+    desc[ACTIVE_DESC_VEC * i + 1] = make_int4(off[b], brick_slot[b], b, 0);
+    desc[ACTIVE_DESC_VEC * i + 2] = make_int4(__float_as_int(box.x), __float_as_int(box.y), __float_as_int(box.z), __float_as_int(box.w));
+}
+
 }  // namespace ofx
 
 using namespace ofx;
@@ -410,6 +426,12 @@ extern "C" int ofx_set_graph(ofx_volume *v, const float *nodes, int32_t M, doubl
     OFX_REQUIRE(res[2] == 0, "ofx_set_graph: a brick of %dx%dx%d voxels uses %d distinct anchor nodes (limit %d); "
                 "nodes are far denser than the voxel grid", BX, BY, BZ, res[2], MAX_BRICK_NODES);
     v->n_active = res[4];
+    if (v->n_active > 0) {
+        active_desc_kernel<<<(v->n_active + 255) / 256, 256, 0, s>>>(v->geom, v->active, v->n_active, v->brick_cnt, v->brick_off,
+                                                                   v->brick_slot, v->brick_box, v->active_desc);
+        OFX_LAUNCH_CHECK();
+    }
+    v->counters_dirty = false;       // scratch was cleared above
     v->graph_ready = true;
     return 0;
 }

@@ -118,9 +118,10 @@ extern "C" int ofx_volume_create(ofx_volume **out, const ofx_volume_desc *d)
     OFX_CUDA(cudaMalloc(&v->brick_radius, nb * sizeof(float)));
     OFX_CUDA(cudaMalloc(&v->active, nb * sizeof(int)));
     OFX_CUDA(cudaMalloc(&v->live, nb * LIVE_DESC_INTS * sizeof(int)));
+    OFX_CUDA(cudaMalloc(&v->active_desc, nb * ACTIVE_DESC_VEC * sizeof(int4)));
     OFX_CUDA(cudaMalloc(&v->brick_slot, nb * sizeof(int)));
     OFX_CUDA(cudaMalloc(&v->brick_box, nb * sizeof(float4)));
-    OFX_CUDA(cudaMalloc(&v->scratch, 16 * sizeof(int)));      // [0..5] set_graph results, [8] n_live, [9] brick work counter
+    OFX_CUDA(cudaMalloc(&v->scratch, 16 * sizeof(int)));      // [0..7] set_graph results, [8] n_live, [9] brick work counter, [10] retired CTAs
     OFX_CUDA(cudaMemset(v->scratch, 0, 16 * sizeof(int)));
     OFX_CUDA(cudaMalloc(&v->stats_scratch, OFX_N_STATS * sizeof(uint64_t)));
     *out = v;
@@ -133,7 +134,7 @@ extern "C" int ofx_volume_destroy(ofx_volume *v)
     cudaFree(v->tables); cudaFree(v->node_rec); cudaFree(v->cache); cudaFree(v->brick_slot); cudaFree(v->brick_cnt);
     cudaFree(v->brick_off); cudaFree(v->brick_radius); cudaFree(v->cand); cudaFree(v->brick_nodes);
     cudaFree(v->active); cudaFree(v->scratch); cudaFree(v->stats_scratch);
-    cudaFree(v->live); cudaFree(v->brick_box); cudaFree(v->depth_tiles);
+    cudaFree(v->live); cudaFree(v->active_desc); cudaFree(v->brick_box); cudaFree(v->depth_tiles);
     delete v;
     return 0;
 }
