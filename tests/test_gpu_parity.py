@@ -396,3 +396,81 @@ def test_full_size_256_properties():
     assert set(np.unique(wt1)) <= {0.0, 1.0, 2.0}
     assert t1.min() >= -1.0 and t1.max() <= 1.0
     assert np.all(c1 < 2 ** 24) and np.array_equal(c1, np.floor(c1))
+
+
+def _axis_tables(w, oracle):
+    """vox2world (tsdf.py:345-348) is separable: one oracle call per axis instead of the full slab."""
+    Dx, Dy, Dz = w.dims
+    px = oracle.vox2world(w.origin, w.voxel_size, (Dx, 1, 1))[:, 0]
+    py = oracle.vox2world(w.origin, w.voxel_size, (1, Dy, 1))[:, 1]
+    pz = oracle.vox2world(w.origin, w.voxel_size, (1, 1, Dz))[:, 2]
+    return px, py, pz
+
+
+@pytest.mark.parametrize("name,n_frames,obs_weight", [("c2-dense", 3, 1.0), ("c2", 4, 1.0), ("c4", 3, 2.0)])
+def test_full_size_sampled_parity(name, n_frames, obs_weight, oracle):
+    """BASELINE configs at FULL size (512^3 / K=4 as benchmarked; 1024^3, 1280x720, ~4k nodes, K=8): the CUDA path
+    integrates the whole volume; a seeded sample of voxels (uniform + concentrated around the surface + whole
+    z-rows) is replayed through the oracle's point operators (skin -> warp -> integrate) and must be bit-identical
+    after every frame."""
+    import torch
+    from occlusionfusion_b200 import WarpField
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload(name)
+    Dx, Dy, Dz = w.dims
+    vol = _mk_volume(w)
+    wf = WarpField(w.graph(), vol, None)
+    wf.graph_neighbours = w.K
+    vol.warpfield = wf
+
+    rng = np.random.default_rng(1234)
+    n_uni = 120_000
+    ijk = [np.stack([rng.integers(0, Dx, n_uni), rng.integers(0, Dy, n_uni), rng.integers(0, Dz, n_uni)], 1)]
+    if w.scene == "band":
+        # voxels around the camera-facing surface of the sphere (where the truncation band and the skin band are)
+        n_s = 200_000
+        d = rng.normal(size=(n_s, 3))
+        d /= np.linalg.norm(d, axis=1, keepdims=True)
+        d[:, 2] = -np.abs(d[:, 2])
+        p = w.centre + (w.radius + rng.uniform(-0.08, 0.08, (n_s, 1))) * d
+        q = np.rint((p - w.origin.astype(np.float64)) / w.voxel_size).astype(np.int64)
+        ijk.append(q[((q >= 0) & (q < np.array(w.dims))).all(1)])
+    rows = np.stack([rng.integers(0, Dx, 48), rng.integers(0, Dy, 48)], 1)          # whole z-rows: every lane of a brick row
+    ijk.append(np.concatenate([np.concatenate([np.repeat(r[None], Dz, 0), np.arange(Dz)[:, None]], 1) for r in rows]))
+    ijk = np.concatenate(ijk)
+    flat = np.unique((ijk[:, 0] * Dy + ijk[:, 1]) * Dz + ijk[:, 2])
+    ix, iy, iz = flat // (Dy * Dz), (flat // Dz) % Dy, flat % Dz
+    px, py, pz = _axis_tables(w, oracle)
+    pts = np.stack([px[ix], py[iy], pz[iz]], 1).astype(np.float32)
+    flat_t = torch.from_numpy(flat).to(vol.device)
+
+    a, wts, valid = oracle.skin(pts, w.nodes, w.K, w.coverage)
+    t = np.ones(len(flat), np.float32)
+    wt = np.zeros(len(flat), np.float32)
+    c = np.zeros(len(flat), np.float32)
+    total_updated = 0
+    for f in range(n_frames):
+        im = w.frame(f)
+        color_im, depth_im = oracle.pack_frame(im)
+        if f == 0:
+            cam_pts, ok = pts, np.ones(len(pts), bool)
+        else:
+            est = w.estimate(f)
+            wf.update_transformations(est)
+            cam_pts, ok = oracle.warp(pts, a, wts, valid, est["node_rotations"], wf.translations), valid
+        vol.integrate({"im": im, "id": f}, obs_weight)
+        oracle.integrate(t, wt, c, cam_pts, ok, depth_im, color_im, w.intr, w.trunc, obs_weight)
+        st = vol.last_stats()
+        total_updated += st["updated"]
+        g_t = vol._tsdf_vol.reshape(-1)[flat_t].cpu().numpy()
+        g_w = vol._weight_vol.reshape(-1)[flat_t].cpu().numpy()
+        g_c = vol._color_vol.reshape(-1)[flat_t].cpu().numpy()
+        assert np.array_equal(g_w, wt), f"frame {f}: weights differ at {(g_w != wt).sum()} of {len(flat)} sampled voxels"
+        assert np.array_equal(g_c, c), f"frame {f}: colours differ at {(g_c != c).sum()} sampled voxels"
+        assert np.array_equal(g_t, t), f"frame {f}: tsdf differs, max {np.abs(g_t - t).max()}"
+    # the sample must have exercised the path: updated voxels, repeated observations, a real surface band
+    assert (wt > 0).sum() > 20_000 and wt.max() == n_frames * obs_weight
+    if w.scene == "band":
+        assert ((t < 1.0) & (t > -1.0)).sum() > 1000 and 0 < valid.sum() < len(valid)
+    # whole-volume counter identity at full size: every update adds obs_weight to exactly one voxel
+    assert vol._weight_vol.sum(dtype=torch.float64).item() == obs_weight * total_updated
