@@ -93,6 +93,17 @@ int ofx_integrate(ofx_volume *v, const float *depth, const float *colour_packed,
                   int32_t W, const float *intr_host, double obs_weight, int32_t identity_warp,
                   uint64_t *stats, void *stream);
 
+/* Optional look-ahead for frame streams (new in this library; the reference integrates strictly frame by frame):
+ * stages the NEXT warped frame's node transforms (as ofx_set_transforms) and its list of bricks inside the
+ * camera frustum in a second per-frame set, so that it may run on another stream while the current frame
+ * integrates.  The next non-identity ofx_integrate (same H, W, intr_host) switches to that set and launches only
+ * the fused kernel.  It writes the set that the most recently ISSUED ofx_integrate does not use, so the host calls
+ * go integrate(t), prepare(t+1), integrate(t+1), ...; on the device the caller orders prepare(t+1) after
+ * integrate(t-1) has finished and integrate(t+1) after prepare(t+1) (events).  Results are identical to
+ * ofx_set_transforms + ofx_integrate. */
+int ofx_prepare_frame(ofx_volume *v, const float *rotations, const float *translations, int32_t H,
+                      int32_t W, const float *intr_host, void *stream);
+
 /* Materialise what the reference keeps on the host, on request only (vis / tests):
  *   world_pts (n,3)                                   tsdf.py:307
  *   world_anchors (n,K) i32, world_weights (n,K) f32, world_valid_pts (n,) u8   warpfield.py:131-141

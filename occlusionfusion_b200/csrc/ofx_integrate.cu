@@ -102,20 +102,26 @@ fused_brick_kernel(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ w
 // box of the warped brick (ofx_brick.cuh: ball_pixbox) and drop the bricks that cannot reach the
 // image.  Survivors are appended to live[] (one atomic per CTA of 32 bricks); the fused kernel
 // then sees only bricks that do arithmetic, so its dynamic scheduler balances equal-cost units.
-constexpr int CULL_LANES = 8;
-constexpr int CULL_THREADS = 256;
+#ifndef OFX_CULL_LANES
+#define OFX_CULL_LANES 4
+#endif
+#ifndef OFX_CULL_THREADS
+#define OFX_CULL_THREADS 128
+#endif
+constexpr int CULL_LANES = OFX_CULL_LANES;
+constexpr int CULL_THREADS = OFX_CULL_THREADS;
 constexpr int CULL_BRICKS_PER_CTA = CULL_THREADS / CULL_LANES;
 
 __global__ void __launch_bounds__(CULL_THREADS)
 brick_cull_kernel(GraphArgs ga, const int4 *__restrict__ active_desc, int n_active, Camera cam, int *__restrict__ live,
-                  int *__restrict__ n_live, unsigned long long *__restrict__ stats)
+                  int *__restrict__ n_live, unsigned long long *__restrict__ acc)
 {
     __shared__ int s_mask[CULL_THREADS / 32];
     __shared__ int s_base;
     const int slot = threadIdx.x / CULL_LANES, sub = threadIdx.x % CULL_LANES;
     const int idx = blockIdx.x * CULL_BRICKS_PER_CTA + slot;
-    // the frame's counters start from zero here (nothing else writes them before the fused kernel)
-    if (blockIdx.x == 0 && threadIdx.x < OFX_N_STATS) stats[threadIdx.x] = 0ull;
+    // the frame's counter accumulators start from zero here (nothing else writes them before the fused kernel)
+    if (blockIdx.x == 0 && threadIdx.x < OFX_N_STATS) acc[threadIdx.x] = 0ull;
     int n_used = 0, o = 0;
     int4 d0 = make_int4(0, 0, 0, 0), d1 = make_int4(0, 0, -1, 0);
     float4 box = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -215,7 +221,7 @@ template <int K, bool VEC, bool OBS32>
 __global__ void __launch_bounds__(PERSISTENT_THREADS, K <= 4 ? OFX_MIN_CTAS : 3)
 fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ weight, float *__restrict__ colour,
                         GraphArgs ga, FrameArgs fa, const int *__restrict__ live, int *counters,
-                        unsigned long long *__restrict__ stats)
+                        unsigned long long *acc, unsigned long long *__restrict__ stats)
 {
     // dynamic shared memory: [N_SLOTS skin-cache slots | ring of node transforms]
     constexpr int KP = K <= 4 ? 4 : 8;
@@ -375,16 +381,21 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
 #endif
     named_bar_sync(1 + N_SLOTS, BRICK_THREADS);    // consumers only
     if (threadIdx.x == 0) {
-        if (s_cnt[0]) atomicAdd(stats + OFX_STAT_UPDATED, (unsigned long long)s_cnt[0]);
-        if (s_cnt[1]) atomicAdd(stats + OFX_STAT_SKIN_VALID, (unsigned long long)s_cnt[1]);
+        if (s_cnt[0]) atomicAdd(acc + OFX_STAT_UPDATED, (unsigned long long)s_cnt[0]);
+        if (s_cnt[1]) atomicAdd(acc + OFX_STAT_SKIN_VALID, (unsigned long long)s_cnt[1]);
         const unsigned long long ws = ((unsigned long long)s_cnt[3] << 32) | s_cnt[2];
-        if (ws) atomicAdd(stats + OFX_STAT_WEIGHT_SUM, ws);
-        // the last CTA to retire leaves the launch counters at zero for the next frame's cull (every
-        // producer has read n_live and drawn its last work item before its consumers get here)
+        if (ws) atomicAdd(acc + OFX_STAT_WEIGHT_SUM, ws);
+        // the last CTA to retire publishes the frame's counters and leaves the launch counters at zero for the
+        // next cull of this set (every producer has read n_live and drawn its last work item before its
+        // consumers get here)
         const int n_live = *reinterpret_cast<volatile int *>(counters);
         __threadfence();
         if (atomicAdd(counters + 2, 1) == (int)gridDim.x - 1) {
-            atomicAdd(stats + OFX_STAT_BRICKS, (unsigned long long)n_live);
+            __threadfence();
+            stats[OFX_STAT_UPDATED] = __ldcg(acc + OFX_STAT_UPDATED);
+            stats[OFX_STAT_SKIN_VALID] = __ldcg(acc + OFX_STAT_SKIN_VALID);
+            stats[OFX_STAT_WEIGHT_SUM] = __ldcg(acc + OFX_STAT_WEIGHT_SUM);
+            stats[OFX_STAT_BRICKS] = (unsigned long long)n_live;
             counters[0] = 0; counters[1] = 0; counters[2] = 0;
         }
     }
@@ -393,6 +404,8 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
 }  // namespace ofx
 
 using namespace ofx;
+
+int ofx_write_transforms(ofx_volume *v, float *table, const float *rotations, const float *translations, cudaStream_t s);
 
 static bool volume_vec_ok(const ofx_volume *v)
 {
@@ -425,8 +438,23 @@ static int launch_brick(ofx_volume *v, int grid, const GraphArgs &ga, const Fram
     return 0;
 }
 
+// The per-frame brick cull of one of the two frame sets (node transforms, live list, launch counters, counter
+// accumulators): on the integrating stream for the current set, or ahead of time for the other one (ofx_prepare_frame).
+static int launch_cull(ofx_volume *v, int set, const Camera &cam, cudaStream_t s)
+{
+    int *counters = v->scratch + 8 + 4 * set;    // {n_live, work, retired CTAs}: zero between launches (the fused kernel resets them)
+    if (v->counters_dirty[set]) OFX_CUDA(cudaMemsetAsync(counters, 0, 3 * sizeof(int), s));
+    v->counters_dirty[set] = true;
+    GraphArgs ga = graph_args(v);
+    ga.node_rec = v->node_rec_set[set];
+    brick_cull_kernel<<<(v->n_active + CULL_BRICKS_PER_CTA - 1) / CULL_BRICKS_PER_CTA, CULL_THREADS, 0, s>>>(
+        ga, v->active_desc, v->n_active, cam, v->live_set[set], counters, v->stats_acc + set * OFX_N_STATS);
+    OFX_LAUNCH_CHECK();
+    return 0;
+}
+
 template <int K, bool VEC, bool OBS32>
-static int launch_persistent_t(ofx_volume *v, const FrameArgs &fa, unsigned long long *stats, cudaStream_t s)
+static int launch_persistent_t(ofx_volume *v, const FrameArgs &fa, unsigned long long *stats, bool culled, cudaStream_t s)
 {
     static int blocks_per_sm = 0;      // per instantiation
     const size_t smem = (size_t)N_SLOTS * slot_bytes_of(K <= 4 ? 4 : 8) + RING_RECS * REC_BYTES + CONSUMER_WARPS * ROW_TAB_BYTES;
@@ -440,29 +468,52 @@ static int launch_persistent_t(ofx_volume *v, const FrameArgs &fa, unsigned long
         OFX_CUDA(cudaMemsetAsync(stats, 0, OFX_N_STATS * sizeof(uint64_t), s));
         return 0;
     }
-    int *counters = v->scratch + 8;    // {n_live, work, retired CTAs}: zero between launches (the fused kernel resets them)
-    if (v->counters_dirty) OFX_CUDA(cudaMemsetAsync(counters, 0, 3 * sizeof(int), s));
-    v->counters_dirty = true;
+    const int set = v->cur_set;
+    if (!culled)
+        if (int rc = launch_cull(v, set, fa.cam, s)) return rc;
+#ifdef OFX_CULL_ONLY     // timing builds only: the cull alone
+    return 0;
+#endif
     const GraphArgs ga = graph_args(v);
-    brick_cull_kernel<<<(v->n_active + CULL_BRICKS_PER_CTA - 1) / CULL_BRICKS_PER_CTA, CULL_THREADS, 0, s>>>(
-        ga, v->active_desc, v->n_active, fa.cam, v->live, counters, stats);
-    OFX_LAUNCH_CHECK();
     const int cap = sm_count() * blocks_per_sm;       // persistent grid: a multiple of the SM count
     const int grid = v->n_active < cap ? v->n_active : cap;   // CTAs beyond the live count retire at once
-    fused_warped_persistent<K, VEC, OBS32><<<grid, PERSISTENT_THREADS, smem, s>>>(v->geom, v->desc.tsdf, v->desc.weight,
-                                                                          v->desc.colour, ga, fa, v->live, counters, stats);
+    fused_warped_persistent<K, VEC, OBS32><<<grid, PERSISTENT_THREADS, smem, s>>>(
+        v->geom, v->desc.tsdf, v->desc.weight, v->desc.colour, ga, fa, v->live, v->scratch + 8 + 4 * set,
+        v->stats_acc + set * OFX_N_STATS, stats);
     OFX_LAUNCH_CHECK();
-    v->counters_dirty = false;
+    v->counters_dirty[set] = false;
     return 0;
 }
 
 template <int K>
-static int launch_persistent(ofx_volume *v, const FrameArgs &fa, unsigned long long *stats, cudaStream_t s)
+static int launch_persistent(ofx_volume *v, const FrameArgs &fa, unsigned long long *stats, bool culled, cudaStream_t s)
 {
     // the float32-observation-weight build is the hot one; the general one shares everything else
     if (fa.fu.obs_is_f32)
-        return volume_vec_ok(v) ? launch_persistent_t<K, true, true>(v, fa, stats, s) : launch_persistent_t<K, false, true>(v, fa, stats, s);
-    return volume_vec_ok(v) ? launch_persistent_t<K, true, false>(v, fa, stats, s) : launch_persistent_t<K, false, false>(v, fa, stats, s);
+        return volume_vec_ok(v) ? launch_persistent_t<K, true, true>(v, fa, stats, culled, s)
+                                : launch_persistent_t<K, false, true>(v, fa, stats, culled, s);
+    return volume_vec_ok(v) ? launch_persistent_t<K, true, false>(v, fa, stats, culled, s)
+                            : launch_persistent_t<K, false, false>(v, fa, stats, culled, s);
+}
+
+// The next frame's node transforms and live-brick list, into the frame set that is NOT in use: may run on another
+// stream while the current frame integrates (the caller orders it after the frame before the current one).
+extern "C" int ofx_prepare_frame(ofx_volume *v, const float *rotations, const float *translations, int32_t H, int32_t W,
+                                 const float *intr_host, void *stream)
+{
+    OFX_REQUIRE(v && rotations && translations && intr_host && H > 0 && W > 0, "ofx_prepare_frame: bad arguments");
+    OFX_REQUIRE(v->graph_ready, "ofx_prepare_frame: call ofx_set_graph first");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int set = 1 - v->cur_set;
+    v->prepared = false;
+    if (int rc = ofx_write_transforms(v, v->node_rec_set[set], rotations, translations, s)) return rc;
+    const Camera cam{intr_host[0], intr_host[1], intr_host[2], intr_host[3], H, W};
+    if (v->n_active > 0)
+        if (int rc = launch_cull(v, set, cam, s)) return rc;
+    for (int i = 0; i < 4; ++i) v->prepared_intr[i] = intr_host[i];
+    v->prepared_hw[0] = H; v->prepared_hw[1] = W;
+    v->prepared = true;
+    return 0;
 }
 
 extern "C" int ofx_integrate(ofx_volume *v, const float *depth, const float *colour_packed, int32_t H, int32_t W,
@@ -479,16 +530,29 @@ extern "C" int ofx_integrate(ofx_volume *v, const float *depth, const float *col
         return launch_brick<4, MODE_IDENTITY>(v, v->n_bricks, ga, fa, st, nullptr, nullptr, s);
     }
     OFX_REQUIRE(v->graph_ready, "ofx_integrate: warped frame before ofx_set_graph");
+    const bool culled = v->prepared;
+    if (culled) {
+        // ofx_prepare_frame has staged this frame in the other set: switch to it
+        const float *pi = v->prepared_intr;
+        OFX_REQUIRE(pi[0] == intr_host[0] && pi[1] == intr_host[1] && pi[2] == intr_host[2] && pi[3] == intr_host[3] &&
+                        v->prepared_hw[0] == H && v->prepared_hw[1] == W,
+                    "ofx_integrate: camera differs from the one given to ofx_prepare_frame");
+        v->cur_set ^= 1;
+        v->node_rec = v->node_rec_set[v->cur_set];
+        v->live = v->live_set[v->cur_set];
+        v->prepared = false;
+        v->transforms_ready = true;
+    }
     OFX_REQUIRE(v->transforms_ready, "ofx_integrate: warped frame before ofx_set_transforms");
     switch (v->K) {
-    case 1: return launch_persistent<1>(v, fa, st, s);
-    case 2: return launch_persistent<2>(v, fa, st, s);
-    case 3: return launch_persistent<3>(v, fa, st, s);
-    case 4: return launch_persistent<4>(v, fa, st, s);
-    case 5: return launch_persistent<5>(v, fa, st, s);
-    case 6: return launch_persistent<6>(v, fa, st, s);
-    case 7: return launch_persistent<7>(v, fa, st, s);
-    default: return launch_persistent<8>(v, fa, st, s);
+    case 1: return launch_persistent<1>(v, fa, st, culled, s);
+    case 2: return launch_persistent<2>(v, fa, st, culled, s);
+    case 3: return launch_persistent<3>(v, fa, st, culled, s);
+    case 4: return launch_persistent<4>(v, fa, st, culled, s);
+    case 5: return launch_persistent<5>(v, fa, st, culled, s);
+    case 6: return launch_persistent<6>(v, fa, st, culled, s);
+    case 7: return launch_persistent<7>(v, fa, st, culled, s);
+    default: return launch_persistent<8>(v, fa, st, culled, s);
     }
 }
 

@@ -431,7 +431,7 @@ extern "C" int ofx_set_graph(ofx_volume *v, const float *nodes, int32_t M, doubl
                                                                    v->brick_slot, v->brick_box, v->active_desc);
         OFX_LAUNCH_CHECK();
     }
-    v->counters_dirty = false;       // scratch was cleared above
+    v->counters_dirty[0] = v->counters_dirty[1] = false;       // scratch was cleared above
     v->graph_ready = true;
     return 0;
 }

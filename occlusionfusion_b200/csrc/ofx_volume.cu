@@ -117,11 +117,14 @@ extern "C" int ofx_volume_create(ofx_volume **out, const ofx_volume_desc *d)
     OFX_CUDA(cudaMalloc(&v->brick_off, nb * sizeof(int)));
     OFX_CUDA(cudaMalloc(&v->brick_radius, nb * sizeof(float)));
     OFX_CUDA(cudaMalloc(&v->active, nb * sizeof(int)));
-    OFX_CUDA(cudaMalloc(&v->live, nb * LIVE_DESC_INTS * sizeof(int)));
+    for (int k = 0; k < 2; ++k) OFX_CUDA(cudaMalloc(&v->live_set[k], nb * LIVE_DESC_INTS * sizeof(int)));
+    v->live = v->live_set[0];
+    OFX_CUDA(cudaMalloc(&v->stats_acc, 2 * OFX_N_STATS * sizeof(unsigned long long)));
+    OFX_CUDA(cudaMemset(v->stats_acc, 0, 2 * OFX_N_STATS * sizeof(unsigned long long)));
     OFX_CUDA(cudaMalloc(&v->active_desc, nb * ACTIVE_DESC_VEC * sizeof(int4)));
     OFX_CUDA(cudaMalloc(&v->brick_slot, nb * sizeof(int)));
     OFX_CUDA(cudaMalloc(&v->brick_box, nb * sizeof(float4)));
-    OFX_CUDA(cudaMalloc(&v->scratch, 16 * sizeof(int)));      // [0..7] set_graph results, [8] n_live, [9] brick work counter, [10] retired CTAs
+    OFX_CUDA(cudaMalloc(&v->scratch, 16 * sizeof(int)));      // [0..7] set_graph results, [8 + 4*set ..] n_live, brick work counter, retired CTAs
     OFX_CUDA(cudaMemset(v->scratch, 0, 16 * sizeof(int)));
     OFX_CUDA(cudaMalloc(&v->stats_scratch, OFX_N_STATS * sizeof(uint64_t)));
     *out = v;
@@ -131,10 +134,10 @@ extern "C" int ofx_volume_create(ofx_volume **out, const ofx_volume_desc *d)
 extern "C" int ofx_volume_destroy(ofx_volume *v)
 {
     if (!v) return 0;
-    cudaFree(v->tables); cudaFree(v->node_rec); cudaFree(v->cache); cudaFree(v->brick_slot); cudaFree(v->brick_cnt);
+    cudaFree(v->tables); cudaFree(v->node_rec_set[0]); cudaFree(v->cache); cudaFree(v->brick_slot); cudaFree(v->brick_cnt);
     cudaFree(v->brick_off); cudaFree(v->brick_radius); cudaFree(v->cand); cudaFree(v->brick_nodes);
     cudaFree(v->active); cudaFree(v->scratch); cudaFree(v->stats_scratch);
-    cudaFree(v->live); cudaFree(v->active_desc); cudaFree(v->brick_box); cudaFree(v->depth_tiles);
+    cudaFree(v->live_set[0]); cudaFree(v->live_set[1]); cudaFree(v->stats_acc); cudaFree(v->active_desc); cudaFree(v->brick_box); cudaFree(v->depth_tiles);
     delete v;
     return 0;
 }
@@ -166,13 +169,29 @@ extern "C" int ofx_volume_world_points(ofx_volume *v, float *out_pts, void *stre
 int ofx_upload_nodes(ofx_volume *v, const float *nodes, int M, cudaStream_t s)
 {
     if (M > v->node_rec_capacity) {
-        if (v->node_rec) OFX_CUDA(cudaFree(v->node_rec));
-        v->node_rec = nullptr;
+        if (v->node_rec_set[0]) OFX_CUDA(cudaFree(v->node_rec_set[0]));
+        v->node_rec = v->node_rec_set[0] = v->node_rec_set[1] = nullptr;
+        v->node_rec_capacity = 0;
         const int cap = M + M / 4 + 64;   // head-room for node insertion (EDGraph.update appends)
-        OFX_CUDA(cudaMalloc(&v->node_rec, (size_t)cap * NODE_REC_FLOATS * sizeof(float)));
+        OFX_CUDA(cudaMalloc(&v->node_rec_set[0], (size_t)2 * cap * NODE_REC_FLOATS * sizeof(float)));
+        v->node_rec_set[1] = v->node_rec_set[0] + (size_t)cap * NODE_REC_FLOATS;
         v->node_rec_capacity = cap;
     }
-    write_node_positions_kernel<<<(M + 255) / 256, 256, 0, s>>>(nodes, M, v->node_rec);
+    v->cur_set = 0;
+    v->prepared = false;
+    v->node_rec = v->node_rec_set[0];
+    v->live = v->live_set[0];
+    for (int k = 0; k < 2; ++k) {
+        write_node_positions_kernel<<<(M + 255) / 256, 256, 0, s>>>(nodes, M, v->node_rec_set[k]);
+        OFX_LAUNCH_CHECK();
+    }
+    return 0;
+}
+
+// R|T of the M nodes into one of the two per-frame tables
+int ofx_write_transforms(ofx_volume *v, float *table, const float *rotations, const float *translations, cudaStream_t s)
+{
+    write_node_transforms_kernel<<<(v->M * 12 + 255) / 256, 256, 0, s>>>(rotations, translations, v->M, table);
     OFX_LAUNCH_CHECK();
     return 0;
 }
@@ -181,9 +200,7 @@ extern "C" int ofx_set_transforms(ofx_volume *v, const float *rotations, const f
 {
     OFX_REQUIRE(v && rotations && translations, "ofx_set_transforms: null argument");
     OFX_REQUIRE(v->graph_ready, "ofx_set_transforms: call ofx_set_graph first");
-    write_node_transforms_kernel<<<(v->M * 12 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(rotations, translations,
-                                                                                          v->M, v->node_rec);
-    OFX_LAUNCH_CHECK();
+    if (int rc = ofx_write_transforms(v, v->node_rec, rotations, translations, (cudaStream_t)stream)) return rc;
     v->transforms_ready = true;
     return 0;
 }

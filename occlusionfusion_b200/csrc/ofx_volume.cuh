@@ -56,7 +56,8 @@ struct ofx_volume {
     int M, K;
     double coverage;
     float cutoff, denom;
-    float *node_rec;          // M x NODE_REC_FLOATS
+    float *node_rec;          // M x NODE_REC_FLOATS: the CURRENT per-frame set (= node_rec_set[cur_set])
+    float *node_rec_set[2];   // two tables (same node positions): ofx_prepare_frame fills the other one while a frame integrates
     int node_rec_capacity;
 
     // skin cache (device form of WarpField.skin_tsdf's cache, warpfield.py:131-141), brick-major and
@@ -80,11 +81,17 @@ struct ofx_volume {
     int n_active;
     float4 *brick_box;           // n_bricks: brick centre (world) + bounding radius h, written by ofx_set_graph
     int4 *active_desc;           // n_active x ACTIVE_DESC_VEC int4: {lx0, iy0, iz0, n_used | list offset, cache slot, brick, 0 | box (float4)}
-    int *live;                   // per frame: descriptors (LIVE_DESC_INTS ints) of the active bricks that survive the cull
+    int *live;                   // per frame: descriptors (LIVE_DESC_INTS ints) of the active bricks that survive the cull (= live_set[cur_set])
+    int *live_set[2];
+    int cur_set;                 // per-frame set (node transforms, live list, launch counters, counter accumulators) in use
+    float prepared_intr[4];      // the camera ofx_prepare_frame culled against
+    int prepared_hw[2];
+    bool prepared;               // the other set holds the next frame's transforms + live list (ofx_prepare_frame)
+    unsigned long long *stats_acc;   // 2 x OFX_N_STATS: per-set accumulators of the persistent kernel
     float *depth_tiles;          // per frame: max depth of each DEPTH_TILE x DEPTH_TILE pixel tile
     int depth_tiles_capacity;
-    int *scratch;                // small device scratch: [0]=total [1]=max [2]=error [8]=n_live [9]=work counter [10]=retired CTAs (all zero between launches)
+    int *scratch;                // small device scratch: [0]=total [1]=max [2]=error [8 + 4*set ..]: n_live, work counter, retired CTAs (all zero between launches)
     uint64_t *stats_scratch;     // OFX_N_STATS counters when the caller passes NULL
     bool graph_ready, transforms_ready;
-    bool counters_dirty;         // a launch failed between the cull and the fused kernel: scratch[8..10] need a reset
+    bool counters_dirty[2];       // a launch failed between the cull and the fused kernel: the launch counters need a reset
 };

@@ -265,9 +265,15 @@ def test_sharded_equals_whole(x_block, oracle):
         _assert_bit_equal(vol, ov, gx)
 
 
-def test_pipelined_driver_equals_sequential(oracle):
-    """sharded.ShardedFusion.pipeline_* (two packets, two streams: the N > 1 bench path) on one shard:
-    same volume and the same per-frame counters as the sequential step(), and as the oracle."""
+@pytest.mark.parametrize("lookahead", [False, True])
+def test_pipelined_driver_equals_sequential(lookahead, oracle, monkeypatch):
+    """sharded.ShardedFusion.pipeline_* (two packets, two streams: the N > 1 bench path) on one shard, without and
+    with the ofx_prepare_frame look-ahead: same volume and the same per-frame counters as the sequential step(),
+    and as the oracle."""
+    if lookahead:
+        monkeypatch.setenv("OFX_LOOKAHEAD", "1")
+    else:
+        monkeypatch.delenv("OFX_LOOKAHEAD", raising=False)
     import torch
     from occlusionfusion_b200 import WarpField
     from occlusionfusion_b200.sharded import CudaShard, ShardedFusion
@@ -474,3 +480,46 @@ def test_full_size_sampled_parity(name, n_frames, obs_weight, oracle):
         assert ((t < 1.0) & (t > -1.0)).sum() > 1000 and 0 < valid.sum() < len(valid)
     # whole-volume counter identity at full size: every update adds obs_weight to exactly one voxel
     assert vol._weight_vol.sum(dtype=torch.float64).item() == obs_weight * total_updated
+
+
+def test_prepare_frame_lookahead_equals_set_transforms():
+    """ofx_prepare_frame (node transforms + frustum cull staged ahead, in the other per-frame set) followed by
+    ofx_integrate == ofx_set_transforms + ofx_integrate, also when prepared and plain frames alternate; a
+    camera that differs from the prepared one is refused."""
+    import torch
+    from occlusionfusion_b200 import WarpField, _capi
+    from occlusionfusion_b200.sharded import CudaShard
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload("tiny")
+    dev = torch.device("cuda", 0)
+    results = []
+    for mode in ("plain", "prepared", "mixed"):
+        vol = _mk_volume(w)
+        wf = WarpField(w.graph(), vol, None)
+        vol.warpfield = wf
+        be = CudaShard(vol)
+        be.set_graph(torch.from_numpy(w.nodes).to(dev), w.coverage, w.K)
+        colour, depth = be.pack_frame(w.frame(0))
+        be.integrate(depth, colour, True, 1.0)
+        stats = []
+        for f in range(1, 7):
+            est = w.estimate(f)
+            T = (-np.einsum("nij,nj->ni", est["node_rotations"], w.nodes) + w.nodes + est["node_translations"]).astype(np.float32)
+            R_d, T_d = torch.from_numpy(est["node_rotations"]).to(dev).contiguous(), torch.from_numpy(T).to(dev)
+            colour, depth = be.pack_frame(w.frame(f))
+            if mode == "prepared" or (mode == "mixed" and f % 3 != 0):
+                be.prepare(R_d, T_d, w.H, w.W)
+            else:
+                be.set_transforms(R_d, T_d)
+            stats.append(be.integrate(depth, colour, False, 1.0).cpu().numpy().copy())
+        results.append((vol.get_volume(), stats))
+        if mode == "mixed":
+            be.prepare(R_d, T_d, w.H + 1, w.W)
+            with pytest.raises(_capi.OfxError):
+                be.integrate(depth, colour, False, 1.0)
+    for vols, stats in results[1:]:
+        for a, b in zip(results[0][0], vols):
+            assert np.array_equal(a, b)
+        for a, b in zip(results[0][1], stats):
+            assert np.array_equal(a, b)
+    assert results[0][1][-1][0] > 1000
