@@ -1,13 +1,13 @@
 """Investigation only: one GPU plays shard 0 of N (c2-dense) and reports the per-frame device times of the
 node-transform kernel, the cull and the fused kernel, plus (OFX_TIMING build) the per-CTA timeline.
-  tools/shard_probe.py N [timing]"""
+  tools/shard_probe.py N [name of an OFX_TIMING build]"""
 import ctypes, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 N = int(sys.argv[1]) if len(sys.argv) > 1 else 8
-timing = len(sys.argv) > 2
+timing = len(sys.argv) > 2          # name of an OFX_TIMING build: libofx_<name>.so
 if timing:
-    os.environ["OFX_LIB"] = os.path.join(ROOT, "occlusionfusion_b200", "lib", "libofx_timing.so")
+    os.environ["OFX_LIB"] = os.path.join(ROOT, "occlusionfusion_b200", "lib", f"libofx_{sys.argv[2]}.so")
 import numpy as np
 import torch
 from occlusionfusion_b200 import TSDFVolume, WarpField, _capi
