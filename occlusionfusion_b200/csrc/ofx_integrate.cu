@@ -120,6 +120,7 @@ brick_cull_kernel(GraphArgs ga, const int4 *__restrict__ active_desc, int n_acti
     __shared__ int s_base;
     const int slot = threadIdx.x / CULL_LANES, sub = threadIdx.x % CULL_LANES;
     const int idx = blockIdx.x * CULL_BRICKS_PER_CTA + slot;
+    grid_dep_launch();           // the fused kernel's CTAs may move in as this grid drains (they wait for it to finish)
     // the frame's counter accumulators start from zero here (nothing else writes them before the fused kernel)
     if (blockIdx.x == 0 && threadIdx.x < OFX_N_STATS) acc[threadIdx.x] = 0ull;
     int n_used = 0, o = 0;
@@ -133,6 +134,7 @@ brick_cull_kernel(GraphArgs ga, const int4 *__restrict__ active_desc, int n_acti
         n_used = d0.w; o = d1.x;
     }
     const int b = d1.z;
+    grid_dep_wait();             // the node-transform kernel before this one has finished
     float u_lo = 3.0e38f, u_hi = -3.0e38f, v_lo = 3.0e38f, v_hi = -3.0e38f;
     int unbounded = 0;
     for (int i = sub; i < n_used; i += CULL_LANES) {
@@ -238,6 +240,7 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
         for (int s = 0; s < N_SLOTS; ++s) mbar_init(&bar_data[s], 1);
         s_cnt[0] = s_cnt[1] = s_cnt[2] = s_cnt[3] = 0u;
     }
+    grid_dep_wait();             // the cull before this kernel has finished: live list, n_live, accumulators
     __syncthreads();
 
     if (warp == CONSUMER_WARPS) {
@@ -438,6 +441,23 @@ static int launch_brick(ofx_volume *v, int grid, const GraphArgs &ga, const Fram
     return 0;
 }
 
+// Launch configuration with programmatic stream serialisation: the kernel's CTAs may be scheduled while the
+// kernel before it in the stream drains; it calls grid_dep_wait() before it touches that kernel's results.
+#ifndef OFX_PDL
+#define OFX_PDL 1
+#endif
+static cudaLaunchConfig_t pdl_config(int grid, int block, size_t smem, cudaStream_t s)
+{
+    static cudaLaunchAttribute attr;
+    attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr.val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3((unsigned)block);
+    cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cfg.attrs = &attr; cfg.numAttrs = OFX_PDL ? 1 : 0;
+    return cfg;
+}
+
 // The per-frame brick cull of one of the two frame sets (node transforms, live list, launch counters, counter
 // accumulators): on the integrating stream for the current set, or ahead of time for the other one (ofx_prepare_frame).
 static int launch_cull(ofx_volume *v, int set, const Camera &cam, cudaStream_t s)
@@ -447,9 +467,9 @@ static int launch_cull(ofx_volume *v, int set, const Camera &cam, cudaStream_t s
     v->counters_dirty[set] = true;
     GraphArgs ga = graph_args(v);
     ga.node_rec = v->node_rec_set[set];
-    brick_cull_kernel<<<(v->n_active + CULL_BRICKS_PER_CTA - 1) / CULL_BRICKS_PER_CTA, CULL_THREADS, 0, s>>>(
-        ga, v->active_desc, v->n_active, cam, v->live_set[set], counters, v->stats_acc + set * OFX_N_STATS);
-    OFX_LAUNCH_CHECK();
+    cudaLaunchConfig_t cfg = pdl_config((v->n_active + CULL_BRICKS_PER_CTA - 1) / CULL_BRICKS_PER_CTA, CULL_THREADS, 0, s);
+    OFX_CUDA(cudaLaunchKernelEx(&cfg, brick_cull_kernel, ga, (const int4 *)v->active_desc, v->n_active, cam, v->live_set[set],
+                                counters, v->stats_acc + set * OFX_N_STATS));
     return 0;
 }
 
@@ -477,10 +497,10 @@ static int launch_persistent_t(ofx_volume *v, const FrameArgs &fa, unsigned long
     const GraphArgs ga = graph_args(v);
     const int cap = sm_count() * blocks_per_sm;       // persistent grid: a multiple of the SM count
     const int grid = v->n_active < cap ? v->n_active : cap;   // CTAs beyond the live count retire at once
-    fused_warped_persistent<K, VEC, OBS32><<<grid, PERSISTENT_THREADS, smem, s>>>(
-        v->geom, v->desc.tsdf, v->desc.weight, v->desc.colour, ga, fa, v->live, v->scratch + 8 + 4 * set,
-        v->stats_acc + set * OFX_N_STATS, stats);
-    OFX_LAUNCH_CHECK();
+    cudaLaunchConfig_t cfg = pdl_config(grid, PERSISTENT_THREADS, smem, s);
+    OFX_CUDA(cudaLaunchKernelEx(&cfg, fused_warped_persistent<K, VEC, OBS32>, v->geom, v->desc.tsdf, v->desc.weight,
+                                v->desc.colour, ga, fa, (const int *)v->live, v->scratch + 8 + 4 * set,
+                                v->stats_acc + set * OFX_N_STATS, stats));
     v->counters_dirty[set] = false;
     return 0;
 }

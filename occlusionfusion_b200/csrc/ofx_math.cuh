@@ -299,6 +299,13 @@ __device__ __forceinline__ void fuse_voxel(float &tsdf, float &weight, float &co
     colour = __fmaf_rn(b, 65536.0f, __fmaf_rn(g, 256.0f, r));
 }
 
+// ---- programmatic dependent launch (the per-frame sequence node transforms -> cull -> fused kernel) ----
+// grid_dep_wait: block until the preceding kernel in the stream has completed and its writes are visible (returns
+// at once when the kernel was launched without the attribute); grid_dep_launch: the next kernel's CTAs may be
+// scheduled as soon as there is room (they wait in grid_dep_wait).
+__device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void grid_dep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ---- TMA (1-D bulk copy) + mbarrier helpers ------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 

@@ -31,6 +31,7 @@ __global__ void write_node_positions_kernel(const float *__restrict__ nodes, int
 __global__ void write_node_transforms_kernel(const float *__restrict__ R, const float *__restrict__ T, int M,
                                              float *__restrict__ rec)
 {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");    // the cull after this kernel waits for its completion
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= M * 12) return;
     const int j = t / 12, e = t % 12;
