@@ -209,6 +209,17 @@ __device__ __forceinline__ unsigned long long gtime()
 }
 #endif
 constexpr int N_SLOTS = OFX_N_SLOTS;
+
+// a CTA's shared-memory counters {updated, skin-valid, weight sum: low 16 bits, weight sum >> 16} into the
+// frame's accumulators (one thread)
+__device__ __forceinline__ void flush_counters(unsigned *s_cnt, unsigned long long *acc)
+{
+    if (s_cnt[0]) atomicAdd(acc + OFX_STAT_UPDATED, (unsigned long long)s_cnt[0]);
+    if (s_cnt[1]) atomicAdd(acc + OFX_STAT_SKIN_VALID, (unsigned long long)s_cnt[1]);
+    const unsigned long long ws = ((unsigned long long)s_cnt[3] << 16) + s_cnt[2];
+    if (ws) atomicAdd(acc + OFX_STAT_WEIGHT_SUM, ws);
+    s_cnt[0] = s_cnt[1] = s_cnt[2] = s_cnt[3] = 0u;
+}
 constexpr int RING_RECS = 256;                              // > MAX_BRICK_NODES: the largest brick fits an empty ring
 constexpr int CONSUMER_WARPS = BRICK_THREADS / 32;          // 8
 constexpr int PERSISTENT_THREADS = BRICK_THREADS + 32;      // + 1 producer warp
@@ -360,22 +371,28 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
                                                       s_dyn + slot * SLOT_BYTES, s_tab, bc, info.n_used, threadIdx.x,
                                                       nullptr, nullptr, c_upd, c_valid, c_wsum,
                                                       [slot] { named_bar_arrive(1 + slot, PERSISTENT_THREADS); });
-        __syncwarp();
 #if OFX_TIMING
         dbg_b += gtime() - t1;
 #endif
-        c_upd = __reduce_add_sync(0xffffffffu, c_upd);
-        c_valid = __reduce_add_sync(0xffffffffu, c_valid);
+        // one warp reduction for both voxel counts (each at most 128 per warp and brick), one for the weight sum;
+        // lane 0 adds them to the CTA's shared-memory counters with result-less 32-bit atomics (nothing waits
+        // for them; 64-bit shared atomics would be CAS loops).  A CTA sees far fewer than 2^32 voxels per
+        // launch; the weight sum is kept in two halves, 16 bits apart, so that neither can overflow.
+        const unsigned both = __reduce_add_sync(0xffffffffu, c_upd | (c_valid << 16));
         c_wsum = __reduce_add_sync(0xffffffffu, c_wsum);
         if (lane == 0) {
-            // 32-bit shared-memory atomics are native (64-bit ones are CAS loops); a CTA sees far fewer
-            // than 2^32 voxels per launch, the weight sum keeps a carry word
-            if (c_upd) atomicAdd(&s_cnt[0], c_upd);
-            if (c_valid) atomicAdd(&s_cnt[1], c_valid);
+            if (both & 0xFFFFu) atomicAdd(&s_cnt[0], both & 0xFFFFu);
+            if (both >> 16) atomicAdd(&s_cnt[1], both >> 16);
             if (c_wsum) {
-                const unsigned old = atomicAdd(&s_cnt[2], c_wsum);
-                if (old + c_wsum < old) atomicAdd(&s_cnt[3], 1u);
+                atomicAdd(&s_cnt[2], c_wsum & 0xFFFFu);
+                if (c_wsum >> 16) atomicAdd(&s_cnt[3], c_wsum >> 16);
             }
+        }
+        if ((it & 4095) == 4095) {
+            // (never in practice: > 4096 bricks per CTA and launch) empty the 32-bit counters before they can overflow
+            named_bar_sync(1 + N_SLOTS, BRICK_THREADS);
+            if (threadIdx.x == 0) flush_counters(s_cnt, acc);
+            named_bar_sync(1 + N_SLOTS, BRICK_THREADS);
         }
     }
 #if OFX_TIMING
@@ -384,10 +401,7 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
 #endif
     named_bar_sync(1 + N_SLOTS, BRICK_THREADS);    // consumers only
     if (threadIdx.x == 0) {
-        if (s_cnt[0]) atomicAdd(acc + OFX_STAT_UPDATED, (unsigned long long)s_cnt[0]);
-        if (s_cnt[1]) atomicAdd(acc + OFX_STAT_SKIN_VALID, (unsigned long long)s_cnt[1]);
-        const unsigned long long ws = ((unsigned long long)s_cnt[3] << 32) | s_cnt[2];
-        if (ws) atomicAdd(acc + OFX_STAT_WEIGHT_SUM, ws);
+        flush_counters(s_cnt, acc);
         // the last CTA to retire publishes the frame's counters and leaves the launch counters at zero for the
         // next cull of this set (every producer has read n_live and drawn its last work item before its
         // consumers get here)
