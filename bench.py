@@ -516,7 +516,7 @@ def main():
                          "traffic": (ncu_traffic(w.name) or {}).get("dram_bytes_per_launch") if world == 1 else None,
                          "traffic_source": (ncu_traffic(w.name) or {}).get("source") if world == 1 else None,
                          "peak_source": peak_src,
-                         "kernel": "fused_warped_persistent<K,VEC,OBS32> (+ brick_cull_kernel and two 16-byte memsets: "
+                         "kernel": "fused_warped_persistent<K,VEC,OBS32> (+ brick_cull_kernel: "
                                    "CUDA events around ofx_integrate)",
                          "kernel_ms": main_res["kernel_ms_local"],
                          "algorithmic_bytes_per_launch": main_res["alg_bytes"],
