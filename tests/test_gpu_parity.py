@@ -413,23 +413,12 @@ def _axis_tables(w, oracle):
     return px, py, pz
 
 
-@pytest.mark.parametrize("name,n_frames,obs_weight", [("c2-dense", 3, 1.0), ("c2", 4, 1.0), ("c4", 3, 2.0)])
-def test_full_size_sampled_parity(name, n_frames, obs_weight, oracle):
-    """BASELINE configs at FULL size (512^3 / K=4 as benchmarked; 1024^3, 1280x720, ~4k nodes, K=8): the CUDA path
-    integrates the whole volume; a seeded sample of voxels (uniform + concentrated around the surface + whole
-    z-rows) is replayed through the oracle's point operators (skin -> warp -> integrate) and must be bit-identical
-    after every frame."""
+def _voxel_sample(w, oracle, vol, seed=1234):
+    """Seeded sample of voxels of the full-size volume: uniform + around the camera-facing surface (band scenes)
+    + whole z-rows.  Returns flat indices (numpy, and as a device tensor) and the voxels' world points."""
     import torch
-    from occlusionfusion_b200 import WarpField
-    from occlusionfusion_b200.synthetic import Workload
-    w = Workload(name)
     Dx, Dy, Dz = w.dims
-    vol = _mk_volume(w)
-    wf = WarpField(w.graph(), vol, None)
-    wf.graph_neighbours = w.K
-    vol.warpfield = wf
-
-    rng = np.random.default_rng(1234)
+    rng = np.random.default_rng(seed)
     n_uni = 120_000
     ijk = [np.stack([rng.integers(0, Dx, n_uni), rng.integers(0, Dy, n_uni), rng.integers(0, Dz, n_uni)], 1)]
     if w.scene == "band":
@@ -449,6 +438,27 @@ def test_full_size_sampled_parity(name, n_frames, obs_weight, oracle):
     px, py, pz = _axis_tables(w, oracle)
     pts = np.stack([px[ix], py[iy], pz[iz]], 1).astype(np.float32)
     flat_t = torch.from_numpy(flat).to(vol.device)
+
+    return flat, flat_t, pts
+
+
+@pytest.mark.parametrize("name,n_frames,obs_weight", [("c0", 4, 1.0), ("c1", 4, 1.0), ("c2-dense", 3, 1.0), ("c2", 4, 1.0), ("c4", 3, 2.0)])
+def test_full_size_sampled_parity(name, n_frames, obs_weight, oracle):
+    """BASELINE configs at FULL size (128^3, 256^3, 512^3 / K=4 as benchmarked; 1024^3, 1280x720, ~4k nodes, K=8): the CUDA path
+    integrates the whole volume; a seeded sample of voxels (uniform + concentrated around the surface + whole
+    z-rows) is replayed through the oracle's point operators (skin -> warp -> integrate) and must be bit-identical
+    after every frame."""
+    import torch
+    from occlusionfusion_b200 import WarpField
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload(name)
+    Dx, Dy, Dz = w.dims
+    vol = _mk_volume(w)
+    wf = WarpField(w.graph(), vol, None)
+    wf.graph_neighbours = w.K
+    vol.warpfield = wf
+
+    flat, flat_t, pts = _voxel_sample(w, oracle, vol)
 
     a, wts, valid = oracle.skin(pts, w.nodes, w.K, w.coverage)
     t = np.ones(len(flat), np.float32)
@@ -475,7 +485,7 @@ def test_full_size_sampled_parity(name, n_frames, obs_weight, oracle):
         assert np.array_equal(g_c, c), f"frame {f}: colours differ at {(g_c != c).sum()} sampled voxels"
         assert np.array_equal(g_t, t), f"frame {f}: tsdf differs, max {np.abs(g_t - t).max()}"
     # the sample must have exercised the path: updated voxels, repeated observations, a real surface band
-    assert (wt > 0).sum() > 20_000 and wt.max() == n_frames * obs_weight
+    assert (wt > 0).sum() > 5_000 and wt.max() == n_frames * obs_weight
     if w.scene == "band":
         assert ((t < 1.0) & (t > -1.0)).sum() > 1000 and 0 < valid.sum() < len(valid)
     # whole-volume counter identity at full size: every update adds obs_weight to exactly one voxel
@@ -523,3 +533,57 @@ def test_prepare_frame_lookahead_equals_set_transforms():
         for a, b in zip(results[0][1], stats):
             assert np.array_equal(a, b)
     assert results[0][1][-1][0] > 1000
+
+
+def test_full_size_sequence_with_node_insertion(oracle):
+    """BASELINE config 3 at full size: a 100-frame sequence at 256^3 with per-frame node transforms and node insertion
+    every 10th frame (the node table grows 800 -> 1000; old nodes keep their indices, EDGraph.update appends;
+    warpfield.py:532-533 re-skins every voxel).  The sampled voxels are replayed through the oracle's point
+    operators and compared after every graph change and at the end, bit-identical, weights == number of hits."""
+    import torch
+    from occlusionfusion_b200 import WarpField
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload("c1")
+    vol = _mk_volume(w)
+    nodes = w.nodes[:800].copy()
+    wf = WarpField(_graph(nodes, w.coverage), vol, None)
+    wf.graph_neighbours = w.K
+    vol.warpfield = wf
+    flat, flat_t, pts = _voxel_sample(w, oracle, vol, seed=77)
+    a, wts, valid = oracle.skin(pts, nodes, w.K, w.coverage)
+    t = np.ones(len(flat), np.float32)
+    wt = np.zeros(len(flat), np.float32)
+    c = np.zeros(len(flat), np.float32)
+
+    def compare(f):
+        g_t = vol._tsdf_vol.reshape(-1)[flat_t].cpu().numpy()
+        g_w = vol._weight_vol.reshape(-1)[flat_t].cpu().numpy()
+        g_c = vol._color_vol.reshape(-1)[flat_t].cpu().numpy()
+        assert np.array_equal(g_w, wt), f"frame {f}: weights differ at {(g_w != wt).sum()} of {len(flat)} sampled voxels"
+        assert np.array_equal(g_c, c), f"frame {f}: colours differ at {(g_c != c).sum()} sampled voxels"
+        assert np.array_equal(g_t, t), f"frame {f}: tsdf differs, max {np.abs(g_t - t).max()}"
+
+    n_valid = [int(valid.sum())]
+    for f in range(100):
+        im = w.frame(f)
+        color_im, depth_im = oracle.pack_frame(im)
+        if f == 0:
+            cam_pts, ok = pts, np.ones(len(pts), bool)
+        else:
+            if f % 10 == 0:
+                compare(f - 1)
+                nodes = w.nodes[: len(nodes) + 20].copy()               # insertion: the table grows, indices are kept
+                wf.graph.nodes = nodes
+                wf.rotations = np.tile(np.eye(3, dtype=np.float32), (len(nodes), 1, 1))
+                wf.translations = np.zeros((len(nodes), 3), np.float32)
+                wf.deformed_nodes = nodes.copy()
+                a, wts, valid = oracle.skin(pts, nodes, w.K, w.coverage)
+                n_valid.append(int(valid.sum()))
+            est = w.estimate(f, nodes)
+            wf.update_transformations(est)
+            cam_pts, ok = oracle.warp(pts, a, wts, valid, est["node_rotations"], wf.translations), valid
+        vol.integrate({"im": im, "id": f})
+        oracle.integrate(t, wt, c, cam_pts, ok, depth_im, color_im, w.intr, w.trunc, 1.0)
+    compare(99)
+    assert len(nodes) == 980 and n_valid[-1] > n_valid[0]                 # the inserted nodes reach new voxels
+    assert wt.max() >= 30 and ((t < 1.0) & (t > -1.0)).sum() > 1000
