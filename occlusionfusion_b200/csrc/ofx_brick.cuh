@@ -163,6 +163,22 @@ __device__ __forceinline__ PixBox ball_pixbox(float bx, float by, float bz, floa
     return b;
 }
 
+// The same for an axis-aligned box of half extents (ex, ey, ez) around (bx, by, bz) in camera space.
+__device__ __forceinline__ PixBox box_pixbox(float bx, float by, float bz, float ex, float ey, float ez, const Camera &cam)
+{
+    PixBox b;
+    const float z_lo = bz - ez, z_hi = bz + ez;
+    b.z_lo = z_lo;
+    b.unbounded = !(z_lo > 1e-4f);
+    const float xl = bx - ex, xh = bx + ex, yl = by - ey, yh = by + ey;
+    const float zl = b.unbounded ? 1.f : z_lo;
+    b.u_lo = cam.fx * (xl / (xl >= 0.f ? z_hi : zl)) + cam.cx;
+    b.u_hi = cam.fx * (xh / (xh >= 0.f ? zl : z_hi)) + cam.cx;
+    b.v_lo = cam.fy * (yl / (yl >= 0.f ? z_hi : zl)) + cam.cy;
+    b.v_hi = cam.fy * (yh / (yh >= 0.f ? zl : z_hi)) + cam.cy;
+    return b;
+}
+
 __device__ __forceinline__ void brick_centre(const VolumeGeom &g, const BrickCoord &bc, float &cx, float &cy, float &cz,
                                              float &h)
 {

@@ -98,10 +98,21 @@ fused_brick_kernel(VolumeGeom g, float *__restrict__ tsdf, float *__restrict__ w
 }
 
 // ---- per-frame brick cull: active bricks -> live list -----------------------------------------------
-// Eight lanes per active brick walk the brick's node list (records come from L2), bound the pixel
-// box of the warped brick (ofx_brick.cuh: ball_pixbox) and drop the bricks that cannot reach the
-// image.  Survivors are appended to live[] (one atomic per CTA of 32 bricks); the fused kernel
-// then sees only bricks that do arithmetic, so its dynamic scheduler balances equal-cost units.
+// A few lanes per active brick walk the brick's node list (records come from L2), bound the pixel box of the
+// warped brick and drop the bricks that cannot reach the image.  The bound: every voxel p of a brick lies in its
+// axis-aligned box (centre c, half extents h); node k maps the box to an oriented box inside the camera-space
+// box R_k c + T_k +- |R_k| h; the blend is a convex combination (up to a scale in (0,1], which the projection
+// ignores) of one point from each of those, so the union of their pixel boxes bounds the voxel's pixel
+// (ofx_brick.cuh: box_pixbox).  Bricks are long in z (4 x 8 x 32 voxels): the oriented box is several times
+// tighter in pixels than the bounding ball used up to v9.  Survivors are appended to live[] (one atomic per
+// CTA); the fused kernel then sees only bricks that do arithmetic, so its dynamic scheduler balances equal-cost units.
+#ifndef OFX_CULL_BALL
+#define OFX_CULL_BALL 0      // 1: bound the warped brick by balls (v4-v9) instead of oriented boxes
+#endif
+#ifndef OFX_CULL_SUB
+#define OFX_CULL_SUB 1       // pieces along z the brick's box is cut into for the bound (2/4/8 drop 0.5-1 % more bricks: no gain)
+#endif
+constexpr int CULL_SUB = OFX_CULL_SUB;
 #ifndef OFX_CULL_LANES
 #define OFX_CULL_LANES 4
 #endif
@@ -125,12 +136,13 @@ brick_cull_kernel(GraphArgs ga, const int4 *__restrict__ active_desc, int n_acti
     if (blockIdx.x == 0 && threadIdx.x < OFX_N_STATS) acc[threadIdx.x] = 0ull;
     int n_used = 0, o = 0;
     int4 d0 = make_int4(0, 0, 0, 0), d1 = make_int4(0, 0, -1, 0);
-    float4 box = make_float4(0.f, 0.f, 0.f, 0.f);
+    float4 box = make_float4(0.f, 0.f, 0.f, 0.f), ext = box;
     if (idx < n_active) {
         const int4 *d = active_desc + ACTIVE_DESC_VEC * idx;
         d0 = __ldg(d); d1 = __ldg(d + 1);
-        const int4 bx = __ldg(d + 2);
+        const int4 bx = __ldg(d + 2), ex = __ldg(d + 3);
         box = make_float4(__int_as_float(bx.x), __int_as_float(bx.y), __int_as_float(bx.z), __int_as_float(bx.w));
+        ext = make_float4(__int_as_float(ex.x), __int_as_float(ex.y), __int_as_float(ex.z), 0.f);
         n_used = d0.w; o = d1.x;
     }
     const int b = d1.z;
@@ -143,10 +155,27 @@ brick_cull_kernel(GraphArgs ga, const int4 *__restrict__ active_desc, int n_acti
         const float bx = a.x * box.x + a.y * box.y + a.z * box.z + d.y;
         const float by = a.w * box.x + c.x * box.y + c.y * box.z + d.z;
         const float bz = c.z * box.x + c.w * box.y + d.x * box.z + d.w;
+        // the rigid image of the brick's box is an oriented box; its camera-space half extents are |R| h
+#if OFX_CULL_BALL
         const PixBox pb = ball_pixbox(bx, by, bz, box.w, cam);
         unbounded |= pb.unbounded;
         u_lo = fminf(u_lo, pb.u_lo); u_hi = fmaxf(u_hi, pb.u_hi);
         v_lo = fminf(v_lo, pb.v_lo); v_hi = fmaxf(v_hi, pb.v_hi);
+#else
+        // (optionally cut into CULL_SUB pieces along z, the brick's long side)
+        const float hz = ext.z * (1.0f / CULL_SUB);
+        const float ex = fabsf(a.x) * ext.x + fabsf(a.y) * ext.y + fabsf(a.z) * hz;
+        const float ey = fabsf(a.w) * ext.x + fabsf(c.x) * ext.y + fabsf(c.y) * hz;
+        const float ez = fabsf(c.z) * ext.x + fabsf(c.w) * ext.y + fabsf(d.x) * hz;
+#pragma unroll
+        for (int sb = 0; sb < CULL_SUB; ++sb) {
+            const float oz = (float)(2 * sb + 1 - CULL_SUB) * hz;      // centre of piece sb relative to the brick centre
+            const PixBox pb = box_pixbox(bx + a.z * oz, by + c.y * oz, bz + d.x * oz, ex, ey, ez, cam);
+            unbounded |= pb.unbounded;
+            u_lo = fminf(u_lo, pb.u_lo); u_hi = fmaxf(u_hi, pb.u_hi);
+            v_lo = fminf(v_lo, pb.v_lo); v_hi = fmaxf(v_hi, pb.v_hi);
+        }
+#endif
     }
 #pragma unroll
     for (int o2 = CULL_LANES / 2; o2 > 0; o2 >>= 1) {

@@ -34,6 +34,7 @@ constexpr float RADIUS_SLACK_ABS = 1e-5f;
 
 struct BrickBox {
     float cx, cy, cz, h;
+    float hx, hy, hz;      // half extents of the voxel-centre box
 };
 
 __device__ __forceinline__ BrickBox brick_box(const VolumeGeom &g, int b)
@@ -48,6 +49,7 @@ __device__ __forceinline__ BrickBox brick_box(const VolumeGeom &g, int b)
     bb.cx = 0.5f * (x_lo + x_hi); bb.cy = 0.5f * (y_lo + y_hi); bb.cz = 0.5f * (z_lo + z_hi);
     const float hx = 0.5f * (x_hi - x_lo), hy = 0.5f * (y_hi - y_lo), hz = 0.5f * (z_hi - z_lo);
     bb.h = sqrtf(hx * hx + hy * hy + hz * hz) * RADIUS_SLACK_REL + RADIUS_SLACK_ABS;
+    bb.hx = hx; bb.hy = hy; bb.hz = hz;
     return bb;
 }
 
@@ -94,9 +96,10 @@ __global__ void __launch_bounds__(128) brick_bound_kernel(VolumeGeom g, int n_br
             // dead brick: even the nearest corner is farther than the cutoff from its K-th node
             R = (sqrtf(bd[K - 1]) - bb.h > cut) ? -1.0f : fminf(dk + 2.0f * bb.h, cut + bb.h);
             radius[b] = R;
-            // centre + bounding radius for the per-frame cull (brick_cull_kernel); wider slack: the
-            // cull also absorbs the float32 rounding of the transformed centre
-            box_out[b] = make_float4(bb.cx, bb.cy, bb.cz, bb.h * 1.001f + 1e-5f);
+            // centre + bounding radius and the box half extents for the per-frame cull (brick_cull_kernel); wider
+            // slack: the cull also absorbs the float32 rounding of the transformed centre
+            box_out[2 * b] = make_float4(bb.cx, bb.cy, bb.cz, bb.h * 1.001f + 1e-5f);
+            box_out[2 * b + 1] = make_float4(bb.hx * 1.001f + 1e-5f, bb.hy * 1.001f + 1e-5f, bb.hz * 1.001f + 1e-5f, 0.0f);
         }
     }
     int count = 0;
@@ -320,7 +323,7 @@ __global__ void __launch_bounds__(BRICK_THREADS) skin_brick_kernel(VolumeGeom g,
 }
 
 // One record per active brick with everything the per-frame cull needs, contiguous in the order of the
-// active list: {lx0, iy0, iz0, n_used | list offset, cache slot, brick, 0 | centre + bounding radius}.
+// active list: {lx0, iy0, iz0, n_used | list offset, cache slot, brick, 0 | centre + bounding radius | half extents}.
 __global__ void active_desc_kernel(VolumeGeom g, const int *__restrict__ active, int n_active, const int *__restrict__ cnt,
                                    const int *__restrict__ off, const int *__restrict__ brick_slot,
                                    const float4 *__restrict__ brick_box, int4 *__restrict__ desc)
@@ -329,10 +332,11 @@ __global__ void active_desc_kernel(VolumeGeom g, const int *__restrict__ active,
     if (i >= n_active) return;
     const int b = active[i];
     const BrickCoord bc = brick_coord(g, b);
-    const float4 box = brick_box[b];
+    const float4 box = brick_box[2 * b], ext = brick_box[2 * b + 1];
     desc[ACTIVE_DESC_VEC * i] = make_int4(bc.lx0, bc.iy0, bc.iz0, cnt[b]);
     desc[ACTIVE_DESC_VEC * i + 1] = make_int4(off[b], brick_slot[b], b, 0);
     desc[ACTIVE_DESC_VEC * i + 2] = make_int4(__float_as_int(box.x), __float_as_int(box.y), __float_as_int(box.z), __float_as_int(box.w));
+    desc[ACTIVE_DESC_VEC * i + 3] = make_int4(__float_as_int(ext.x), __float_as_int(ext.y), __float_as_int(ext.z), 0);
 }
 
 }  // namespace ofx

@@ -124,7 +124,7 @@ extern "C" int ofx_volume_create(ofx_volume **out, const ofx_volume_desc *d)
     OFX_CUDA(cudaMemset(v->stats_acc, 0, 2 * OFX_N_STATS * sizeof(unsigned long long)));
     OFX_CUDA(cudaMalloc(&v->active_desc, nb * ACTIVE_DESC_VEC * sizeof(int4)));
     OFX_CUDA(cudaMalloc(&v->brick_slot, nb * sizeof(int)));
-    OFX_CUDA(cudaMalloc(&v->brick_box, nb * sizeof(float4)));
+    OFX_CUDA(cudaMalloc(&v->brick_box, 2 * nb * sizeof(float4)));
     OFX_CUDA(cudaMalloc(&v->scratch, 16 * sizeof(int)));      // [0..7] set_graph results, [8 + 4*set ..] n_live, brick work counter, retired CTAs
     OFX_CUDA(cudaMemset(v->scratch, 0, 16 * sizeof(int)));
     OFX_CUDA(cudaMalloc(&v->stats_scratch, OFX_N_STATS * sizeof(uint64_t)));

@@ -15,7 +15,7 @@ constexpr int VOX_PER_THREAD = 4;
 constexpr int BRICK_THREADS = BX * BY * (BZ / VOX_PER_THREAD);   // 256
 constexpr int BRICK_VOXELS = BX * BY * BZ;                       // 1024
 constexpr int NODE_REC_FLOATS = 16;   // {gx,gy,gz,0, R00..R22, T0,T1,T2} = 64 B in global memory
-constexpr int ACTIVE_DESC_VEC = 3;     // active-brick descriptor in int4 units: the live descriptor + the brick's bounding ball
+constexpr int ACTIVE_DESC_VEC = 4;     // active-brick descriptor in int4 units: the live descriptor + the brick's bounding ball + box half extents
 constexpr int LIVE_DESC_INTS = 8;      // live-brick descriptor: {lx0, iy0, iz0, n_used | list offset, cache slot, brick, 0}
 constexpr int NODE_XFORM_OFFSET = 4;  // the 48-byte {R, T} tail is what the fused kernels stage (one TMA bulk copy)
 constexpr int NODE_XFORM_FLOATS = 12;
@@ -79,8 +79,8 @@ struct ofx_volume {
     int64_t list_capacity;
     int *active;                 // bricks with at least one skin-valid voxel
     int n_active;
-    float4 *brick_box;           // n_bricks: brick centre (world) + bounding radius h, written by ofx_set_graph
-    int4 *active_desc;           // n_active x ACTIVE_DESC_VEC int4: {lx0, iy0, iz0, n_used | list offset, cache slot, brick, 0 | box (float4)}
+    float4 *brick_box;           // 2 x n_bricks: {brick centre (world), bounding radius h}, {box half extents, 0}; written by ofx_set_graph
+    int4 *active_desc;           // n_active x ACTIVE_DESC_VEC int4: {lx0, iy0, iz0, n_used | list offset, cache slot, brick, 0 | centre + radius | half extents}
     int *live;                   // per frame: descriptors (LIVE_DESC_INTS ints) of the active bricks that survive the cull (= live_set[cur_set])
     int *live_set[2];
     int cur_set;                 // per-frame set (node transforms, live list, launch counters, counter accumulators) in use
