@@ -24,8 +24,8 @@ _u8p = np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")
 
 
 def build(force=False):
-    src = os.path.join(_HERE, "ofx_oracle.c")
-    if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < os.path.getmtime(src):
+    srcs = [os.path.join(_HERE, f) for f in ("ofx_oracle.c", "ofx_oracle_graph.c")]
+    if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < max(os.path.getmtime(s) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s", "libofx_oracle.so"])
     return _LIB_PATH
 
@@ -49,6 +49,13 @@ def _load():
     lib.ofx_oracle_integrate.restype = C.c_int64
     lib.ofx_oracle_integrate.argtypes = [_f32p, _f32p, _f32p, C.c_int64, _f32p, _u8p, _f32p, _f32p,
                                          C.c_int, C.c_int, _f64p, C.c_double, C.c_double]
+    lib.ofx_oracle_nearest_node.argtypes = [_f32p, C.c_int64, _f32p, C.c_int, _f32p, _i32p]
+    lib.ofx_oracle_greedy_update.restype = C.c_int
+    lib.ofx_oracle_greedy_update.argtypes = [_f32p, _i32p, C.c_int, _f32p, C.c_int, C.c_double, _i32p]
+    lib.ofx_oracle_sample_nodes.restype = C.c_int
+    lib.ofx_oracle_sample_nodes.argtypes = [_f32p, _u8p, C.c_int, C.c_float, C.c_int, _i32p, _f32p]
+    lib.ofx_oracle_erode_mesh.argtypes = [_i32p, C.c_int, C.c_int, C.c_int, C.c_int, _u8p]
+    lib.ofx_oracle_truncated_region.argtypes = [_f32p, C.c_int, C.c_int, C.c_int, C.c_double, _u8p]
     return lib
 
 
@@ -137,6 +144,47 @@ def integrate(tsdf, weight, colour, cam_pts, valid_points, depth, color_im, intr
                                           tsdf.size, _c(cam_pts, np.float32), _c(valid_points, np.uint8),
                                           depth, color_im, H, W, _c(intr4, np.float64),
                                           float(trunc), float(obs_weight)))
+
+
+def nearest_node(points, nodes):
+    """warpfield.py:463: float32 distance to / index of the nearest node."""
+    points, nodes = _c(points, np.float32).reshape(-1, 3), _c(nodes, np.float32)
+    dist, idx = np.empty(len(points), np.float32), np.empty(len(points), np.int32)
+    lib().ofx_oracle_nearest_node(points, len(points), nodes, len(nodes), dist, idx)
+    return dist, idx
+
+
+def greedy_update(verts, cand, nodes, coverage):
+    """embedded_deformation_graph.py:516-536: accepted vertex ids, in acceptance order."""
+    verts, nodes, cand = _c(verts, np.float32), _c(nodes, np.float32).reshape(-1, 3), _c(cand, np.int32)
+    acc = np.empty(max(len(cand), 1), np.int32)
+    n = lib().ofx_oracle_greedy_update(verts, cand, len(cand), nodes, len(nodes), float(coverage), acc)
+    return acc[:n].copy()
+
+
+def sample_nodes(verts, non_eroded, coverage, use_only_non_eroded=True):
+    """graph_proc.cpp:79-136 (randomShuffle = false): (node positions, node vertex ids)."""
+    verts = _c(verts, np.float32)
+    ne = _c(np.asarray(non_eroded).reshape(-1), np.uint8)
+    idx, pos = np.empty(max(len(verts), 1), np.int32), np.empty((max(len(verts), 1), 3), np.float32)
+    n = lib().ofx_oracle_sample_nodes(verts, ne, len(verts), float(coverage), int(use_only_non_eroded), idx, pos)
+    return pos[:n].copy(), idx[:n].copy()
+
+
+def erode_mesh(n_verts, faces, n_iter, min_neighbours):
+    """graph_proc.cpp:17-77: (V,) bool, True = not eroded."""
+    faces = _c(faces, np.int32).reshape(-1, 3)
+    out = np.empty(max(int(n_verts), 1), np.uint8)
+    lib().ofx_oracle_erode_mesh(faces, len(faces), int(n_verts), int(n_iter), int(min_neighbours), out)
+    return out[:int(n_verts)].astype(bool)
+
+
+def truncated_region(tsdf, max_diff):
+    """tsdf.py:706-745: bool volume."""
+    tsdf = _c(tsdf, np.float32)
+    out = np.empty(tsdf.shape, np.uint8)
+    lib().ofx_oracle_truncated_region(tsdf, *tsdf.shape, float(max_diff), out)
+    return out.astype(bool)
 
 
 def origin_translations(R, t, nodes):
