@@ -133,6 +133,36 @@ int ofx_check_visibility(const float *points, int64_t n, const float *depth, int
                          const float *intr_host, double trunc_margin, uint8_t *valid,
                          double *depth_diff, void *stream);
 
+/* ---- graph maintenance and surface mask (callers either side of the path when nodes are inserted) -------- */
+/* source_frame_kdtree.query(points, k=1) (fusion_with_occlusion/warpfield.py:463, WarpField.find_unreachable_nodes):
+ * float32 distance to and index of the nearest node, ties -> lower index.  dist or idx may be NULL. */
+int ofx_nearest_node(const float *points, int64_t n, const float *nodes, int32_t M, float *dist,
+                     int32_t *idx, void *stream);
+/* The greedy coverage rule of EDGraph.update (fusion_with_occlusion/embedded_deformation_graph.py:516-536):
+ * walk cand[0..n_cand) (vertex ids into verts (V,3), in the caller's order -- farthest first, warpfield.py:469-483);
+ * accept a vertex unless an existing node (nodes (M,3), M may be 0) or an already accepted vertex is closer than
+ * node_coverage (float32 norm, float64 comparison).  accepted (capacity n_cand) receives the accepted vertex ids in
+ * acceptance order, *n_accepted (device) their number.  Identical to the serial loop, order included. */
+int ofx_greedy_insert(const float *verts, int32_t V, const int32_t *cand, int32_t n_cand,
+                      const float *nodes, int32_t M, double node_coverage, int32_t *accepted,
+                      int32_t *n_accepted, void *stream);
+/* sample_nodes (csrc/cpu/graph_proc.cpp:79-136, binding csrc/main.cpp:29) with randomShuffle = false, as
+ * EDGraph.create_graph_from_mesh calls it (embedded_deformation_graph.py:196-206): vertices in index order, eroded
+ * ones skipped when use_only_non_eroded, a vertex becomes a node unless squaredNorm(v - node) <= coverage^2 (float32)
+ * for an earlier node.  node_idx (capacity V), node_pos (capacity V x 3, may be NULL), *n_nodes (device). */
+int ofx_sample_nodes(const float *verts, int32_t V, const uint8_t *non_eroded, float node_coverage,
+                     int32_t use_only_non_eroded, int32_t *node_idx, float *node_pos,
+                     int32_t *n_nodes, void *stream);
+/* erode_mesh (csrc/cpu/graph_proc.cpp:17-77, binding csrc/main.cpp:28): n_iterations rounds of "keep the faces whose
+ * three vertices each touch >= min_neighbours kept faces"; non_eroded (V,) u8 = vertex of a surviving face.
+ * Faces (F,3) i32; a face with an index outside [0,V) is ignored (undefined behaviour in the reference). */
+int ofx_erode_mesh(const int32_t *faces, int32_t F, int32_t V, int32_t n_iterations,
+                   int32_t min_neighbours, uint8_t *non_eroded, void *stream);
+/* TSDFVolume.compute_truncated_region (fusion_with_occlusion/tsdf.py:706-745): region (Dx,Dy,Dz) u8, the mask the
+ * reference hands to marching cubes (tsdf.py:794).  tsdf is a whole (unsharded) volume, C order. */
+int ofx_truncated_region(const float *tsdf, int32_t Dx, int32_t Dy, int32_t Dz, double max_diff,
+                         uint8_t *region, void *stream);
+
 /* ---- multi-GPU plumbing ------------------------------------------------------------------------ */
 /* Copies `bytes` (a multiple of 16, both pointers 16-byte aligned) from `src` to `dst` with `ctas`
  * thread blocks.  `src` may be a PEER pointer (another GPU's buffer mapped into this process through

@@ -258,6 +258,28 @@ class TSDFVolume:
         self._color_vol.copy_(torch.from_numpy(np.ascontiguousarray(data[1], dtype=np.float32)))
         self._weight_vol.copy_(torch.from_numpy(np.ascontiguousarray(data[2], dtype=np.float32)))
 
+    @staticmethod
+    def compute_truncated_region(tsdf_vol, max_diff):
+        """The mask the reference hands to marching cubes (tsdf.py:706-745, call at :791): True where |tsdf| <= 0.9, the
+        voxel is not on the volume boundary and no neighbour differs by more than max_diff.  Runs on the device
+        (ofx_truncated_region).  tsdf_vol: (Dx,Dy,Dz) float32 numpy array -> bool numpy array (as the reference), or a
+        CUDA tensor -> CUDA bool tensor (no copies)."""
+        _capi.require_cuda()
+        as_numpy = not isinstance(tsdf_vol, torch.Tensor)
+        dev = tsdf_vol.device if not as_numpy and tsdf_vol.is_cuda else torch.device("cuda", torch.cuda.current_device())
+        t = _capi.to_device(tsdf_vol, torch.float32, dev)
+        assert t.dim() == 3
+        out = torch.empty(t.shape, dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            _capi.check(_capi.load().ofx_truncated_region(_capi.ptr(t), t.shape[0], t.shape[1], t.shape[2], float(max_diff),
+                                                          _capi.ptr(out), _capi.stream_ptr(dev)))
+        return out.cpu().numpy().astype(bool) if as_numpy else out.bool()
+
+    def get_truncated_region(self, max_diff=1.2):
+        """compute_truncated_region of this volume's TSDF, on the device, as a CUDA bool tensor (tsdf.py:791 uses 1.2)."""
+        assert self.n_shards == 1, "the truncated region looks at x-neighbours: gather the shards first (ShardedFusion.gather_volume)"
+        return self.compute_truncated_region(self._tsdf_vol, max_diff)
+
     def get_canonical_model(self):
-        raise NotImplementedError("surface extraction (tsdf.py:704-809) is a 'next' row (SURVEY.md 8 f3); "
-                                  "pass canonical vertices to WarpField.update_graph explicitly")
+        raise NotImplementedError("marching cubes (skimage call at tsdf.py:794) is not rebuilt: get_truncated_region() gives its "
+                                  "mask; pass canonical vertices / faces to WarpField.update_graph explicitly")

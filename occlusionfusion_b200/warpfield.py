@@ -227,12 +227,14 @@ class WarpField:
     # ------------------------------------------------------------------ node insertion
     def find_unreachable_nodes(self, points):
         """Indices of points farther than 2*node_coverage from every node, farthest first
-        (warpfield.py:455-485).  Nearest-node distance = K=1 query on the device."""
+        (warpfield.py:455-485).  Nearest-node distance: ofx_nearest_node (exact float32 brute force on the device)."""
         pts = _capi.to_device(points, torch.float32, self.device).reshape(-1, 3)
         nd = _capi.to_device(self.graph.nodes, torch.float32, self.device)
-        # exact float32 nearest distance, chunked (n x M) on the device
-        dist = torch.cat([torch.cdist(pts[i:i + 65536].double(), nd.double()).min(dim=1).values
-                          for i in range(0, pts.shape[0], 65536)]).float().cpu().numpy() if pts.shape[0] else np.zeros(0, np.float32)
+        dist_d = torch.empty(pts.shape[0], dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            _capi.check(self._lib.ofx_nearest_node(_capi.ptr(pts), pts.shape[0], _capi.ptr(nd), nd.shape[0],
+                                                   _capi.ptr(dist_d), None, _capi.stream_ptr(self.device)))
+        dist = dist_d.cpu().numpy()                       # float32, as the float32 KD-tree returns it (warpfield.py:463-464)
         unreachable_verts = np.where(dist > 2 * self.node_coverage)[0]
         if len(unreachable_verts) == 0:
             return []
@@ -250,14 +252,18 @@ class WarpField:
         if canonical_model is None:
             canonical_model = self.tsdf.get_canonical_model()
         verts, faces = canonical_model[0], canonical_model[1]
-        keep = self.graph.erode_mesh(verts, faces, num_iterations=3).reshape(-1) if hasattr(self.graph, "erode_mesh") \
-            else np.arange(len(verts))
-        new_verts_indices = self.find_unreachable_nodes(verts[keep])
+        # warpfield.py:500-506: candidates are searched among the NON-ERODED vertices (erode_mesh, 3 requested rounds --
+        # EDGraph.erode_mesh replaces any truthy count by erosion_num_iterations, as the reference does) ...
+        non_eroded = self.graph.erode_mesh(verts, faces, num_iterations=3).reshape(-1) if hasattr(self.graph, "erode_mesh") \
+            else np.ones(len(verts), dtype=bool)
+        new_verts_indices = self.find_unreachable_nodes(verts[non_eroded])
         if len(new_verts_indices) == 0:
             self.updating_warpfield = False
             return False
         old_num_nodes = self.graph.nodes.shape[0]
-        update = self.graph.update(verts[keep], faces, new_verts_indices)
+        # ... and, as in the reference (warpfield.py:516), the indices -- positions within the non-eroded subset -- are
+        # handed to EDGraph.update together with the FULL vertex array.  Kept for identical results.
+        update = self.graph.update(verts, faces, new_verts_indices)
         if update:
             M = self.graph.nodes.shape[0]
             R_rel, t_rel = self.get_transformation_wrt_graph_node()

@@ -2,6 +2,7 @@
 import types
 
 import numpy as np
+import pytest
 
 from conftest import load_golden
 
@@ -40,17 +41,40 @@ def test_origin_translations_bit_identical_to_reference_loop(golden):
         assert np.array_equal(_rot_apply(R, p), np.array([R[i] @ p[i] for i in range(len(p))]))
 
 
-def test_edgraph_update_greedy():
-    """Node insertion follows embedded_deformation_graph.py:516-542: order-dependent greedy sampling."""
+def test_edgraph_update_needs_the_device():
+    """Node insertion (embedded_deformation_graph.py:516-542) runs in libofx.so; without a GPU only the trivial
+    early-outs work and everything else fails loudly (no CPU fallback).  Parity: tests/test_z_graph_gpu.py."""
+    import torch
     from occlusionfusion_b200 import EDGraph
+    from occlusionfusion_b200._capi import OfxError
     nodes = np.array([[0, 0, 0], [1, 0, 0]], np.float32)
     g = EDGraph(nodes=nodes, graph_generation_parameters={"node_coverage": 0.5})
-    verts = np.array([[0.1, 0, 0], [2, 0, 0], [2.2, 0, 0], [3, 0, 0], [1.4, 0, 0]], np.float32)
-    assert g.update(verts, None, []) is False
-    assert g.update(verts, None, [0]) is False                      # within coverage of node 0
-    assert g.update(verts, None, [0, 1, 2, 3, 4]) is True           # 1 accepted, 2 too close to 1, 3 accepted, 4 too close to node 1
-    assert np.array_equal(g.nodes, np.array([[0, 0, 0], [1, 0, 0], [2, 0, 0], [3, 0, 0]], np.float32))
-    assert g.nodes.dtype == np.float32
+    verts = np.array([[0.1, 0, 0], [2, 0, 0]], np.float32)
+    assert g.update(verts, None, []) is False                       # :513-514
+    if not torch.cuda.is_available():
+        with pytest.raises(OfxError):
+            g.update(verts, None, [0, 1])
+        with pytest.raises(OfxError):
+            g.erode_mesh(verts, np.zeros((1, 3), np.int32))
+
+
+def test_graph_bin_formats_match_reference_bytes(tmp_path):
+    """utils/utils.py:205-321: the files our writers produce are byte-identical to the ones the reference's own
+    save_graph_* wrote (golden, oracle/make_golden_graph.py) and load back to the same arrays."""
+    from conftest import load_golden
+    from occlusionfusion_b200 import formats as F
+    g = load_golden("ref_graph")
+    for kind in ("nodes", "edges", "edges_weights", "node_deformations", "clusters"):
+        a = g[f"fmt_{kind}_in"]
+        path = str(tmp_path / (kind + ".bin"))
+        getattr(F, "save_graph_" + kind)(path, a)
+        assert open(path, "rb").read() == g[f"fmt_{kind}_bytes"].tobytes(), kind
+        b = getattr(F, "load_graph_" + kind)(path)
+        assert b.dtype == a.dtype and np.array_equal(b, a), kind
+    with pytest.raises(AssertionError):
+        F.load_graph_nodes(str(tmp_path / "missing.bin"))
+    with pytest.raises(AssertionError):
+        F.save_graph_nodes(str(tmp_path / "bad.bin"), np.zeros((3, 2), np.float32))
 
 
 def test_plane_map_partitions_volume():

@@ -1,0 +1,192 @@
+"""GPU parity for the "next" rows: node-insertion machinery and the truncated-region
+mask, through the drop-in classes (C ABI of libofx.so), against (1) golden vectors produced by RUNNING THE REFERENCE
+(its Python EDGraph.update / numba compute_truncated_region and its C++ erode_mesh / sample_nodes compiled from
+/root/reference; oracle/make_golden_graph.py) and (2) the C oracle on larger seeded inputs.  Index / mask outputs:
+bit-exact, acceptance order included."""
+import types
+
+import numpy as np
+import pytest
+
+from conftest import load_golden
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def gg():
+    return load_golden("ref_graph")
+
+
+def _graph(nodes, coverage=0.05, **params):
+    from occlusionfusion_b200 import EDGraph
+    return EDGraph(nodes=nodes, graph_generation_parameters={"node_coverage": float(coverage), **params})
+
+
+def _big_mesh(rng, n=300, hole_frac=0.05):
+    u, v = np.meshgrid(np.linspace(-0.8, 0.8, n), np.linspace(-0.6, 0.6, n), indexing="ij")
+    z = 1.0 + 0.2 * np.sin(4 * u) * np.cos(3 * v)
+    verts = (np.stack([u, v, z], -1).reshape(-1, 3) + rng.uniform(-1e-3, 1e-3, (n * n, 3))).astype(np.float32)
+    ij = np.argwhere(rng.random((n - 1, n - 1)) > hole_frac)
+    a = ij[:, 0] * n + ij[:, 1]
+    faces = np.concatenate([np.stack([a, a + 1, a + n], 1), np.stack([a + 1, a + n + 1, a + n], 1)]).astype(np.int32)
+    return verts, faces
+
+
+def test_erode_mesh_golden_and_oracle(gg, oracle):
+    V = len(gg["mesh_verts"])
+    for it, mn in ((1, 3), (3, 3), (2, 4)):
+        g = _graph(np.zeros((1, 3), np.float32), erosion_num_iterations=it, erosion_min_neighbours=mn)
+        got = g.erode_mesh(gg["mesh_verts"], gg["mesh_faces"])
+        assert got.shape == (V, 1) and got.dtype == bool
+        assert np.array_equal(got.reshape(-1), gg[f"erode_{it}_{mn}"]), (it, mn)
+    # num_iterations = 0 is falsy -> no erosion rounds (embedded_deformation_graph.py:166)
+    got = _graph(np.zeros((1, 3), np.float32)).erode_mesh(gg["mesh_verts"], gg["mesh_faces"], num_iterations=0)
+    assert np.array_equal(got.reshape(-1), gg["erode_0_3"])
+    verts, faces = _big_mesh(np.random.default_rng(5))
+    for it in (1, 4):
+        g = _graph(np.zeros((1, 3), np.float32), erosion_num_iterations=it)
+        assert np.array_equal(g.erode_mesh(verts, faces).reshape(-1), oracle.erode_mesh(len(verts), faces, it, 3))
+
+
+def test_sample_nodes_golden_and_oracle(gg, oracle):
+    g = _graph(np.zeros((1, 3), np.float32), float(gg["coverage"]))
+    for use_ne in (1, 0):
+        pos, idx = g.sample_nodes(gg["mesh_verts"], gg["erode_1_3"], bool(use_ne))
+        assert idx.shape[1] == 1 and idx.dtype == np.int32 and pos.dtype == np.float32
+        assert np.array_equal(idx.reshape(-1), gg[f"sample_idx_{use_ne}"])
+        assert np.array_equal(pos, gg[f"sample_pos_{use_ne}"])
+    # pairs that pin the float32 summation order of the reference's compiled Eigen squaredNorm
+    for (p, q), n in zip(gg["adv_pairs"], gg["adv_n_nodes"]):
+        pos, idx = g.sample_nodes(np.stack([p, q]), np.ones(2, bool))
+        assert len(idx) == n
+    # 90 000 vertices, ~700 nodes, against the oracle; and EDGraph.from_mesh = erode + sample
+    from occlusionfusion_b200 import EDGraph
+    verts, faces = _big_mesh(np.random.default_rng(6))
+    ne = oracle.erode_mesh(len(verts), faces, 1, 3)
+    opos, oidx = oracle.sample_nodes(verts, ne, 0.05, True)
+    built = EDGraph.from_mesh(verts, faces)
+    assert len(oidx) > 300
+    assert np.array_equal(built.node_indices.reshape(-1), oidx) and np.array_equal(built.nodes, opos)
+    # nothing to sample from
+    pos, idx = g.sample_nodes(verts[:64], np.zeros(64, bool))
+    assert pos.shape == (0, 3) and idx.shape == (0, 1)
+
+
+def test_greedy_update_golden_and_oracle(gg, oracle):
+    before = gg["upd_nodes_before"]
+    for cand, after in ((gg["upd_cand"], gg["upd_nodes_after"]), (gg["upd2_cand"], gg["upd2_nodes_after"])):
+        g = _graph(before.copy(), float(gg["coverage"]))
+        assert g.update(gg["mesh_verts"], gg["mesh_faces"], cand) is True
+        assert g.nodes.dtype == np.float32 and np.array_equal(g.nodes, after)
+    # every candidate inside the existing coverage -> no update (embedded_deformation_graph.py:522, 538-539)
+    g = _graph(before.copy(), float(gg["coverage"]))
+    near = np.nonzero(oracle.nearest_node(gg["mesh_verts"], before)[0] < 0.02)[0][:50]
+    assert g.update(gg["mesh_verts"], None, near) is False and len(g.nodes) == len(before)
+    # small analytic case: 1 accepted, 2 too close to 1, 3 accepted, 4 too close to node 1
+    g = _graph(np.array([[0, 0, 0], [1, 0, 0]], np.float32), 0.5)
+    verts = np.array([[0.1, 0, 0], [2, 0, 0], [2.2, 0, 0], [3, 0, 0], [1.4, 0, 0]], np.float32)
+    assert g.update(verts, None, [0]) is False
+    assert g.update(verts, None, [0, 1, 2, 3, 4]) is True
+    assert np.array_equal(g.nodes, np.array([[0, 0, 0], [1, 0, 0], [2, 0, 0], [3, 0, 0]], np.float32))
+    # large: 90 000 vertices, graph on one half, ~40 000 candidates farthest first, against the oracle
+    rng = np.random.default_rng(7)
+    verts, faces = _big_mesh(rng)
+    onodes, _ = oracle.sample_nodes(verts[verts[:, 0] < 0.0], np.ones((verts[:, 0] < 0.0).sum(), bool), 0.05, False)
+    dist, _ = oracle.nearest_node(verts, onodes)
+    cand = np.where(dist > 0.1)[0]
+    cand = cand[np.argsort(dist[cand], kind="stable")[::-1]].astype(np.int32)
+    acc = oracle.greedy_update(verts, cand, onodes, 0.05)
+    g = _graph(onodes.copy(), 0.05)
+    assert g.update(verts, faces, cand) is True
+    assert len(acc) > 100 and np.array_equal(g.nodes[len(onodes):], verts[acc])
+    # same candidates in a shuffled order, with duplicates
+    cand2 = np.concatenate([rng.permutation(cand)[:5000], cand[:100]]).astype(np.int32)
+    acc2 = oracle.greedy_update(verts, cand2, onodes, 0.05)
+    g = _graph(onodes.copy(), 0.05)
+    g.update(verts, faces, cand2)
+    assert np.array_equal(g.nodes[len(onodes):], verts[acc2])
+
+
+def test_find_unreachable_nodes_and_update_graph(gg, oracle):
+    """WarpField.find_unreachable_nodes (warpfield.py:455-485) + update_graph (:487-582) through the device operators."""
+    from occlusionfusion_b200 import TSDFVolume, WarpField
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload("tiny")
+    vol = TSDFVolume(w.bbox, w.max_depth, w.intr, w.fopt, None)
+    nodes = gg["upd_nodes_before"]
+    wf = WarpField(_graph(nodes.copy(), float(gg["coverage"])), vol, None)
+    got = np.asarray(wf.find_unreachable_nodes(gg["mesh_verts"]))
+    dist, idx = oracle.nearest_node(gg["mesh_verts"], nodes)
+    want = np.where(dist > 2 * float(gg["coverage"]))[0]
+    want = want[np.argsort(dist[want])[::-1]]
+    assert np.array_equal(got, want)
+    assert set(got.tolist()) == set(gg["upd_cand"].tolist())            # the reference's own candidate set
+    assert len(wf.find_unreachable_nodes(nodes)) == 0                   # every node reaches itself -> [] (warpfield.py:472)
+    # the device distances and indices themselves
+    import torch
+    from occlusionfusion_b200 import _capi
+    pts = torch.from_numpy(gg["mesh_verts"]).cuda()
+    nd = torch.from_numpy(nodes).cuda()
+    d = torch.empty(len(pts), dtype=torch.float32, device="cuda")
+    i = torch.empty(len(pts), dtype=torch.int32, device="cuda")
+    _capi.check(_capi.load().ofx_nearest_node(_capi.ptr(pts), len(pts), _capi.ptr(nd), len(nd), _capi.ptr(d), _capi.ptr(i),
+                                              _capi.stream_ptr()))
+    assert np.array_equal(d.cpu().numpy(), dist) and np.array_equal(i.cpu().numpy(), idx)
+    assert np.abs(dist - gg["upd_nearest_dist"]).max() <= 1e-7           # vs the reference run (float64 tree cast to f32)
+    # update_graph end to end (erode -> unreachable among the non-eroded -> greedy insert -> re-skin), expected result
+    # assembled from the oracle's stages with the reference's indexing (warpfield.py:500-516)
+    verts, faces, c = gg["mesh_verts"], gg["mesh_faces"], float(gg["coverage"])
+    ne = oracle.erode_mesh(len(verts), faces, 1, 3)
+    dsub, _ = oracle.nearest_node(verts[ne], nodes)
+    cand = np.where(dsub > 2 * c)[0]
+    cand = cand[np.argsort(dsub[cand])[::-1]]
+    acc = oracle.greedy_update(verts, cand, nodes, c)
+    wf.frame_id = vol.frame_id = 0
+    assert wf.update_graph((verts, faces)) is True
+    assert len(acc) > 20 and np.array_equal(wf.graph.nodes, np.concatenate([nodes, verts[acc]]))
+    assert wf.rotations.shape == (len(wf.graph.nodes), 3, 3) and wf.translations.shape == wf.graph.nodes.shape
+    a, wt, v = wf.skin_tsdf()                                            # the volume was re-skinned against the new table
+    ov = oracle.OracleVolume(w.dims, w.origin, w.voxel_size, w.intr, w.trunc)
+    ov.set_graph(wf.graph.nodes, c, wf.graph_neighbours)
+    oa, owt, ovl = ov.skin_tsdf()
+    assert np.array_equal(a, oa) and np.array_equal(wt, owt) and np.array_equal(v, ovl)
+
+
+def test_truncated_region_golden_and_oracle(gg, oracle):
+    import torch
+    from occlusionfusion_b200 import TSDFVolume
+    k4 = load_golden("ref_k4")
+    for key in ("tsdf_0", "tsdf_2"):                                     # Dz = 36: the float4 path
+        for md in (1.2, 0.5):
+            got = TSDFVolume.compute_truncated_region(k4[key], md)
+            want = np.unpackbits(gg[f"trunc_{key}_{md}"])[:got.size].astype(bool).reshape(got.shape)
+            assert got.dtype == bool and np.array_equal(got, want), (key, md)
+    t = gg["trunc_smooth_in"]
+    for md in (1.2, 0.3):
+        got = TSDFVolume.compute_truncated_region(t, md)
+        want = np.unpackbits(gg[f"trunc_smooth_{md}"])[:got.size].astype(bool).reshape(got.shape)
+        assert np.array_equal(got, want), md
+    # ragged Dz (scalar path), degenerate dims, and a CUDA tensor in -> CUDA tensor out
+    rng = np.random.default_rng(8)
+    for dims in ((17, 19, 23), (3, 3, 3), (2, 5, 8), (1, 1, 1), (40, 36, 64)):
+        x = np.clip(rng.normal(0, 0.6, dims), -1, 1).astype(np.float32)
+        got = TSDFVolume.compute_truncated_region(x, 0.8)
+        assert np.array_equal(got, oracle.truncated_region(x, 0.8)), dims
+    xt = torch.from_numpy(x).cuda()
+    out = TSDFVolume.compute_truncated_region(xt, 0.8)
+    assert out.is_cuda and out.dtype == torch.bool and np.array_equal(out.cpu().numpy(), oracle.truncated_region(x, 0.8))
+
+
+def test_truncated_region_of_integrated_volume(oracle):
+    """After real integrations: the mask of the device volume equals the oracle's mask of the oracle's volume."""
+    from occlusionfusion_b200 import TSDFVolume
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload("tiny")
+    vol = TSDFVolume(w.bbox, w.max_depth, w.intr, w.fopt, None)
+    ov = oracle.OracleVolume(w.dims, w.origin, w.voxel_size, w.intr, w.trunc)
+    vol.integrate({"im": w.frame(0), "id": 0})
+    ov.integrate(w.frame(0), True)
+    got = vol.get_truncated_region().cpu().numpy()
+    want = oracle.truncated_region(ov.tsdf, 1.2)
+    assert want.sum() > 100 and np.array_equal(got, want)
