@@ -41,6 +41,9 @@ def parse():
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of a CUDA graph replay")
     ap.add_argument("--no-pipeline", action="store_true", help="N > 1: broadcast -> kernel -> all-gather strictly in sequence")
     ap.add_argument("--cpu-planes", type=int, default=0, help="x-planes in the CPU sample (0 = auto)")
+    ap.add_argument("--graph-ops", action="store_true",
+                    help="time the graph-maintenance / surface-mask operators (SURVEY section 8 rows f2/f3) instead of the "
+                         "integrate path: one JSON line, each operator next to its CPU baseline")
     return ap.parse_args()
 
 
@@ -456,6 +459,140 @@ def bench_e2e(w, vol, wf, sf, frames, ests, args, rank, world, device):
 
 
 # ------------------------------------------------------------------------------------------------
+def bench_graph_ops(args, device):
+    """Rows f2 / f3 (ofx_graph.cu), each operator timed with CUDA events (median of 5 after a warm-up call, inputs resident)
+    next to its CPU baseline on the same input: the reference's own C++ (oracle/_ref/ref_graph.so, kind "reference") for
+    erode_mesh / sample_nodes when it loads, else the oracle port; the oracle port (C, OpenMP where the reference's numba
+    prange is parallel) for the rest.  truncated_region also carries a roofline (5 B/voxel: 4 read + 1 written)."""
+    import ctypes
+    import torch
+    from occlusionfusion_b200 import _capi, TSDFVolume
+    from occlusionfusion_b200.synthetic import Workload
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle as O
+    O.build()
+    ref_graph = None
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "oracle", "_ref"))
+        import ref_graph
+    except Exception as e:      # noqa: BLE001
+        print(f"bench: oracle/_ref/ref_graph.so not loadable ({e}); CPU baselines use the oracle port", file=sys.stderr)
+    lib = _capi.load()
+    S = lambda: _capi.stream_ptr(device)      # noqa: E731
+
+    def gpu_ms(fn, reps=5):
+        fn()
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(reps):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            torch.cuda.synchronize()
+            ts.append(a.elapsed_time(b))
+        return float(np.median(ts))
+
+    def cpu_ms(fn, reps=3):
+        ts = []
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            r = fn()
+            ts.append((time.perf_counter() - t0) * 1e3)
+        return float(np.median(ts)), r
+
+    def mesh(n, rng):
+        u, v = np.meshgrid(np.linspace(-0.8, 0.8, n), np.linspace(-0.6, 0.6, n), indexing="ij")
+        z = 1.0 + 0.2 * np.sin(4 * u) * np.cos(3 * v)
+        verts = (np.stack([u, v, z], -1).reshape(-1, 3) + rng.uniform(-1e-3, 1e-3, (n * n, 3))).astype(np.float32)
+        ij = np.argwhere(rng.random((n - 1, n - 1)) > 0.05)
+        a = ij[:, 0] * n + ij[:, 1]
+        faces = np.concatenate([np.stack([a, a + 1, a + n], 1), np.stack([a + 1, a + n + 1, a + n], 1)]).astype(np.int32)
+        return verts, faces
+
+    peak, peak_src = hbm_peak()
+    cores = O.max_threads()
+    out = {"metric": "graph_ops_ms", "unit": "ms", "higher_is_better": False, "n_gpus": 1, "data": "synthetic",
+           "gpu": torch.cuda.get_device_name(device), "host_cores": os.cpu_count(), "ops": {}}
+    rng = np.random.default_rng(11)
+    cov = 0.05
+    for n in (300, 700):
+        verts, faces = mesh(n, rng)
+        V, F = len(verts), len(faces)
+        v_d, f_d = torch.from_numpy(verts).to(device), torch.from_numpy(faces).to(device)
+        ne = torch.empty(V, dtype=torch.uint8, device=device)
+        t_erode = gpu_ms(lambda: _capi.check(lib.ofx_erode_mesh(_capi.ptr(f_d), F, V, 3, 3, _capi.ptr(ne), S())))
+        if ref_graph is not None:
+            c_erode, ne_ref = cpu_ms(lambda: np.asarray(ref_graph.erode_mesh(verts, faces, 3, 3)).reshape(-1))
+        else:
+            c_erode, ne_ref = cpu_ms(lambda: O.erode_mesh(V, faces, 3, 3))
+        assert np.array_equal(ne.cpu().numpy().astype(bool), ne_ref)
+        idx = torch.empty(V, dtype=torch.int32, device=device)
+        pos = torch.empty((V, 3), dtype=torch.float32, device=device)
+        cnt = torch.zeros(1, dtype=torch.int32, device=device)
+        t_sample = gpu_ms(lambda: _capi.check(lib.ofx_sample_nodes(_capi.ptr(v_d), V, _capi.ptr(ne), ctypes.c_float(cov), 1,
+                                                                   _capi.ptr(idx), _capi.ptr(pos), _capi.ptr(cnt), S())), reps=3)
+        M = int(cnt.item())
+        if ref_graph is not None:
+            def ref_sample():
+                p_, i_ = np.zeros(0, np.float32), np.zeros(0, np.int32)
+                k = ref_graph.sample_nodes(verts, ne_ref.reshape(-1, 1), p_, i_, cov, True, False)
+                return i_[:k].reshape(-1).copy()
+            c_sample, idx_ref = cpu_ms(ref_sample, reps=1)
+        else:
+            c_sample, (_, idx_ref) = cpu_ms(lambda: O.sample_nodes(verts, ne_ref, cov, True), reps=1)
+        assert np.array_equal(idx[:M].cpu().numpy(), idx_ref)
+        nodes = pos[: M // 2].contiguous()                       # a graph that covers about half of the mesh
+        nodes_h = nodes.cpu().numpy()
+        dist = torch.empty(V, dtype=torch.float32, device=device)
+        t_near = gpu_ms(lambda: _capi.check(lib.ofx_nearest_node(_capi.ptr(v_d), V, _capi.ptr(nodes), nodes.shape[0],
+                                                                 _capi.ptr(dist), None, S())))
+        c_near, (d_ref, _) = cpu_ms(lambda: O.nearest_node(verts, nodes_h), reps=1)
+        d = dist.cpu().numpy()
+        assert np.array_equal(d, d_ref)
+        cand = np.where(d > 2 * cov)[0]
+        cand = cand[np.argsort(d[cand])[::-1]].astype(np.int32)
+        c_d = torch.from_numpy(cand).to(device)
+        acc = torch.empty(max(len(cand), 1), dtype=torch.int32, device=device)
+        t_greedy = gpu_ms(lambda: _capi.check(lib.ofx_greedy_insert(_capi.ptr(v_d), V, _capi.ptr(c_d), len(cand), _capi.ptr(nodes),
+                                                                    nodes.shape[0], cov, _capi.ptr(acc), _capi.ptr(cnt), S())), reps=3)
+        c_greedy, acc_ref = cpu_ms(lambda: O.greedy_update(verts, cand, nodes_h, cov), reps=1)
+        k = int(cnt.item())
+        assert np.array_equal(acc[:k].cpu().numpy(), acc_ref)
+        kind = "reference" if ref_graph is not None else "port"
+        out["ops"][f"mesh_{n}x{n}"] = {
+            "V": V, "F": F, "nodes_sampled": M, "graph_nodes": int(nodes.shape[0]), "candidates": int(len(cand)), "inserted": k,
+            "erode_mesh_3_rounds": {"gpu_ms": t_erode, "cpu_ms": c_erode, "cpu_kind": kind, "cpu_cores": 1},
+            "sample_nodes": {"gpu_ms": t_sample, "cpu_ms": c_sample, "cpu_kind": kind, "cpu_cores": 1},
+            "nearest_node": {"gpu_ms": t_near, "cpu_ms": c_near, "cpu_kind": "port", "cpu_cores": 1,
+                             "gpu_gpairs_per_s": V * nodes.shape[0] / t_near / 1e6},
+            "greedy_insert": {"gpu_ms": t_greedy, "cpu_ms": c_greedy, "cpu_kind": "port", "cpu_cores": 1},
+        }
+    # truncated region: (1) the TSDF of a real integration (c2: sphere at 512^3, source frame), (2) a wavy sheet with a 15 % band
+    w = Workload("c2")
+    vol = TSDFVolume(w.bbox, w.max_depth, w.intr, w.fopt, None, device=device)
+    vol.integrate({"im": w.frame(0), "id": 0})
+    D = 512
+    g = torch.Generator(device=device).manual_seed(3)
+    z = torch.linspace(-6, 6, D, device=device).view(1, 1, D).expand(D, D, D)
+    sheet = (z + 0.3 * torch.randn((D, D, 1), device=device, generator=g)).clamp(-1, 1).contiguous()
+    for name, t in (("c2_source_frame_512", vol._tsdf_vol), ("wavy_sheet_512", sheet)):
+        reg = torch.empty(t.shape, dtype=torch.uint8, device=device)
+        dims = [int(x) for x in t.shape]
+        ms = gpu_ms(lambda: _capi.check(lib.ofx_truncated_region(_capi.ptr(t), dims[0], dims[1], dims[2], 1.2, _capi.ptr(reg), S())))
+        th = t.cpu().numpy()
+        c_ms, want = cpu_ms(lambda: O.truncated_region(th, 1.2), reps=2)
+        assert np.array_equal(reg.cpu().numpy().astype(bool), want)
+        gbs = 5.0 * t.numel() / ms / 1e6
+        out["ops"][f"truncated_region_{name}"] = {
+            "gpu_ms": ms, "cpu_ms": c_ms, "cpu_kind": "port", "cpu_cores": cores, "voxels": int(t.numel()),
+            "band_frac": float((t.abs() <= 0.9).float().mean()), "region_frac": float(want.mean()),
+            "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
+                         "peak_source": peak_src, "bytes_formula": "5*N (4 read + 1 written)"}}
+    out["parity"] = "every GPU result above was compared with its CPU baseline's result: identical"
+    print(json.dumps(out), flush=True)
+
+
 def main():
     args = parse()
     real_stdout = os.fdopen(os.dup(1), "w")
@@ -483,6 +620,13 @@ def main():
             dist.init_process_group("nccl", device_id=device)
     from occlusionfusion_b200.synthetic import Workload
 
+    if args.graph_ops:
+        if rank == 0:
+            bench_graph_ops(args, device)
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
     main_res = bench_workload(args.workload, args, rank, world, device)
     also = {}
     if world == 1 and args.also:
