@@ -143,7 +143,7 @@ __global__ void __launch_bounds__(256) greedy_prefilter_kernel(const float *__re
 // instead of at every live candidate.  The next head is found by scanning the live words forward from the previous head
 // (the head only moves forward: one pass over the words in total).  Slot collisions only add candidates to a sweep; the
 // distance test decides.
-constexpr int GREEDY_CELLS = 1 << 16;
+constexpr int GREEDY_CELLS = 1 << 14;   // slots; collisions only lengthen a sweep (v2 used 2^16: the scan alone took 110 us)
 
 __device__ __forceinline__ int cell_coord(float p, double inv_cell)
 {
@@ -181,7 +181,11 @@ __global__ void __launch_bounds__(1024) cell_scan_kernel(const int *__restrict__
     int local[PER];
     int sum = 0;
 #pragma unroll
-    for (int k = 0; k < PER; ++k) { local[k] = count[tid * PER + k]; sum += local[k]; }
+    for (int k = 0; k < PER; k += 4) {
+        const int4 c4 = *reinterpret_cast<const int4 *>(count + tid * PER + k);
+        local[k] = c4.x; local[k + 1] = c4.y; local[k + 2] = c4.z; local[k + 3] = c4.w;
+        sum += (c4.x + c4.y) + (c4.z + c4.w);
+    }
     int incl = sum;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
@@ -378,22 +382,31 @@ __global__ void __launch_bounds__(256) truncated_region_vec_kernel(const float *
     const int lane = threadIdx.x & 31;
     const int warps = gridDim.x * (blockDim.x >> 5);
     const int qpr = D >> 2;                                                // quads per row
+    const int ipr = (qpr + 31) >> 5;                                       // 32-quad chunks per row
     const int rows = W * H;
     const float INF = __int_as_float(0x7f800000);
-    for (int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); r < rows; r += warps) {
+    // Work items of this warp: (row, chunk) pairs, rows r0, r0 + warps, ...  Three items of look-ahead, carried ACROSS row
+    // boundaries (v2 restarted the look-ahead at every row: half of its warp-state samples sat on that first load).
+    int fr = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), fc = 0;  // position of the next fetch
+    auto fetch = [&]() -> float4 {
+        float4 v = make_float4(1.f, 1.f, 1.f, 1.f);
+        const int q = (fc << 5) + lane;
+        if (fr < rows && q < qpr) v = __ldg(reinterpret_cast<const float4 *>(t + (int64_t)fr * D) + q);
+        if (++fc == ipr) { fc = 0; fr += warps; }
+        return v;
+    };
+    int r = fr, ch = 0;                                                    // position of the item being examined
+    float4 n1 = fetch(), n2 = fetch(), n3 = fetch();
+    while (r < rows) {
         const int w = r / H, h = r - w * H;
         const bool row_in = h > 0 && h < H - 1 && w > 0 && w < W - 1;
         const float *rowp = t + (int64_t)r * D;
         uint8_t *outp = out + (int64_t)r * D;
-        float4 nxt = make_float4(1.f, 1.f, 1.f, 1.f), nxt2 = nxt;         // two quads of look-ahead: ~48 KB of loads in flight per SM
-        if (lane < qpr) nxt = __ldg(reinterpret_cast<const float4 *>(rowp) + lane);
-        if (lane + 32 < qpr) nxt2 = __ldg(reinterpret_cast<const float4 *>(rowp) + lane + 32);
-        for (int q0 = 0; q0 < qpr; q0 += 32) {
-            const int q = q0 + lane, d0 = q << 2;
+        for (; ch < ipr; ++ch) {
+            const int q = (ch << 5) + lane, d0 = q << 2;
             const bool live = q < qpr;
-            const float4 c4 = nxt;
-            nxt = nxt2;
-            if (q + 64 < qpr) nxt2 = __ldg(reinterpret_cast<const float4 *>(rowp) + q + 64);
+            const float4 c4 = n1;
+            n1 = n2; n2 = n3; n3 = fetch();
             const float c[4] = {c4.x, c4.y, c4.z, c4.w};
             bool cand[4];
 #pragma unroll
@@ -430,6 +443,8 @@ __global__ void __launch_bounds__(256) truncated_region_vec_kernel(const float *
             }
             if (live) *reinterpret_cast<uchar4 *>(outp + d0) = res;
         }
+        ch = 0;
+        r += warps;
     }
 }
 
