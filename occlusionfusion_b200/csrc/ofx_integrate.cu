@@ -220,6 +220,11 @@ brick_cull_kernel(GraphArgs ga, const int4 *__restrict__ active_desc, int n_acti
 #ifndef OFX_N_SLOTS
 #define OFX_N_SLOTS 1
 #endif
+// 1: the consumers block in hardware on a named barrier ("full") that the producer warp arrives at once the brick's TMA
+// bytes have landed, instead of all eight consumer warps polling the mbarrier (N_SLOTS == 1 only)
+#ifndef OFX_FULL_BAR
+#define OFX_FULL_BAR 0
+#endif
 #ifndef OFX_MIN_CTAS
 #define OFX_MIN_CTAS 4
 #endif
@@ -252,6 +257,8 @@ __device__ __forceinline__ void flush_counters(unsigned *s_cnt, unsigned long lo
 constexpr int RING_RECS = 256;                              // > MAX_BRICK_NODES: the largest brick fits an empty ring
 constexpr int CONSUMER_WARPS = BRICK_THREADS / 32;          // 8
 constexpr int PERSISTENT_THREADS = BRICK_THREADS + 32;      // + 1 producer warp
+constexpr int FULL_BAR_ID = 2 + OFX_N_SLOTS;                // named barriers: 0 __syncthreads, 1..N_SLOTS room, 1+N_SLOTS consumers only
+static_assert(!OFX_FULL_BAR || OFX_N_SLOTS == 1, "OFX_FULL_BAR needs a single stage");
 
 struct SlotInfo {
     int lx0, iy0, iz0;
@@ -293,6 +300,9 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
         int rel = 0;                  // iterations [0, rel) have been released by the consumers
         int head = 0, tail = 0;       // ring: next free record / first record of the oldest unreleased brick
         bool wrapped = false;         // in use: [tail, head) when !wrapped, [tail, end) + [0, head) when wrapped
+#if OFX_FULL_BAR
+        int pending_it = -1;          // brick whose bytes are in flight and whose consumers have not been woken yet
+#endif
         for (int it = 0;; ++it) {
             const int slot = it % N_SLOTS;
             // everything that does not depend on the hand-back happens before waiting for it: the brick's
@@ -313,6 +323,15 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
                     rec_src = ga.node_rec + (int64_t)__ldg(ga.brick_nodes + o + lane) * NODE_REC_FLOATS + NODE_XFORM_OFFSET;
                 if (lane < 5 * KP / 4) bulk_prefetch_l2(slot_src + lane * 4096, 4096u);
             }
+#if OFX_FULL_BAR
+            if (pending_it >= 0) {
+                // the previous brick's bytes have landed -> wake its consumers (they block on the named barrier)
+                mbar_wait(&bar_data[pending_it % N_SLOTS], (uint32_t)(pending_it / N_SLOTS) & 1u);
+                __threadfence_block();
+                named_bar_arrive(FULL_BAR_ID, PERSISTENT_THREADS);
+                pending_it = -1;
+            }
+#endif
             // room: a free descriptor slot and n_used contiguous records
             int start = -1;
             while (true) {
@@ -339,7 +358,13 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
                 }
             }
             if (!more) {
+#if OFX_FULL_BAR
+                if (lane == 0) s_info[slot].n_used = -1;
+                __threadfence_block();
+                named_bar_arrive(FULL_BAR_ID, PERSISTENT_THREADS);
+#else
                 if (lane == 0) { s_info[slot].n_used = -1; mbar_arrive(&bar_data[slot]); }
+#endif
                 break;
             }
             if (lane == 0) {
@@ -362,6 +387,9 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
                 mbar_wait(&bar_data[slot], (uint32_t)(it / N_SLOTS) & 1u);
                 dbg_b += gtime() - t2;
             }
+#endif
+#if OFX_FULL_BAR
+            pending_it = it;
 #endif
             int f = 0;
             if (lane == 0) f = atomicAdd(counters + 1, 1);
@@ -386,7 +414,12 @@ fused_warped_persistent(VolumeGeom g, float *__restrict__ tsdf, float *__restric
 #if OFX_TIMING
         const unsigned long long t0 = gtime();
 #endif
+#if OFX_FULL_BAR
+        (void)ph;
+        named_bar_sync(FULL_BAR_ID, PERSISTENT_THREADS);   // the producer has seen this brick's TMA bytes land (or: no more bricks)
+#else
         mbar_wait(&bar_data[slot], ph);            // descriptor written and the TMA bytes of this brick have landed
+#endif
 #if OFX_TIMING
         const unsigned long long t1 = gtime();
         dbg_a += t1 - t0; ++dbg_n;

@@ -190,3 +190,90 @@ def test_truncated_region_of_integrated_volume(oracle):
     got = vol.get_truncated_region().cpu().numpy()
     want = oracle.truncated_region(ov.tsdf, 1.2)
     assert want.sum() > 100 and np.array_equal(got, want)
+
+
+def _hemisphere_mesh(w, nt=40, nphi=80):
+    """The camera-facing hemisphere of the band scene as a (theta, phi) grid mesh."""
+    th = np.linspace(0.02, np.pi / 2 - 0.02, nt)
+    ph = np.linspace(0, 2 * np.pi, nphi, endpoint=False)
+    T, P = np.meshgrid(th, ph, indexing="ij")
+    d = np.stack([np.sin(T) * np.cos(P), np.sin(T) * np.sin(P), -np.cos(T)], -1).reshape(-1, 3)
+    verts = (w.centre + w.radius * d).astype(np.float32)
+    i, j = np.meshgrid(np.arange(nt - 1), np.arange(nphi), indexing="ij")
+    a, b = (i * nphi + j).ravel(), (i * nphi + (j + 1) % nphi).ravel()
+    faces = np.concatenate([np.stack([a, b, a + nphi], 1), np.stack([b, b + nphi, a + nphi], 1)]).astype(np.int32)
+    return verts, faces
+
+
+def test_sequence_with_update_graph_on_device(oracle):
+    """BASELINE config 3 in small, with the node insertion itself on the device: the graph starts on 60 % of the scene,
+    WarpField.update_graph (erode -> unreachable vertices -> greedy insertion -> re-skin) extends it from the canonical mesh
+    between frames, and every frame stays bit-identical to the oracle driven through the same stages."""
+    from occlusionfusion_b200 import TSDFVolume, WarpField
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload("tiny")
+    verts, faces = _hemisphere_mesh(w)
+    vol = TSDFVolume(w.bbox, w.max_depth, w.intr, w.fopt, None)
+    ov = oracle.OracleVolume(w.dims, w.origin, w.voxel_size, w.intr, w.trunc)
+    nodes = w.nodes[: int(0.6 * w.M)].copy()
+    wf = WarpField(_graph(nodes, w.coverage), vol, None)
+    wf.graph_neighbours = w.K
+    vol.warpfield = wf
+    ov.set_graph(nodes, w.coverage, w.K)
+    grown = []
+    for f in range(7):
+        if f in (3, 5):                                          # between frames: warp field and volume agree on the frame id
+            ne = oracle.erode_mesh(len(verts), faces, 1, 3)
+            d, _ = oracle.nearest_node(verts[ne], wf.graph.nodes)
+            cand = np.where(d > 2 * w.coverage)[0]
+            cand = cand[np.argsort(d[cand])[::-1]]
+            acc = oracle.greedy_update(verts, cand, wf.graph.nodes, w.coverage)
+            want = np.concatenate([wf.graph.nodes, verts[acc]]) if len(acc) else wf.graph.nodes
+            assert wf.update_graph((verts, faces)) is (len(acc) > 0)
+            assert np.array_equal(wf.graph.nodes, want)
+            grown.append(len(acc))
+            ov.set_graph(wf.graph.nodes, w.coverage, w.K)
+        im = w.frame(f)
+        if f > 0:
+            est = w.estimate(f, wf.graph.nodes)
+            wf.update_transformations(est)
+            ov.set_transforms(est["node_rotations"], wf.translations)
+        vol.integrate({"im": im, "id": f})
+        n = ov.integrate(im, f == 0)
+        assert vol.last_stats()["updated"] == n, f
+    assert grown[0] > 5 and grown[1] == 0                        # the first update covers the scene, the second finds nothing
+    t, c, wt = vol.get_volume()
+    assert np.array_equal(wt, ov.weight) and np.array_equal(c, ov.colour) and np.array_equal(t, ov.tsdf)
+
+
+def test_graph_capi_edge_cases():
+    """Empty inputs and bad arguments at the C ABI: nothing launches, counts come back zero, errors carry a message."""
+    import ctypes
+    import torch
+    from occlusionfusion_b200 import _capi
+    lib, S, P = _capi.load(), _capi.stream_ptr, _capi.ptr
+    dev = torch.device("cuda")
+    pts = torch.rand((8, 3), device=dev)
+    n_out = torch.full((1,), 7, dtype=torch.int32, device=dev)
+    acc = torch.empty(8, dtype=torch.int32, device=dev)
+    assert lib.ofx_nearest_node(None, 0, P(pts), 8, None, None, S()) == 0                       # no points
+    assert lib.ofx_nearest_node(P(pts), 8, P(pts), 0, P(pts), None, S()) != 0                   # no nodes
+    assert b"ofx_nearest_node" in lib.ofx_last_error()
+    assert lib.ofx_greedy_insert(P(pts), 8, None, 0, P(pts), 8, 0.05, None, P(n_out), S()) == 0  # no candidates
+    assert int(n_out.item()) == 0
+    n_out.fill_(7)
+    assert lib.ofx_sample_nodes(None, 0, None, ctypes.c_float(0.05), 1, None, None, P(n_out), S()) == 0
+    assert int(n_out.item()) == 0
+    assert lib.ofx_sample_nodes(P(pts), 8, None, ctypes.c_float(0.05), 1, P(acc), None, P(n_out), S()) != 0   # mask required
+    ne = torch.full((8,), 9, dtype=torch.uint8, device=dev)
+    assert lib.ofx_erode_mesh(None, 0, 8, 1, 3, P(ne), S()) == 0 and int(ne.sum()) == 0           # no faces: everything eroded
+    bad = torch.tensor([[0, 1, 99], [0, 1, 2], [1, 2, 3], [0, 2, 3], [0, 1, 3]], dtype=torch.int32, device=dev)
+    assert lib.ofx_erode_mesh(P(bad), 5, 8, 0, 3, P(ne), S()) == 0                                # out-of-range face ignored
+    assert ne.cpu().tolist() == [1, 1, 1, 1, 0, 0, 0, 0]
+    assert lib.ofx_truncated_region(None, 0, 4, 4, 1.2, None, S()) == 0
+    assert lib.ofx_truncated_region(None, 4, 4, 4, 1.2, None, S()) != 0
+    # no existing nodes (M = 0): plain greedy coverage sampling in candidate order
+    v = torch.tensor([[0, 0, 0], [0.01, 0, 0], [1, 0, 0], [1, 0.02, 0]], dtype=torch.float32, device=dev)
+    cand = torch.tensor([3, 0, 1, 2], dtype=torch.int32, device=dev)
+    assert lib.ofx_greedy_insert(P(v), 4, P(cand), 4, None, 0, 0.05, P(acc), P(n_out), S()) == 0
+    assert int(n_out.item()) == 2 and acc[:2].cpu().tolist() == [3, 0]
