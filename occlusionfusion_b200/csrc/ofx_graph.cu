@@ -345,7 +345,13 @@ __global__ void __launch_bounds__(256) erode_mark_kernel(const int32_t *__restri
 // (double)|nb - c| > max_diff) are done in float32 against the largest float <= the bound (same truth value for every
 // float).  "Some neighbour differs by more than max_diff" is decided from the min and max over the 3x3x3 block:
 // fl(nb - c) is monotone in nb, so the largest |nb - c| is fl(max - c) or fl(c - min).
-struct TruncBounds { float band, diff; };   // float_at_most(0.9), float_at_most(max_diff)
+struct TruncBounds { float band, diff; };
+#ifndef OFX_TR_CTAS
+#define OFX_TR_CTAS 4          // CTAs per SM in the grid of the vector kernel = the resident count (56-64 registers); 8 and 16 measured 4-8 % slower
+#endif
+#ifndef OFX_TR_STREAM
+#define OFX_TR_STREAM 0        // 1: evict-first loads / stores for the streamed volume (measured: no difference)
+#endif   // float_at_most(0.9), float_at_most(max_diff)
 
 // scalar form (any Dz): one thread per voxel
 __global__ void __launch_bounds__(256) truncated_region_scalar_kernel(const float *__restrict__ t, int W, int H, int D, TruncBounds b,
@@ -391,7 +397,11 @@ __global__ void __launch_bounds__(256) truncated_region_vec_kernel(const float *
     auto fetch = [&]() -> float4 {
         float4 v = make_float4(1.f, 1.f, 1.f, 1.f);
         const int q = (fc << 5) + lane;
+#if OFX_TR_STREAM
+        if (fr < rows && q < qpr) v = __ldcs(reinterpret_cast<const float4 *>(t + (int64_t)fr * D) + q);
+#else
         if (fr < rows && q < qpr) v = __ldg(reinterpret_cast<const float4 *>(t + (int64_t)fr * D) + q);
+#endif
         if (++fc == ipr) { fc = 0; fr += warps; }
         return v;
     };
@@ -441,7 +451,11 @@ __global__ void __launch_bounds__(256) truncated_region_vec_kernel(const float *
                 }
                 res = make_uchar4(rb[0], rb[1], rb[2], rb[3]);
             }
+#if OFX_TR_STREAM
+            if (live) __stcs(reinterpret_cast<uchar4 *>(outp + d0), res);
+#else
             if (live) *reinterpret_cast<uchar4 *>(outp + d0) = res;
+#endif
         }
         ch = 0;
         r += warps;
@@ -568,7 +582,7 @@ extern "C" int ofx_truncated_region(const float *tsdf, int32_t Dx, int32_t Dy, i
     cudaStream_t s = (cudaStream_t)stream;
     const bool vec = Dz % 4 == 0 && Dz >= 32 && (int64_t)Dx * Dy < INT_MAX && (((uintptr_t)tsdf & 15) == 0) && (((uintptr_t)region & 3) == 0);
     const TruncBounds b{float_at_most(0.9), float_at_most(max_diff)};
-    if (vec) truncated_region_vec_kernel<<<graph_grid_for((int64_t)Dx * Dy * 32, 256, 8), 256, 0, s>>>(tsdf, Dx, Dy, Dz, b, region);
+    if (vec) truncated_region_vec_kernel<<<graph_grid_for((int64_t)Dx * Dy * 32, 256, OFX_TR_CTAS), 256, 0, s>>>(tsdf, Dx, Dy, Dz, b, region);
     else truncated_region_scalar_kernel<<<graph_grid_for(n, 256, 8), 256, 0, s>>>(tsdf, Dx, Dy, Dz, b, region);
     OFX_LAUNCH_CHECK();
     return 0;
