@@ -163,6 +163,29 @@ int ofx_erode_mesh(const int32_t *faces, int32_t F, int32_t V, int32_t n_iterati
 int ofx_truncated_region(const float *tsdf, int32_t Dx, int32_t Dy, int32_t Dz, double max_diff,
                          uint8_t *region, void *stream);
 
+/* ---- host half of the graph builder (HOST pointers; no device work) ------------------------------------------ */
+/* compute_edges_geodesic (csrc/cpu/graph_proc.cpp:155-300, binding csrc/main.cpp:30; callers
+ * embedded_deformation_graph.py:226-233, 313-320): for every node (node_idx: its mesh vertex, < 0 = skip) walk the mesh
+ * outwards in order of geodesic distance until max_neighbours other nodes were met; edges (M, max_neighbours) i32 and
+ * weights / distances (same shape, f32) are filled for the neighbours found (the caller pre-fills -1 / 0 / 0 as the
+ * reference does), node_to_vertex (M, V) f32 receives the distance of every vertex visited (may be NULL).
+ * only_valid: vertices with valid[v] == 0 are never entered (reaching one is an error; the reference exits the process).
+ * enforce_total == 0 limits the walk to 2 * node_coverage.  n_threads <= 0: all host threads (nodes are independent). */
+int ofx_compute_edges_geodesic_host(const float *verts_host, const uint8_t *valid_host, int32_t V,
+                                    const int32_t *faces_host, int32_t F, const int32_t *node_idx_host,
+                                    int32_t M, int32_t max_neighbours, float node_coverage,
+                                    int32_t *edges_host, float *weights_host, float *distances_host,
+                                    float *node_to_vertex_host, int32_t only_valid,
+                                    int32_t enforce_total, int32_t n_threads);
+/* node_and_edge_clean_up (graph_proc.cpp:388-438, binding main.cpp:32): clears valid_mask (M,) u8 of every node left
+ * with at most one neighbour, repeatedly, in node order. */
+int ofx_node_and_edge_clean_up_host(const int32_t *edges_host, int32_t M, int32_t E,
+                                    uint8_t *valid_mask_host);
+/* compute_clusters (graph_proc.cpp:440-481, binding main.cpp:33): connected components of the undirected edge set,
+ * numbered by their smallest node; clusters (M,) i32, sizes (capacity M, may be NULL), *n_clusters. */
+int ofx_compute_clusters_host(const int32_t *edges_host, int32_t M, int32_t E, int32_t *clusters_host,
+                              int32_t *sizes_host, int32_t *n_clusters_host);
+
 /* ---- multi-GPU plumbing ------------------------------------------------------------------------ */
 /* Copies `bytes` (a multiple of 16, both pointers 16-byte aligned) from `src` to `dst` with `ctas`
  * thread blocks.  `src` may be a PEER pointer (another GPU's buffer mapped into this process through

@@ -127,6 +127,54 @@ def main():
     out["adv_pairs"], out["adv_n_nodes"] = pairs, np.asarray(res, np.int32)
     out["coverage"] = np.float64(coverage)
 
+    # ---- f2: geodesic edges, clean-up, clusters (reference C++) --------------------------------------------------------
+    node_idx = out["sample_idx_1"].reshape(-1, 1).astype(np.int32)
+    M, V = len(node_idx), len(verts)
+
+    def ref_edges(valid, nidx, E, cov, only_valid, enforce):
+        e = -np.ones((len(nidx), E), np.int32)
+        w_ = np.zeros((len(nidx), E), np.float32)
+        d_ = np.zeros((len(nidx), E), np.float32)
+        n2v = -np.ones((len(nidx), V), np.float32)
+        ref_graph.compute_edges_geodesic(verts, valid, faces, nidx, E, cov, e, w_, d_, n2v, only_valid, enforce)
+        return e, w_, d_, n2v
+
+    cases = {"a": (ne, node_idx, 8, coverage, True, True),                        # create_graph_from_mesh, edg.py:226-233
+             "b": (np.ones((V, 1), bool), node_idx[::3].copy(), 4, 2 * coverage, False, True),   # pyramid level, edg.py:313-320
+             "c": (ne, node_idx, 8, coverage, True, False)}                       # walk limited to 2 * coverage
+    for name, (valid, nidx, E, cov, ov_, enf) in cases.items():
+        e, w_, d_, n2v = ref_edges(valid, nidx, E, cov, ov_, enf)
+        out[f"geo_{name}_node_idx"], out[f"geo_{name}_valid"] = nidx, valid.reshape(-1)
+        out[f"geo_{name}_params"] = np.array([E, cov, ov_, enf], np.float64)
+        out[f"geo_{name}_edges"], out[f"geo_{name}_weights"], out[f"geo_{name}_dist"] = e, w_, d_
+        out[f"geo_{name}_n2v_count"] = (n2v != -1).sum(1).astype(np.int32)
+        out[f"geo_{name}_n2v_sum"] = np.where(n2v != -1, n2v, 0).astype(np.float64).sum(1)
+        out[f"geo_{name}_n2v_head"] = n2v[:6].copy()
+        mask = np.ones((len(nidx), 1), bool)
+        ref_graph.node_and_edge_clean_up(e, mask)
+        out[f"geo_{name}_clean"] = mask.reshape(-1)
+        clusters = -np.ones((len(nidx), 1), np.int32)
+        sizes = ref_graph.compute_clusters(e, clusters)
+        out[f"geo_{name}_clusters"], out[f"geo_{name}_cluster_sizes"] = clusters.reshape(-1), np.asarray(sizes, np.int32)
+    # clean-up / clusters on random sparse edge tables (several components, nodes that lose their neighbours over several
+    # passes, nodes that arrive invalid)
+    for k in range(6):
+        Mr, Er = 40 + 10 * k, 4
+        e = -np.ones((Mr, Er), np.int32)
+        for i in range(Mr):
+            deg = rng.choice([0, 1, 1, 2, 2, 3, 4])
+            lo, hi = (i // 14) * 14, min(Mr, (i // 14) * 14 + 14)          # components of at most 14 nodes
+            nb = rng.choice([j for j in range(lo, hi) if j != i], size=min(deg, hi - lo - 1), replace=False)
+            e[i, :len(nb)] = nb
+        m0 = np.ones((Mr, 1), bool)
+        m0[rng.choice(Mr, 3, replace=False)] = False
+        m1 = m0.copy()
+        ref_graph.node_and_edge_clean_up(e, m1)
+        cl = -np.ones((Mr, 1), np.int32)
+        sizes = ref_graph.compute_clusters(e, cl)
+        out[f"rnd{k}_edges"], out[f"rnd{k}_mask_in"], out[f"rnd{k}_mask_out"] = e, m0.reshape(-1), m1.reshape(-1)
+        out[f"rnd{k}_clusters"], out[f"rnd{k}_sizes"] = cl.reshape(-1), np.asarray(sizes, np.int32)
+
     # ---- f2: find_unreachable_nodes + EDGraph.update (reference Python) -----------------------------------------
     # graph covers the left part of the mesh; the right part is "newly revealed"
     left = verts[verts[:, 0] < 0.05]

@@ -1,0 +1,85 @@
+"""CPU: the host half of the graph builder in libofx.so (ofx_compute_edges_geodesic_host, ofx_node_and_edge_clean_up_host,
+ofx_compute_clusters_host) through the reference's call signatures, against golden vectors produced by the reference's own
+C++ (csrc/cpu/graph_proc.cpp compiled from /root/reference, oracle/make_golden_graph.py).  Edges, masks and clusters:
+identical; weights and distances: bit-identical (same float32 operation order, same libm exp)."""
+import numpy as np
+import pytest
+
+from conftest import load_golden
+
+
+@pytest.fixture(scope="module")
+def gg():
+    return load_golden("ref_graph")
+
+
+def _run_geo(gg, name, n_threads=0):
+    from occlusionfusion_b200.graph_proc import compute_edges_geodesic_c
+    E, cov, only_valid, enforce = gg[f"geo_{name}_params"]
+    nidx = gg[f"geo_{name}_node_idx"]
+    M, V = len(nidx), len(gg["mesh_verts"])
+    e = -np.ones((M, int(E)), np.int32)
+    w = np.zeros((M, int(E)), np.float32)
+    d = np.zeros((M, int(E)), np.float32)
+    n2v = -np.ones((M, V), np.float32)
+    compute_edges_geodesic_c(gg["mesh_verts"], gg[f"geo_{name}_valid"], gg["mesh_faces"], nidx, int(E), float(cov), e, w, d, n2v,
+                             bool(only_valid), bool(enforce), n_threads)
+    return e, w, d, n2v
+
+
+@pytest.mark.parametrize("name", ["a", "b", "c"])
+def test_geodesic_edges_match_reference(gg, name):
+    e, w, d, n2v = _run_geo(gg, name)
+    assert np.array_equal(e, gg[f"geo_{name}_edges"])
+    assert np.array_equal(d, gg[f"geo_{name}_dist"]) and np.array_equal(w, gg[f"geo_{name}_weights"])
+    assert np.array_equal((n2v != -1).sum(1), gg[f"geo_{name}_n2v_count"])
+    assert np.array_equal(np.where(n2v != -1, n2v, 0).astype(np.float64).sum(1), gg[f"geo_{name}_n2v_sum"])
+    assert np.array_equal(n2v[:6], gg[f"geo_{name}_n2v_head"])
+    e1, w1, d1, n1 = _run_geo(gg, name, n_threads=1)                    # the thread count does not change anything
+    assert np.array_equal(e, e1) and np.array_equal(w, w1) and np.array_equal(d, d1) and np.array_equal(n2v, n1)
+    if name == "c":
+        assert (e == -1).any() and (d <= 2 * 0.05 + 1e-6).all()          # the walk stops at 2 * node_coverage
+
+
+def test_clean_up_and_clusters_match_reference(gg):
+    from occlusionfusion_b200.graph_proc import compute_clusters_c, node_and_edge_clean_up_c
+    names = [f"geo_{n}" for n in "abc"]
+    for n in names:
+        e = gg[f"{n}_edges"]
+        mask = np.ones((len(e), 1), bool)
+        node_and_edge_clean_up_c(e, mask)
+        assert np.array_equal(mask.reshape(-1), gg[f"{n}_clean"])
+        cl = -np.ones((len(e), 1), np.int32)
+        assert compute_clusters_c(e, cl) == gg[f"{n}_cluster_sizes"].tolist()
+        assert np.array_equal(cl.reshape(-1), gg[f"{n}_clusters"])
+    removed = 0
+    for k in range(6):
+        e = gg[f"rnd{k}_edges"]
+        mask = gg[f"rnd{k}_mask_in"].reshape(-1, 1).copy()
+        node_and_edge_clean_up_c(e, mask)
+        assert np.array_equal(mask.reshape(-1), gg[f"rnd{k}_mask_out"]), k
+        removed += int(gg[f"rnd{k}_mask_in"].sum() - mask.sum())
+        cl = -np.ones((len(e), 1), np.int32)
+        assert compute_clusters_c(e, cl) == gg[f"rnd{k}_sizes"].tolist(), k
+        assert np.array_equal(cl.reshape(-1), gg[f"rnd{k}_clusters"]), k
+    assert removed > 100
+
+
+def test_graph_host_argument_errors(gg):
+    from occlusionfusion_b200._capi import OfxError
+    from occlusionfusion_b200.graph_proc import compute_clusters_c, compute_edges_geodesic_c
+    v, f = gg["mesh_verts"], gg["mesh_faces"].copy()
+    e, w, d = -np.ones((2, 4), np.int32), np.zeros((2, 4), np.float32), np.zeros((2, 4), np.float32)
+    f[0, 0] = len(v) + 5
+    with pytest.raises(OfxError, match="out of range"):
+        compute_edges_geodesic_c(v, np.ones(len(v), bool), f, np.array([3, 9], np.int32), 4, 0.05, e, w, d, None, True, True)
+    with pytest.raises(TypeError):
+        compute_edges_geodesic_c(v, np.ones(len(v), bool), gg["mesh_faces"], np.array([3, 9]), 4, 0.05, e.astype(np.int64), w, d,
+                                 None, True, True)
+    with pytest.raises(OfxError, match="out of range"):
+        compute_clusters_c(np.array([[5, -1]], np.int32), -np.ones((1, 1), np.int32))
+    # a node whose vertex is an invalid (eroded) one: the reference exits the process, here it is an error
+    valid = np.ones(len(v), bool)
+    valid[3] = False
+    with pytest.raises(OfxError, match="not a valid vertex"):
+        compute_edges_geodesic_c(v, valid, gg["mesh_faces"], np.array([3, 9], np.int32), 4, 0.05, e, w, d, None, True, True)
