@@ -6,8 +6,10 @@ half of graph creation (`erode_mesh` :153-172, node sampling :186-206).
 These run on the device through libofx.so (ofx_erode_mesh, ofx_sample_nodes, ofx_greedy_insert:
 include/ofx.h), replacing NeuralNRT._C.erode_mesh / sample_nodes (csrc/cpu/graph_proc.cpp:17-136) and
 the Python loop of `update`; results are identical to the serial code, acceptance order included.
-Geodesic edges, clusters and the pyramid (:207-331, graph_proc.cpp:155-481) are not rebuilt (the
-fusion path reads only `nodes`); nodes may also be supplied by the caller.
+Geodesic edges, the "not enough neighbours" clean-up, clusters and the pyramid (:207-480,
+graph_proc.cpp:155-481) are host work in the reference and here: native host code in libofx.so
+(graph_proc.py, `*_host` entry points) under Python mirrors of the reference's methods.  Nodes may also
+be supplied by the caller (the fusion path itself reads only `nodes`).
 """
 import ctypes
 import logging
@@ -16,6 +18,7 @@ import numpy as np
 import torch
 
 from . import _capi
+from .graph_proc import compute_clusters_c, compute_edges_geodesic_c, node_and_edge_clean_up_c
 
 DEFAULT_GRAPH_PARAMETERS = {           # embedded_deformation_graph.py:62-73
     "max_triangle_distance": 0.05,
@@ -61,6 +64,132 @@ class EDGraph:
         g.vertices, g.faces = vertices, faces
         g.nodes, g.node_indices = g.sample_nodes(vertices, non_eroded)
         return g
+
+    def create_graph_from_mesh(self, vertices, faces):
+        """The whole of embedded_deformation_graph.py:174-256: erode, sample nodes (device), geodesic edges between them
+        (host threads), drop nodes with too few neighbours, clusters, pyramid.  Sets nodes, node_indices, edges,
+        edges_weights, edges_distances, clusters, pyd, vertices, faces."""
+        num_neighbours = self.graph_generation_parameters["num_neighbours"]
+        node_coverage = self.graph_generation_parameters["node_coverage"]
+        assert vertices.shape[0] > 0 and faces.shape[0] > 0                                   # :184
+        valid_vertices = self.erode_mesh(vertices, faces)
+        node_coords, node_indices = self.sample_nodes(vertices, valid_vertices)
+        num_nodes = node_coords.shape[0]
+        graph_edges = -np.ones((num_nodes, num_neighbours), dtype=np.int32)                   # :217-220
+        graph_edges_weights = np.zeros((num_nodes, num_neighbours), dtype=np.float32)
+        graph_edges_distances = np.zeros((num_nodes, num_neighbours), dtype=np.float32)
+        # node_to_vertex_distances (num_nodes x num_vertices) is only scratch in the reference (:221, 247): not materialised
+        compute_edges_geodesic_c(vertices, np.ones_like(valid_vertices), faces, node_indices, num_neighbours, node_coverage,
+                                 graph_edges, graph_edges_weights, graph_edges_distances, None, True, True)   # :224-233
+        self.vertices, self.faces = vertices, faces
+        self.nodes, self.node_indices = node_coords, node_indices
+        self.edges, self.edges_weights, self.edges_distances = graph_edges, graph_edges_weights, graph_edges_distances
+        self.clusters = -np.ones((num_nodes, 1), dtype=np.int32)
+        self.remove_nodes_with_not_enough_neighbours()
+        self.compute_clusters()
+        self.create_graph_pyramid()
+
+    def remove_nodes_with_not_enough_neighbours(self):
+        """embedded_deformation_graph.py:334-368: nodes left with at most one neighbour go (repeatedly), the others are
+        renumbered."""
+        valid_nodes_mask = np.ones((self.nodes.shape[0], 1), dtype=bool)
+        node_and_edge_clean_up_c(self.edges, valid_nodes_mask)
+        reduced = self.get_reduced_graph(valid_nodes_mask)
+        self.nodes = reduced["valid_nodes_at_source"]
+        self.edges = reduced["graph_edges"]
+        self.edges_weights = reduced["graph_edges_weights"]
+        self.edges_distances = reduced["graph_edges_distances"]
+        self.clusters = reduced["graph_clusters"]
+        self.node_indices = self.node_indices[reduced["valid_nodes_mask"]]                   # :368 (flattens to 1-D, as there)
+
+    def compute_clusters(self):
+        """Connected components of the node graph into self.clusters (embedded_deformation_graph.py:371-380)."""
+        clusters_size_list = compute_clusters_c(self.edges, self.clusters)
+        for i, cluster_size in enumerate(clusters_size_list):
+            if cluster_size <= 2:
+                self.log.error(f"Cluster is too small {clusters_size_list}")
+                self.log.error(f"It only has nodes:{np.where(self.clusters == i)[0]}")
+        return clusters_size_list
+
+    def get_reduced_graph(self, valid_nodes_mask):
+        """The graph restricted to the nodes with valid_nodes_mask set (embedded_deformation_graph.py:382-477): rows of the
+        dropped nodes go, neighbour ids are renumbered, dropped neighbours are squeezed out of each row (order kept) and the
+        row's weights renormalised."""
+        keep = np.asarray(valid_nodes_mask).squeeze()
+        black = np.where(np.asarray(valid_nodes_mask) == False)[0].tolist()                   # noqa: E712
+        node_coords = self.nodes[keep]
+        graph_edges = self.edges[keep]
+        graph_edges_weights = self.edges_weights[keep]
+        graph_edges_distances = self.edges_distances[keep]
+        graph_clusters = self.clusters[keep]
+        num_nodes = node_coords.shape[0]
+        if num_nodes == 0:
+            raise RuntimeError("No nodes left in the graph")                                  # the reference exit()s, :400-402
+        if len(black) > 0:
+            new_id = np.where(keep, np.cumsum(keep) - 1, -1).astype(np.int32)                 # old id -> new id, -1 = dropped
+            E = graph_edges.shape[1]
+            for r in range(num_nodes):
+                row = graph_edges[r].copy()
+                ok = ~np.isin(row, black)                                                     # -1 entries count as kept (:424)
+                k = int(ok.sum())
+                w_row, d_row = graph_edges_weights[r, ok].copy(), graph_edges_distances[r, ok].copy()
+                ids = row[ok]
+                graph_edges[r] = -1
+                graph_edges_weights[r] = 0
+                graph_edges_distances[r] = 0
+                graph_edges[r, :k] = np.where(ids == -1, -1, new_id[np.maximum(ids, 0)])
+                graph_edges_weights[r, :k] = w_row
+                graph_edges_distances[r, :k] = d_row
+                sum_weights = np.sum(graph_edges_weights[r])
+                if sum_weights > 0:
+                    graph_edges_weights[r] /= (sum_weights + 1e-6)                            # :452-454
+                assert k <= E
+        return {
+            "all_nodes_at_source": self.nodes.copy(), "valid_nodes_at_source": node_coords, "graph_edges": graph_edges,
+            "graph_edges_weights": graph_edges_weights, "graph_edges_distances": graph_edges_distances,
+            "graph_clusters": graph_clusters, "num_nodes": np.array(num_nodes, dtype=np.int64),
+            "valid_nodes_mask": valid_nodes_mask,
+        }
+
+    def create_graph_pyramid(self):
+        """Four-level node pyramid for motion completion (embedded_deformation_graph.py:261-331): level l keeps, in node
+        order, the nodes at least 2^l * node_coverage away from every node kept before them; up_sample_idx maps a node of
+        the finer level to the nearest node kept before it; each level gets geodesic edges (8, 6, 4, 3 neighbours)."""
+        node_coverage = self.graph_generation_parameters["node_coverage"]
+        num_neighbours_list = [8, 6, 4, 3]
+        pyd = {"nn_index_l0": self.edges}
+        old_nodes, level_node_indices = self.nodes, self.node_indices
+        V = self.vertices.shape[0]
+        for level in range(1, 4):
+            node_coverage = node_coverage * 2
+            down_sample_idx, up_sample_idx = [], []
+            for i in range(old_nodes.shape[0]):
+                if not down_sample_idx:
+                    up_sample_idx.append(i)
+                    down_sample_idx.append(i)
+                    continue
+                nodes_dist = np.linalg.norm(old_nodes[down_sample_idx] - old_nodes[i], axis=1)
+                nearest = np.argmin(nodes_dist)
+                up_sample_idx.append(nearest)
+                if nodes_dist[nearest] < node_coverage:
+                    continue
+                down_sample_idx.append(i)
+            E = num_neighbours_list[level]
+            level_node_indices = level_node_indices[down_sample_idx]
+            n = level_node_indices.shape[0]
+            graph_edges = -np.ones((n, E), dtype=np.int32)
+            graph_edges_weights = np.zeros((n, E), dtype=np.float32)
+            graph_edges_distances = np.zeros((n, E), dtype=np.float32)
+            compute_edges_geodesic_c(self.vertices, np.ones(V, dtype=bool), self.faces, level_node_indices, E, node_coverage,
+                                     graph_edges, graph_edges_weights, graph_edges_distances, None, False, True)   # :313-320
+            pyd["down_sample_idx" + str(level)] = down_sample_idx
+            pyd["up_sample_idx" + str(level)] = up_sample_idx
+            pyd["nn_index_l" + str(level)] = graph_edges
+            old_nodes = old_nodes[down_sample_idx]
+        self.pyd = pyd
+
+    def get_graph_pyramid(self):
+        return self.pyd
 
     def erode_mesh(self, vertices, faces, num_iterations=-1):
         """(V,1) bool, True = vertex survives the erosion (embedded_deformation_graph.py:153-172).  As in the reference,

@@ -42,8 +42,9 @@ def import_ref_edgraph(ref_graph):
     c = sys.modules["NeuralNRT._C"]
     for name in ("erode_mesh", "sample_nodes"):
         setattr(c, name, getattr(ref_graph, name))
-    for name in ("compute_edges_geodesic", "node_and_edge_clean_up", "compute_clusters", "compute_mesh_from_depth"):
-        setattr(c, name, None)
+    for name in ("compute_edges_geodesic", "node_and_edge_clean_up", "compute_clusters"):
+        setattr(c, name, getattr(ref_graph, name))
+    c.compute_mesh_from_depth = None
     if "model" not in sys.modules:
         m = ref_shims._module("model")
         m.dataset = ref_shims._module("model.dataset")
@@ -174,6 +175,28 @@ def main():
         sizes = ref_graph.compute_clusters(e, cl)
         out[f"rnd{k}_edges"], out[f"rnd{k}_mask_in"], out[f"rnd{k}_mask_out"] = e, m0.reshape(-1), m1.reshape(-1)
         out[f"rnd{k}_clusters"], out[f"rnd{k}_sizes"] = cl.reshape(-1), np.asarray(sizes, np.int32)
+
+    # ---- f2: the reference's Python around them: remove_nodes_with_not_enough_neighbours / get_reduced_graph /
+    #      compute_clusters / create_graph_pyramid (edg.py:261-480) on an EDGraph object filled by hand -------------------
+    g_obj = object.__new__(ref_edg.EDGraph)
+    g_obj.log = logging.getLogger("golden")
+    g_obj.graph_generation_parameters = {"node_coverage": coverage, "min_neighbours": 2, "num_neighbours": 8}
+    g_obj.vertices, g_obj.faces = verts, faces
+    g_obj.nodes, g_obj.node_indices = out["sample_pos_1"].copy(), node_idx.copy()
+    e_mod = out["geo_a_edges"].copy()
+    for row in (5, 17, 40, 41, 120):
+        e_mod[row, 1:] = -1                                   # nodes left with one neighbour -> removed, neighbours renumbered
+    g_obj.edges, g_obj.edges_weights, g_obj.edges_distances = e_mod, out["geo_a_weights"].copy(), out["geo_a_dist"].copy()
+    g_obj.clusters = -np.ones((M, 1), np.int32)
+    out["red_edges_in"] = e_mod.copy()
+    g_obj.remove_nodes_with_not_enough_neighbours()
+    g_obj.compute_clusters()
+    g_obj.create_graph_pyramid()
+    out["red_nodes"], out["red_node_indices"] = g_obj.nodes, g_obj.node_indices
+    out["red_edges"], out["red_weights"], out["red_dist"] = g_obj.edges, g_obj.edges_weights, g_obj.edges_distances
+    out["red_clusters"] = g_obj.clusters
+    for k, v in g_obj.pyd.items():
+        out["pyd_" + k] = np.asarray(v)
 
     # ---- f2: find_unreachable_nodes + EDGraph.update (reference Python) -----------------------------------------
     # graph covers the left part of the mesh; the right part is "newly revealed"

@@ -83,3 +83,27 @@ def test_graph_host_argument_errors(gg):
     valid[3] = False
     with pytest.raises(OfxError, match="not a valid vertex"):
         compute_edges_geodesic_c(v, valid, gg["mesh_faces"], np.array([3, 9], np.int32), 4, 0.05, e, w, d, None, True, True)
+
+
+def test_reduced_graph_clusters_and_pyramid_match_reference(gg):
+    """remove_nodes_with_not_enough_neighbours / get_reduced_graph / compute_clusters / create_graph_pyramid
+    (embedded_deformation_graph.py:261-480) against the reference's own Python + C++ run on the same hand-filled graph."""
+    from occlusionfusion_b200 import EDGraph
+    g = EDGraph(nodes=gg["sample_pos_1"].copy(), graph_generation_parameters={"node_coverage": float(gg["coverage"])})
+    g.vertices, g.faces = gg["mesh_verts"], gg["mesh_faces"]
+    g.node_indices = gg["geo_a_node_idx"].copy()
+    g.edges, g.edges_weights, g.edges_distances = gg["red_edges_in"].copy(), gg["geo_a_weights"].copy(), gg["geo_a_dist"].copy()
+    g.clusters = -np.ones((len(g.nodes), 1), np.int32)
+    g.remove_nodes_with_not_enough_neighbours()
+    assert len(g.nodes) == len(gg["red_nodes"]) < len(gg["sample_pos_1"])
+    assert np.array_equal(g.nodes, gg["red_nodes"]) and np.array_equal(g.node_indices, gg["red_node_indices"])
+    assert np.array_equal(g.edges, gg["red_edges"]) and np.array_equal(g.edges_distances, gg["red_dist"])
+    assert np.array_equal(g.edges_weights, gg["red_weights"])
+    g.compute_clusters()
+    assert np.array_equal(g.clusters, gg["red_clusters"])
+    g.create_graph_pyramid()
+    pyd = g.get_graph_pyramid()
+    keys = [k[4:] for k in gg.files if k.startswith("pyd_")]
+    assert sorted(pyd) == sorted(keys) and len(keys) == 10
+    for k in keys:
+        assert np.array_equal(np.asarray(pyd[k]), gg["pyd_" + k]), k

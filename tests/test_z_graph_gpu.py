@@ -277,3 +277,30 @@ def test_graph_capi_edge_cases():
     cand = torch.tensor([3, 0, 1, 2], dtype=torch.int32, device=dev)
     assert lib.ofx_greedy_insert(P(v), 4, P(cand), 4, None, 0, 0.05, P(acc), P(n_out), S()) == 0
     assert int(n_out.item()) == 2 and acc[:2].cpu().tolist() == [3, 0]
+
+
+def test_create_graph_from_mesh_end_to_end(gg, oracle):
+    """EDGraph.create_graph_from_mesh (embedded_deformation_graph.py:174-256): device erosion + node sampling, then the host
+    half (geodesic edges, clean-up, clusters, pyramid), against the same pipeline assembled from the separately pinned parts."""
+    from occlusionfusion_b200.graph_proc import compute_clusters_c, compute_edges_geodesic_c, node_and_edge_clean_up_c
+    verts, faces = gg["mesh_verts"], gg["mesh_faces"]
+    g = _graph(np.zeros((0, 3), np.float32), float(gg["coverage"]))
+    g.create_graph_from_mesh(verts, faces)
+    idx0 = gg["sample_idx_1"]                                            # the reference's own sample_nodes on this mesh
+    e = -np.ones((len(idx0), 8), np.int32)
+    w = np.zeros((len(idx0), 8), np.float32)
+    d = np.zeros((len(idx0), 8), np.float32)
+    compute_edges_geodesic_c(verts, np.ones(len(verts), bool), faces, idx0, 8, float(gg["coverage"]), e, w, d, None, True, True)
+    mask = np.ones((len(idx0), 1), bool)
+    node_and_edge_clean_up_c(e, mask)
+    keep = mask.reshape(-1)
+    assert np.array_equal(g.node_indices.reshape(-1), idx0[keep]) and np.array_equal(g.nodes, gg["sample_pos_1"][keep])
+    assert g.edges.shape == (keep.sum(), 8) and (g.edges[:, :2] >= 0).all() and g.edges.max() < keep.sum()
+    if keep.all():
+        assert np.array_equal(g.edges, e) and np.array_equal(g.edges_weights, w) and np.array_equal(g.edges_distances, d)
+    cl = -np.ones((len(g.edges), 1), np.int32)
+    sizes = compute_clusters_c(g.edges, cl)
+    assert np.array_equal(g.clusters, cl) and sum(sizes) == len(g.nodes)
+    pyd = g.get_graph_pyramid()
+    assert pyd["nn_index_l0"] is g.edges and pyd["nn_index_l1"].shape[1] == 6 and pyd["nn_index_l3"].shape[1] == 3
+    assert len(pyd["up_sample_idx1"]) == len(g.nodes) and len(pyd["down_sample_idx1"]) == len(pyd["nn_index_l1"])
