@@ -560,7 +560,24 @@ def bench_graph_ops(args, device):
         k = int(cnt.item())
         assert np.array_equal(acc[:k].cpu().numpy(), acc_ref)
         kind = "reference" if ref_graph is not None else "port"
+        # host half of the builder: geodesic edges between the sampled nodes (host threads) next to the reference's serial C++
+        from occlusionfusion_b200.graph_proc import compute_edges_geodesic_c
+        nidx = idx[:M].cpu().numpy().reshape(-1, 1)
+        ge, gw, gd = -np.ones((M, 8), np.int32), np.zeros((M, 8), np.float32), np.zeros((M, 8), np.float32)
+        t0 = time.perf_counter()
+        compute_edges_geodesic_c(verts, np.ones(V, bool), faces, nidx, 8, cov, ge, gw, gd, None, True, True)
+        t_geo = (time.perf_counter() - t0) * 1e3
+        c_geo = None
+        if ref_graph is not None and V <= 100000:           # the reference needs a dense (M, V) float32 scratch matrix
+            re_, rw, rd = -np.ones((M, 8), np.int32), np.zeros((M, 8), np.float32), np.zeros((M, 8), np.float32)
+            n2v = -np.ones((M, V), np.float32)
+            t0 = time.perf_counter()
+            ref_graph.compute_edges_geodesic(verts, np.ones((V, 1), bool), faces, nidx, 8, cov, re_, rw, rd, n2v, True, True)
+            c_geo = (time.perf_counter() - t0) * 1e3
+            assert np.array_equal(ge, re_) and np.array_equal(gw, rw) and np.array_equal(gd, rd)
         out["ops"][f"mesh_{n}x{n}"] = {
+            "edges_geodesic_host": {"ms": t_geo, "host_threads": os.cpu_count(), "cpu_ms": c_geo, "cpu_kind": "reference",
+                                    "cpu_cores": 1, "where": "host C++ in libofx (the reference's is host C++ too)"},
             "V": V, "F": F, "nodes_sampled": M, "graph_nodes": int(nodes.shape[0]), "candidates": int(len(cand)), "inserted": k,
             "erode_mesh_3_rounds": {"gpu_ms": t_erode, "cpu_ms": c_erode, "cpu_kind": kind, "cpu_cores": 1},
             "sample_nodes": {"gpu_ms": t_sample, "cpu_ms": c_sample, "cpu_kind": kind, "cpu_cores": 1},
