@@ -138,6 +138,11 @@ int ofx_check_visibility(const float *points, int64_t n, const float *depth, int
  * float32 distance to and index of the nearest node, ties -> lower index.  dist or idx may be NULL. */
 int ofx_nearest_node(const float *points, int64_t n, const float *nodes, int32_t M, float *dist,
                      int32_t *idx, void *stream);
+/* np.argmin(np.linalg.norm(points - q, axis=1)) for every query q (EDGraph.update re-anchoring the nodes on the new mesh,
+ * fusion_with_occlusion/embedded_deformation_graph.py:545-547, which builds the dense (queries x points) matrix on the
+ * host): float32 norms, first index among equal norms.  dist or idx may be NULL. */
+int ofx_argmin_norm(const float *queries, int64_t n, const float *points, int32_t M, float *dist,
+                    int32_t *idx, void *stream);
 /* The greedy coverage rule of EDGraph.update (fusion_with_occlusion/embedded_deformation_graph.py:516-536):
  * walk cand[0..n_cand) (vertex ids into verts (V,3), in the caller's order -- farthest first, warpfield.py:469-483);
  * accept a vertex unless an existing node (nodes (M,3), M may be 0) or an already accepted vertex is closer than

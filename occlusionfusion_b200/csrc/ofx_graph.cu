@@ -67,6 +67,9 @@ constexpr int GREEDY_THREADS = 1024;
 // ---- nearest node ----------------------------------------------------------------------------------------------
 // One thread per point, node positions staged tile by tile in shared memory; strict < keeps the lower node index on
 // ties.  dist = sqrtf(min d2) (IEEE), as the float32 KD-tree returns it.
+// BY_NORM: compare the float32 norms instead of the squared distances -- np.argmin(np.linalg.norm(pts - q, axis=1)) keeps the
+// FIRST index among equal norms, and two different squared distances can round to the same norm (edg.py:545-547).
+template <bool BY_NORM>
 __global__ void __launch_bounds__(256) nearest_node_kernel(const float *__restrict__ pts, int64_t n,
                                                            const float *__restrict__ nodes, int M,
                                                            float *__restrict__ dist, int32_t *__restrict__ idx)
@@ -87,13 +90,14 @@ __global__ void __launch_bounds__(256) nearest_node_kernel(const float *__restri
             __syncthreads();
             if (live) {
                 for (int j = 0; j < cnt; ++j) {
-                    const float d2 = dist2(px, py, pz, s_nodes[3 * j], s_nodes[3 * j + 1], s_nodes[3 * j + 2]);
+                    float d2 = dist2(px, py, pz, s_nodes[3 * j], s_nodes[3 * j + 1], s_nodes[3 * j + 2]);
+                    if (BY_NORM) d2 = sqrtf(d2);
                     if (d2 < best) { best = d2; bi = base + j; }
                 }
             }
         }
         if (live) {
-            if (dist) dist[i] = sqrtf(best);
+            if (dist) dist[i] = BY_NORM ? best : sqrtf(best);
             if (idx) idx[i] = bi;
         }
     }
@@ -514,7 +518,18 @@ extern "C" int ofx_nearest_node(const float *points, int64_t n, const float *nod
     OFX_REQUIRE(n >= 0 && M >= 1, "ofx_nearest_node: need n >= 0 and M >= 1 (n=%lld, M=%d)", (long long)n, M);
     if (n == 0) return 0;
     OFX_REQUIRE(points && nodes && (dist || idx), "ofx_nearest_node: null pointer");
-    nearest_node_kernel<<<graph_grid_for(n, 256, 4), 256, 0, (cudaStream_t)stream>>>(points, n, nodes, M, dist, idx);
+    nearest_node_kernel<false><<<graph_grid_for(n, 256, 4), 256, 0, (cudaStream_t)stream>>>(points, n, nodes, M, dist, idx);
+    OFX_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int ofx_argmin_norm(const float *queries, int64_t n, const float *points, int32_t M, float *dist, int32_t *idx,
+                               void *stream)
+{
+    OFX_REQUIRE(n >= 0 && M >= 1, "ofx_argmin_norm: need n >= 0 and M >= 1 (n=%lld, M=%d)", (long long)n, M);
+    if (n == 0) return 0;
+    OFX_REQUIRE(queries && points && (dist || idx), "ofx_argmin_norm: null pointer");
+    nearest_node_kernel<true><<<graph_grid_for(n, 64, 16), 64, 0, (cudaStream_t)stream>>>(queries, n, points, M, dist, idx);
     OFX_LAUNCH_CHECK();
     return 0;
 }

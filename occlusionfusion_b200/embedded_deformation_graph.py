@@ -231,7 +231,8 @@ class EDGraph:
         vertices in the given order (farthest first, warpfield.py:469-483); accept a vertex when it
         is at least node_coverage away from every existing node and every accepted vertex; append
         accepted vertices to `nodes` (old nodes keep their indices, :542).  Returns True when nodes
-        were added.  Edge / cluster / pyramid rebuild (:545-603) is a "next" row."""
+        were added.  With faces given, the edges / clusters / pyramid are rebuilt on the new mesh as the reference does
+        (:545-603, `rebuild_edges`); faces=None appends the nodes only."""
         if len(new_verts_indices) == 0:
             return False
         _capi.require_cuda()
@@ -252,4 +253,36 @@ class EDGraph:
             return False
         new_nodes = np.asarray(canonical_model_vertices)[accepted[:k].cpu().numpy()]
         self.nodes = np.concatenate([self.nodes, new_nodes], axis=0).astype(np.float32)          # :542
+        if canonical_model_faces is not None:
+            self.rebuild_edges(canonical_model_vertices, canonical_model_faces)                  # :545-603
         return True
+
+    def rebuild_edges(self, canonical_model_vertices, canonical_model_faces):
+        """The second half of the reference's update (embedded_deformation_graph.py:545-603): anchor every node on its
+        nearest vertex of the new canonical mesh (ofx_argmin_norm on the device instead of the dense nodes x vertices
+        matrix), geodesic edges between the nodes, drop nodes with too few neighbours, clusters, pyramid."""
+        _capi.require_cuda()
+        dev = self.device
+        verts_np = np.ascontiguousarray(canonical_model_vertices, dtype=np.float32)
+        verts = _capi.to_device(verts_np, torch.float32, dev).reshape(-1, 3)
+        nodes = _capi.to_device(self.nodes, torch.float32, dev).reshape(-1, 3)
+        idx = torch.empty(nodes.shape[0], dtype=torch.int32, device=dev)
+        with torch.cuda.device(dev):
+            _capi.check(_capi.load().ofx_argmin_norm(_capi.ptr(nodes), nodes.shape[0], _capi.ptr(verts), verts.shape[0], None,
+                                                     _capi.ptr(idx), _capi.stream_ptr(dev)))
+        self.node_indices = idx.cpu().numpy().astype(np.int64)[:, None]                          # :547-550
+        num_nodes = self.nodes.shape[0]
+        num_neighbours = self.graph_generation_parameters["num_neighbours"]
+        node_coverage = self.graph_generation_parameters["node_coverage"]
+        graph_edges = -np.ones((num_nodes, num_neighbours), dtype=np.int32)
+        graph_edges_weights = np.zeros((num_nodes, num_neighbours), dtype=np.float32)
+        graph_edges_distances = np.zeros((num_nodes, num_neighbours), dtype=np.float32)
+        compute_edges_geodesic_c(verts_np, np.ones(verts_np.shape[0], dtype=bool), canonical_model_faces, self.node_indices,
+                                 num_neighbours, node_coverage, graph_edges, graph_edges_weights, graph_edges_distances, None,
+                                 True, True)                                                     # :575-582
+        self.vertices, self.faces = canonical_model_vertices, canonical_model_faces
+        self.edges, self.edges_weights, self.edges_distances = graph_edges, graph_edges_weights, graph_edges_distances
+        self.clusters = -np.ones((num_nodes, 1), dtype=np.int32)
+        self.remove_nodes_with_not_enough_neighbours()
+        self.compute_clusters()
+        self.create_graph_pyramid()

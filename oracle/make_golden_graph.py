@@ -221,6 +221,19 @@ def main():
         pass
     out["upd_nodes_before"], out["upd_cand"], out["upd_nodes_after"] = nodes, cand.astype(np.int32), g_self.nodes
     out["upd_nearest_dist"] = dist.reshape(-1).astype(np.float32)
+    # ---- f2: the WHOLE of EDGraph.update (edg.py:496-605: insertion, nearest vertices, edge rebuild, clean-up, clusters,
+    #      pyramid) with the reference's Python and C++ ---------------------------------------------------------------------
+    g_full = object.__new__(ref_edg.EDGraph)
+    g_full.log = logging.getLogger("golden")
+    g_full.graph_generation_parameters = {"node_coverage": coverage, "min_neighbours": 2, "num_neighbours": 8}
+    g_full.nodes = nodes.copy()
+    assert g_full.update(verts, faces, cand) is True
+    out["full_nodes"], out["full_node_indices"] = g_full.nodes, np.asarray(g_full.node_indices)
+    out["full_edges"], out["full_weights"], out["full_dist"] = g_full.edges, g_full.edges_weights, g_full.edges_distances
+    out["full_clusters"] = g_full.clusters
+    for k, v in g_full.pyd.items():
+        out["fullpyd_" + k] = np.asarray(v)
+
     # second case: candidates that partly fall inside the existing graph's coverage (:522 pre-check) and a shuffled order
     cand2 = rng.permutation(len(verts))[:1500].astype(np.int32)
     g2 = types.SimpleNamespace(nodes=nodes.copy(), graph_generation_parameters={"node_coverage": coverage},

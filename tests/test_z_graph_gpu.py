@@ -98,13 +98,13 @@ def test_greedy_update_golden_and_oracle(gg, oracle):
     cand = cand[np.argsort(dist[cand], kind="stable")[::-1]].astype(np.int32)
     acc = oracle.greedy_update(verts, cand, onodes, 0.05)
     g = _graph(onodes.copy(), 0.05)
-    assert g.update(verts, faces, cand) is True
+    assert g.update(verts, None, cand) is True
     assert len(acc) > 100 and np.array_equal(g.nodes[len(onodes):], verts[acc])
     # same candidates in a shuffled order, with duplicates
     cand2 = np.concatenate([rng.permutation(cand)[:5000], cand[:100]]).astype(np.int32)
     acc2 = oracle.greedy_update(verts, cand2, onodes, 0.05)
     g = _graph(onodes.copy(), 0.05)
-    g.update(verts, faces, cand2)
+    g.update(verts, None, cand2)
     assert np.array_equal(g.nodes[len(onodes):], verts[acc2])
 
 
@@ -304,3 +304,18 @@ def test_create_graph_from_mesh_end_to_end(gg, oracle):
     pyd = g.get_graph_pyramid()
     assert pyd["nn_index_l0"] is g.edges and pyd["nn_index_l1"].shape[1] == 6 and pyd["nn_index_l3"].shape[1] == 3
     assert len(pyd["up_sample_idx1"]) == len(g.nodes) and len(pyd["down_sample_idx1"]) == len(pyd["nn_index_l1"])
+
+
+def test_full_update_matches_reference(gg):
+    """The whole of the reference's EDGraph.update (embedded_deformation_graph.py:496-605) run here with its own Python and
+    C++: insertion, nearest vertices, geodesic edges, clean-up, clusters, pyramid."""
+    g = _graph(gg["upd_nodes_before"].copy(), float(gg["coverage"]))
+    assert g.update(gg["mesh_verts"], gg["mesh_faces"], gg["upd_cand"]) is True
+    assert np.array_equal(g.nodes, gg["full_nodes"])
+    assert np.array_equal(np.asarray(g.node_indices).reshape(-1), gg["full_node_indices"].reshape(-1))
+    assert np.array_equal(g.edges, gg["full_edges"]) and np.array_equal(g.edges_distances, gg["full_dist"])
+    assert np.array_equal(g.edges_weights, gg["full_weights"]) and np.array_equal(g.clusters, gg["full_clusters"])
+    keys = [k[8:] for k in gg.files if k.startswith("fullpyd_")]
+    assert sorted(g.pyd) == sorted(keys)
+    for k in keys:
+        assert np.array_equal(np.asarray(g.pyd[k]), gg["fullpyd_" + k]), k
