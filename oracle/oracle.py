@@ -24,7 +24,7 @@ _u8p = np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")
 
 
 def build(force=False):
-    srcs = [os.path.join(_HERE, f) for f in ("ofx_oracle.c", "ofx_oracle_graph.c")]
+    srcs = [os.path.join(_HERE, f) for f in ("ofx_oracle.c", "ofx_oracle_graph.c", "ofx_oracle_mc.c")]
     if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < max(os.path.getmtime(s) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s", "libofx_oracle.so"])
     return _LIB_PATH
@@ -56,6 +56,8 @@ def _load():
     lib.ofx_oracle_sample_nodes.argtypes = [_f32p, _u8p, C.c_int, C.c_float, C.c_int, _i32p, _f32p]
     lib.ofx_oracle_erode_mesh.argtypes = [_i32p, C.c_int, C.c_int, C.c_int, C.c_int, _u8p]
     lib.ofx_oracle_truncated_region.argtypes = [_f32p, C.c_int, C.c_int, C.c_int, C.c_double, _u8p]
+    lib.ofx_oracle_mc_triangles.restype = C.c_int64
+    lib.ofx_oracle_mc_triangles.argtypes = [_f32p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p]
     return lib
 
 
@@ -185,6 +187,34 @@ def truncated_region(tsdf, max_diff):
     out = np.empty(tsdf.shape, np.uint8)
     lib().ofx_oracle_truncated_region(tsdf, *tsdf.shape, float(max_diff), out)
     return out.astype(bool)
+
+
+def mc_vertex_positions(vol, keys, level=0.0):
+    """Vertices named by grid-edge keys (3 * lower-corner index + axis) -> (n,3) float32 voxel coordinates: the lower corner
+    plus t = (level - v0) / (v1 - v0) along the edge's axis, float32 throughout."""
+    vol = _c(vol, np.float32)
+    W, H, D = vol.shape
+    lower, axis = keys // 3, (keys % 3).astype(np.int64)
+    stride = np.array([H * D, D, 1], np.int64)[axis]
+    v0, v1 = vol.reshape(-1)[lower], vol.reshape(-1)[lower + stride]
+    t = (np.float32(level) - v0) / (v1 - v0)
+    pos = np.stack([lower // (H * D), (lower // D) % H, lower % D], 1).astype(np.float32)
+    pos[np.arange(len(keys)), axis] += t
+    return pos
+
+
+def marching_cubes(vol, mask=None, level=0.0):
+    """Classic marching cubes with the generated case table (ofx_oracle_mc.c): verts (n,3) f32 in voxel coordinates (axis
+    order of the array), faces (T,3) i32.  Vertices unique per grid edge, sorted by edge key; faces in cube scan order."""
+    vol = _c(vol, np.float32)
+    W, H, D = vol.shape
+    m = None if mask is None else _c(mask, np.uint8)
+    mp = None if m is None else m.ctypes.data
+    nt = lib().ofx_oracle_mc_triangles(vol, mp, W, H, D, float(level), None)
+    keys = np.empty(3 * nt, np.int64)
+    lib().ofx_oracle_mc_triangles(vol, mp, W, H, D, float(level), keys.ctypes.data)
+    ukeys, inverse = np.unique(keys, return_inverse=True)
+    return mc_vertex_positions(vol, ukeys, level), inverse.reshape(-1, 3).astype(np.int32), ukeys
 
 
 def origin_translations(R, t, nodes):
