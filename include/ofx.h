@@ -168,6 +168,24 @@ int ofx_erode_mesh(const int32_t *faces, int32_t F, int32_t V, int32_t n_iterati
 int ofx_truncated_region(const float *tsdf, int32_t Dx, int32_t Dy, int32_t Dz, double max_diff,
                          uint8_t *region, void *stream);
 
+/* ---- marching cubes (the scikit-image call at fusion_with_occlusion/tsdf.py:794 and the colour unpack at :797-807) ----
+ * Classic form with the case table of csrc/ofx_mc_tables.h.  vol / mask / colour are whole (Dx,Dy,Dz) volumes, C order;
+ * cube i = (x*Dy + y)*Dz + z is processed when mask == NULL or mask[i] != 0; corners with value < level are inside.
+ *   1. ofx_mc_count:    tri_count (N,) u8 = triangles of every cube.
+ *   2. the caller forms tri_offset (N,) i32 = exclusive prefix sum of tri_count, T = total.
+ *   3. ofx_mc_emit:     keys (3T,) i64, three per triangle in cube order: a triangle corner is named by its grid edge,
+ *                       key = 3 * (linear index of the edge's lower corner) + axis.
+ *   4. the caller sorts the keys into unique vertices (faces = index of each key among the unique keys).
+ *   5. ofx_mc_vertices: per unique key the vertex in voxel coordinates (lower corner + (level - v0)/(v1 - v0) along the
+ *                       axis, float32), optionally the unit gradient normal (towards increasing values) and the colour of
+ *                       the nearest voxel unpacked to r, g, b bytes (tsdf.py:797-807; rgb needs colour). */
+int ofx_mc_count(const float *vol, const uint8_t *mask, int32_t Dx, int32_t Dy, int32_t Dz, float level,
+                 uint8_t *tri_count, void *stream);
+int ofx_mc_emit(const float *vol, const uint8_t *mask, int32_t Dx, int32_t Dy, int32_t Dz, float level,
+                const uint8_t *tri_count, const int32_t *tri_offset, int64_t *keys, void *stream);
+int ofx_mc_vertices(const float *vol, const float *colour, int32_t Dx, int32_t Dy, int32_t Dz, float level,
+                    const int64_t *keys, int64_t n, float *verts, float *normals, uint8_t *rgb, void *stream);
+
 /* ---- host half of the graph builder (HOST pointers; no device work) ------------------------------------------ */
 /* compute_edges_geodesic (csrc/cpu/graph_proc.cpp:155-300, binding csrc/main.cpp:30; callers
  * embedded_deformation_graph.py:226-233, 313-320): for every node (node_idx: its mesh vertex, < 0 = skip) walk the mesh

@@ -23,6 +23,7 @@ SYMBOLS = [
     "ofx_volume_world_points", "ofx_volume_skin", "ofx_volume_deform", "ofx_pack_frame", "ofx_skin",
     "ofx_warp_points", "ofx_check_visibility", "ofx_peer_copy",
     "ofx_nearest_node", "ofx_argmin_norm", "ofx_greedy_insert", "ofx_sample_nodes", "ofx_erode_mesh", "ofx_truncated_region",
+    "ofx_mc_count", "ofx_mc_emit", "ofx_mc_vertices",
     "ofx_compute_edges_geodesic_host", "ofx_node_and_edge_clean_up_host", "ofx_compute_clusters_host",
 ]
 
@@ -77,6 +78,9 @@ def load():
     lib.ofx_sample_nodes.argtypes = [vp, i32, vp, C.c_float, i32, vp, vp, vp, vp]
     lib.ofx_erode_mesh.argtypes = [vp, i32, i32, i32, i32, vp, vp]
     lib.ofx_truncated_region.argtypes = [vp, i32, i32, i32, f64, vp, vp]
+    lib.ofx_mc_count.argtypes = [vp, vp, i32, i32, i32, C.c_float, vp, vp]
+    lib.ofx_mc_emit.argtypes = [vp, vp, i32, i32, i32, C.c_float, vp, vp, vp, vp]
+    lib.ofx_mc_vertices.argtypes = [vp, vp, i32, i32, i32, C.c_float, vp, i64, vp, vp, vp, vp]
     lib.ofx_compute_edges_geodesic_host.argtypes = [vp, vp, i32, vp, i32, vp, i32, i32, C.c_float, vp, vp, vp, vp, i32, i32, i32]
     lib.ofx_node_and_edge_clean_up_host.argtypes = [vp, i32, i32, vp]
     lib.ofx_compute_clusters_host.argtypes = [vp, i32, i32, vp, vp, vp]

@@ -1,0 +1,166 @@
+// ofx_mc.cu -- marching cubes on the device: the step the reference hands to scikit-image
+// (`measure.marching_cubes(tsdf_vol, mask=diff_tsdf, level=0)`, fusion_with_occlusion/tsdf.py:794) plus the vertex colour
+// unpack that follows it (tsdf.py:797-807).  Classic form: one case-table lookup per cube (csrc/ofx_mc_tables.h, derived
+// by tools/gen_mc_tables.py), vertices on the grid edges at the linear zero crossing.  scikit-image is absent here, so this
+// is checked against the CPU restatement of the same contract (the marching-cubes file of the test-only CPU checker), not against the reference's output.
+//   Three streaming passes, no atomics, deterministic output order:
+//     ofx_mc_count     per cube: number of triangles (u8)                      4 B read + 1 B mask + 1 B written per voxel
+//     [exclusive prefix sum of the counts: caller, e.g. torch.cumsum]
+//     ofx_mc_emit      per cube: its triangles as grid-edge keys (3 * lower-corner index + axis) at the cube's offset
+//     [unique keys = vertices, inverse = faces: caller, e.g. torch.unique]
+//     ofx_mc_vertices  per unique key: position (voxel coordinates), gradient normal, unpacked colour
+// A block walks z-rows (row = x*Dy + y: one division per row), threads run along z (coalesced).
+#include "../../include/ofx.h"
+#include "ofx_common.h"
+#include "ofx_mc_tables.h"
+
+namespace ofx {
+
+int sm_count();   // ofx_points.cu
+
+__device__ __forceinline__ int mc_case(const float *__restrict__ vol, const uint8_t *__restrict__ mask, int64_t i, int x, int y,
+                                       int z, int W, int H, int D, float level)
+{
+    if (x + 1 >= W || y + 1 >= H || z + 1 >= D) return 0;
+    if (mask && !__ldg(mask + i)) return 0;
+    const int64_t sx = (int64_t)H * D, sy = D;
+    int c = 0;
+    c |= (__ldg(vol + i) < level) << 0;
+    c |= (__ldg(vol + i + sx) < level) << 1;
+    c |= (__ldg(vol + i + sy) < level) << 2;
+    c |= (__ldg(vol + i + sx + sy) < level) << 3;
+    c |= (__ldg(vol + i + 1) < level) << 4;
+    c |= (__ldg(vol + i + sx + 1) < level) << 5;
+    c |= (__ldg(vol + i + sy + 1) < level) << 6;
+    c |= (__ldg(vol + i + sx + sy + 1) < level) << 7;
+    return c;
+}
+
+__global__ void __launch_bounds__(256) mc_count_kernel(const float *__restrict__ vol, const uint8_t *__restrict__ mask, int W, int H,
+                                                       int D, float level, uint8_t *__restrict__ count)
+{
+    for (int r = blockIdx.x; r < W * H; r += gridDim.x) {
+        const int x = r / H, y = r - x * H;
+        for (int z = threadIdx.x; z < D; z += blockDim.x) {
+            const int64_t i = (int64_t)r * D + z;
+            count[i] = OFX_MC_TRIS[mc_case(vol, mask, i, x, y, z, W, H, D, level)];
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) mc_emit_kernel(const float *__restrict__ vol, const uint8_t *__restrict__ mask, int W, int H,
+                                                      int D, float level, const uint8_t *__restrict__ count,
+                                                      const int32_t *__restrict__ offset, int64_t *__restrict__ keys)
+{
+    for (int r = blockIdx.x; r < W * H; r += gridDim.x) {
+        const int x = r / H, y = r - x * H;
+        for (int z = threadIdx.x; z < D; z += blockDim.x) {
+            const int64_t i = (int64_t)r * D + z;
+            const int nt = __ldg(count + i);
+            if (!nt) continue;
+            const int c = mc_case(vol, mask, i, x, y, z, W, H, D, level);
+            int64_t *out = keys + 3 * (int64_t)__ldg(offset + i);
+            for (int k = 0; k < 3 * nt; ++k) {
+                const int e = OFX_MC_EDGES[c][k], axis = e >> 2, b = e & 3;
+                // lower corner of edge e: offsets (b & 1, b >> 1) along the two other axes, in increasing axis order
+                const int ox = axis == 0 ? 0 : (b & 1), oz = axis == 2 ? 0 : (b >> 1);
+                const int oy = axis == 0 ? (b & 1) : (axis == 1 ? 0 : (b >> 1));
+                out[k] = 3 * (i + ((int64_t)ox * H + oy) * D + oz) + axis;
+            }
+        }
+    }
+}
+
+// central-difference gradient of the volume at a grid point (one-sided at the volume boundary)
+__device__ __forceinline__ void mc_gradient(const float *__restrict__ vol, int x, int y, int z, int W, int H, int D, float g[3])
+{
+    const int64_t sx = (int64_t)H * D, sy = D, i = ((int64_t)x * H + y) * D + z;
+    g[0] = __ldg(vol + i + (x + 1 < W ? sx : 0)) - __ldg(vol + i - (x > 0 ? sx : 0));
+    g[1] = __ldg(vol + i + (y + 1 < H ? sy : 0)) - __ldg(vol + i - (y > 0 ? sy : 0));
+    g[2] = __ldg(vol + i + (z + 1 < D ? 1 : 0)) - __ldg(vol + i - (z > 0 ? 1 : 0));
+}
+
+__global__ void __launch_bounds__(256) mc_vertices_kernel(const float *__restrict__ vol, const float *__restrict__ colour, int W, int H,
+                                                          int D, float level, const int64_t *__restrict__ keys, int64_t n,
+                                                          float *__restrict__ verts, float *__restrict__ normals,
+                                                          uint8_t *__restrict__ rgb)
+{
+    for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t key = __ldg(keys + j), lower = key / 3;
+        const int axis = (int)(key - 3 * lower);
+        const int z = (int)(lower % D), y = (int)((lower / D) % H), x = (int)(lower / ((int64_t)D * H));
+        const int64_t stride = axis == 0 ? (int64_t)H * D : (axis == 1 ? D : 1);
+        const float v0 = __ldg(vol + lower), v1 = __ldg(vol + lower + stride);
+        const float t = (level - v0) / (v1 - v0);
+        float p[3] = {(float)x, (float)y, (float)z};
+        p[axis] += t;
+        verts[3 * j] = p[0]; verts[3 * j + 1] = p[1]; verts[3 * j + 2] = p[2];
+        if (normals) {
+            float g0[3], g1[3];
+            mc_gradient(vol, x, y, z, W, H, D, g0);
+            mc_gradient(vol, x + (axis == 0), y + (axis == 1), z + (axis == 2), W, H, D, g1);
+            float g[3], s = 0.0f;
+#pragma unroll
+            for (int a = 0; a < 3; ++a) { g[a] = g0[a] + t * (g1[a] - g0[a]); s += g[a] * g[a]; }
+            const float inv = s > 0.0f ? 1.0f / sqrtf(s) : 0.0f;       // towards increasing values: inside -> outside
+            normals[3 * j] = g[0] * inv; normals[3 * j + 1] = g[1] * inv; normals[3 * j + 2] = g[2] * inv;
+        }
+        if (rgb) {
+            // tsdf.py:797-807: colour of the voxel nearest to the vertex (np.round: half to even), unpacked b, g, r
+            const int ix = (int)rintf(p[0]), iy = (int)rintf(p[1]), iz = (int)rintf(p[2]);
+            const float c = __ldg(colour + ((int64_t)ix * H + iy) * D + iz);
+            const float b = floorf(c / 65536.0f);
+            const float g = floorf((c - b * 65536.0f) / 256.0f);
+            const float r = c - b * 65536.0f - g * 256.0f;
+            rgb[3 * j] = (uint8_t)floorf(r); rgb[3 * j + 1] = (uint8_t)floorf(g); rgb[3 * j + 2] = (uint8_t)floorf(b);
+        }
+    }
+}
+
+}  // namespace ofx
+
+using namespace ofx;
+
+static int mc_check(const float *vol, int32_t Dx, int32_t Dy, int32_t Dz, const char *who)
+{
+    OFX_REQUIRE(Dx >= 0 && Dy >= 0 && Dz >= 0 && (int64_t)Dx * Dy < 2147483647LL, "%s: bad dimensions", who);
+    OFX_REQUIRE((int64_t)Dx * Dy * Dz == 0 || vol, "%s: null volume", who);
+    return 0;
+}
+
+extern "C" int ofx_mc_count(const float *vol, const uint8_t *mask, int32_t Dx, int32_t Dy, int32_t Dz, float level,
+                            uint8_t *tri_count, void *stream)
+{
+    if (mc_check(vol, Dx, Dy, Dz, "ofx_mc_count")) return 1;
+    if ((int64_t)Dx * Dy * Dz == 0) return 0;
+    OFX_REQUIRE(tri_count, "ofx_mc_count: null pointer");
+    const int rows = Dx * Dy, grid = rows < sm_count() * 8 ? rows : sm_count() * 8;
+    mc_count_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(vol, mask, Dx, Dy, Dz, level, tri_count);
+    OFX_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int ofx_mc_emit(const float *vol, const uint8_t *mask, int32_t Dx, int32_t Dy, int32_t Dz, float level,
+                           const uint8_t *tri_count, const int32_t *tri_offset, int64_t *keys, void *stream)
+{
+    if (mc_check(vol, Dx, Dy, Dz, "ofx_mc_emit")) return 1;
+    if ((int64_t)Dx * Dy * Dz == 0) return 0;
+    OFX_REQUIRE(tri_count && tri_offset && keys, "ofx_mc_emit: null pointer");
+    const int rows = Dx * Dy, grid = rows < sm_count() * 8 ? rows : sm_count() * 8;
+    mc_emit_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(vol, mask, Dx, Dy, Dz, level, tri_count, tri_offset, keys);
+    OFX_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int ofx_mc_vertices(const float *vol, const float *colour, int32_t Dx, int32_t Dy, int32_t Dz, float level,
+                               const int64_t *keys, int64_t n, float *verts, float *normals, uint8_t *rgb, void *stream)
+{
+    if (mc_check(vol, Dx, Dy, Dz, "ofx_mc_vertices")) return 1;
+    if (n == 0) return 0;
+    OFX_REQUIRE(keys && verts && n > 0 && (!rgb || colour), "ofx_mc_vertices: bad arguments");
+    int64_t blocks = (n + 255) / 256, cap = (int64_t)sm_count() * 8;
+    mc_vertices_kernel<<<(int)(blocks < cap ? blocks : cap), 256, 0, (cudaStream_t)stream>>>(vol, colour, Dx, Dy, Dz, level, keys, n,
+                                                                                            verts, normals, rgb);
+    OFX_LAUNCH_CHECK();
+    return 0;
+}

@@ -6,9 +6,10 @@ every per-voxel computation runs in libofx.so (include/ofx.h).  What the referen
 full-volume host arrays (`world_pts`, `vox_coords`, cached anchors/weights) is never
 materialised on the per-frame path; `world_pts` is produced on request.
 
-Not rebuilt here (SURVEY.md section 8f "next" rows): marching-cubes mesh extraction
-(tsdf.py:704-809) and everything that needs a visualiser.
+Surface extraction (tsdf.py:704-809) runs on the device too: truncated region + classic marching cubes + colour unpack
+(`get_mesh`, `get_canonical_model`).  Not rebuilt: everything that needs a visualiser.
 """
+import ctypes as C
 import logging
 import os
 import pickle
@@ -280,6 +281,61 @@ class TSDFVolume:
         assert self.n_shards == 1, "the truncated region looks at x-neighbours: gather the shards first (ShardedFusion.gather_volume)"
         return self.compute_truncated_region(self._tsdf_vol, max_diff)
 
-    def get_canonical_model(self):
-        raise NotImplementedError("marching cubes (skimage call at tsdf.py:794) is not rebuilt: get_truncated_region() gives its "
-                                  "mask; pass canonical vertices / faces to WarpField.update_graph explicitly")
+    @staticmethod
+    def marching_cubes(tsdf_vol, mask=None, level=0.0, color_vol=None):
+        """Classic marching cubes on the device (ofx_mc_count / ofx_mc_emit / ofx_mc_vertices; the scikit-image call of
+        tsdf.py:794 -- Lewiner's variant there, see DESIGN.md for what differs).  tsdf_vol / mask / color_vol: (Dx,Dy,Dz)
+        numpy arrays or CUDA tensors.  Returns CUDA tensors: verts (n,3) f32 in voxel coordinates (array axis order), faces
+        (T,3) i64, normals (n,3) f32 (unit gradient, towards increasing values), rgb (n,3) u8 or None.  Vertices are unique
+        per grid edge and sorted by edge; faces come in cube order."""
+        _capi.require_cuda()
+        lib = _capi.load()
+        dev = tsdf_vol.device if isinstance(tsdf_vol, torch.Tensor) and tsdf_vol.is_cuda \
+            else torch.device("cuda", torch.cuda.current_device())
+        t = _capi.to_device(tsdf_vol, torch.float32, dev)
+        assert t.dim() == 3
+        Dx, Dy, Dz = (int(d) for d in t.shape)
+        if mask is None:
+            m = None
+        elif isinstance(mask, torch.Tensor):
+            m = mask.to(dev).to(torch.uint8).contiguous()
+        else:
+            m = _capi.to_device(np.asarray(mask).astype(np.uint8), torch.uint8, dev)
+        c = None if color_vol is None else _capi.to_device(color_vol, torch.float32, dev)
+        lvl = C.c_float(level)
+        with torch.cuda.device(dev):
+            S = _capi.stream_ptr(dev)
+            count = torch.empty(t.numel(), dtype=torch.uint8, device=dev)
+            _capi.check(lib.ofx_mc_count(_capi.ptr(t), _capi.ptr(m), Dx, Dy, Dz, lvl, _capi.ptr(count), S))
+            incl = torch.cumsum(count, 0, dtype=torch.int32)                  # plumbing: prefix sum of the per-cube counts
+            T = int(incl[-1].item()) if incl.numel() else 0
+            offset = incl - count.to(torch.int32)
+            del incl
+            keys = torch.empty(3 * T, dtype=torch.int64, device=dev)
+            if T:
+                _capi.check(lib.ofx_mc_emit(_capi.ptr(t), _capi.ptr(m), Dx, Dy, Dz, lvl, _capi.ptr(count), _capi.ptr(offset),
+                                            _capi.ptr(keys), S))
+            ukeys, inverse = torch.unique(keys, sorted=True, return_inverse=True)    # plumbing: vertices = unique grid edges
+            n = int(ukeys.numel())
+            verts = torch.empty((n, 3), dtype=torch.float32, device=dev)
+            normals = torch.empty((n, 3), dtype=torch.float32, device=dev)
+            rgb = torch.empty((n, 3), dtype=torch.uint8, device=dev) if c is not None else None
+            if n:
+                _capi.check(lib.ofx_mc_vertices(_capi.ptr(t), _capi.ptr(c), Dx, Dy, Dz, lvl, _capi.ptr(ukeys.contiguous()), n,
+                                                _capi.ptr(verts), _capi.ptr(normals), _capi.ptr(rgb), S))
+        return verts, inverse.reshape(-1, 3), normals, rgb
+
+    def get_mesh(self):
+        """(verts, faces, norms, colors) of the zero level set inside the truncated region (tsdf.py:779-809): verts in world
+        coordinates, colors uint8 (r, g, b) of the voxel nearest to each vertex."""
+        assert self.n_shards == 1, "marching cubes needs the whole volume: gather the shards first (ShardedFusion.gather_volume)"
+        region = self.get_truncated_region(1.2)                                # tsdf.py:791
+        verts, faces, norms, rgb = self.marching_cubes(self._tsdf_vol, region, 0.0, self._color_vol)
+        verts = verts.cpu().numpy() * np.float32(self._voxel_size) + np.asarray(self._vol_origin, dtype=np.float32)   # :798
+        return verts, faces.cpu().numpy().astype(np.int32), norms.cpu().numpy(), rgb.cpu().numpy()
+
+    def get_canonical_model(self):                                            # tsdf.py:811-821
+        if hasattr(self, "canonical_model"):
+            return self.canonical_model
+        self.canonical_model = self.get_mesh()
+        return self.canonical_model

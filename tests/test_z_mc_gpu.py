@@ -1,0 +1,90 @@
+"""GPU: marching cubes on the device (ofx_mc_*; TSDFVolume.marching_cubes / get_mesh) against the CPU oracle's restatement
+of the same contract (oracle/ofx_oracle_mc.c): vertices, faces and colours identical.  Parity with the reference itself is
+UNPINNED for this step: the reference calls scikit-image (Lewiner's variant), which is not installed here."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _np_normals(vol, keys, level=0.0):
+    W, H, D = vol.shape
+    lower, axis = keys // 3, keys % 3
+    x, y, z = lower // (H * D), (lower // D) % H, lower % D
+
+    def grad(x, y, z):
+        xp, xm = np.minimum(x + 1, W - 1), np.maximum(x - 1, 0)
+        yp, ym = np.minimum(y + 1, H - 1), np.maximum(y - 1, 0)
+        zp, zm = np.minimum(z + 1, D - 1), np.maximum(z - 1, 0)
+        return np.stack([vol[xp, y, z] - vol[xm, y, z], vol[x, yp, z] - vol[x, ym, z], vol[x, y, zp] - vol[x, y, zm]], 1)
+
+    g0 = grad(x, y, z)
+    g1 = grad(x + (axis == 0), y + (axis == 1), z + (axis == 2))
+    stride = np.array([H * D, D, 1])[axis]
+    v0, v1 = vol.reshape(-1)[lower], vol.reshape(-1)[lower + stride]
+    t = ((np.float32(level) - v0) / (v1 - v0)).astype(np.float32)[:, None]
+    g = (g0 + t * (g1 - g0)).astype(np.float32)
+    s = (g[:, 0] * g[:, 0] + g[:, 1] * g[:, 1]) + g[:, 2] * g[:, 2]
+    return g * np.where(s > 0, np.float32(1) / np.sqrt(s), 0).astype(np.float32)[:, None]
+
+
+def _check(vol, mask, oracle, colour=None):
+    from occlusionfusion_b200 import TSDFVolume
+    v, f, n, rgb = TSDFVolume.marching_cubes(vol, mask, 0.0, colour)
+    ov, of, okeys = oracle.marching_cubes(vol, mask, 0.0)
+    assert np.array_equal(f.cpu().numpy(), of) and np.array_equal(v.cpu().numpy(), ov)
+    if len(ov):
+        assert np.abs(n.cpu().numpy() - _np_normals(vol, okeys)).max() < 1e-6
+    if colour is not None and len(ov):
+        ind = np.round(ov).astype(int)                                   # tsdf.py:797-807
+        c = colour[ind[:, 0], ind[:, 1], ind[:, 2]]
+        b = np.floor(c / 65536)
+        g = np.floor((c - b * 65536) / 256)
+        r = c - b * 65536 - g * 256
+        assert np.array_equal(rgb.cpu().numpy(), np.floor(np.asarray([r, g, b])).T.astype(np.uint8))
+    return ov, of
+
+
+def test_sphere_is_watertight_and_matches_oracle(oracle):
+    n = 48
+    x, y, z = np.meshgrid(*(np.arange(n),) * 3, indexing="ij")
+    centre = np.array([22.3, 24.1, 21.7])
+    vol = (np.sqrt((x - centre[0]) ** 2 + (y - centre[1]) ** 2 + (z - centre[2]) ** 2) - 14.4).astype(np.float32)
+    v, f = _check(vol, None, oracle)
+    e = np.sort(np.concatenate([f[:, [0, 1]], f[:, [1, 2]], f[:, [2, 0]]]), axis=1)
+    _, counts = np.unique(e, axis=0, return_counts=True)
+    assert (counts == 2).all() and len(v) - len(counts) + len(f) == 2          # closed manifold, Euler characteristic 2
+    assert np.abs(np.linalg.norm(v - centre, axis=1) - 14.4).max() < 0.02
+    a, b, c = v[f[:, 0]], v[f[:, 1]], v[f[:, 2]]
+    assert (((np.cross(b - a, c - a)) * ((a + b + c) / 3 - centre)).sum(1) > 0).all()   # normals from inside to outside
+
+
+def test_random_fields_masks_and_ragged_dims(oracle):
+    rng = np.random.default_rng(3)
+    for dims in ((14, 13, 15), (9, 33, 70), (2, 2, 2), (1, 5, 5), (31, 8, 260)):
+        vol = rng.normal(size=dims).astype(np.float32)
+        colour = np.floor(rng.random(dims) * 16777215).astype(np.float32)
+        _check(vol, None, oracle, colour)
+        _check(vol, rng.random(dims) < 0.4, oracle, colour)
+    _check(np.ones((8, 8, 8), np.float32), None, oracle)                       # no surface at all
+
+
+def test_get_mesh_of_integrated_volume(oracle):
+    """TSDFVolume.get_mesh (tsdf.py:779-809): truncated region -> marching cubes -> world coordinates + colours."""
+    from occlusionfusion_b200 import TSDFVolume
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload("tiny")
+    vol = TSDFVolume(w.bbox, w.max_depth, w.intr, w.fopt, None)
+    ov = oracle.OracleVolume(w.dims, w.origin, w.voxel_size, w.intr, w.trunc)
+    vol.integrate({"im": w.frame(0), "id": 0})
+    ov.integrate(w.frame(0), True)
+    verts, faces, norms, colors = vol.get_canonical_model()
+    region = oracle.truncated_region(ov.tsdf, 1.2)
+    overts, ofaces, _ = oracle.marching_cubes(ov.tsdf, region, 0.0)
+    assert len(ofaces) > 200 and np.array_equal(faces, ofaces) and faces.dtype == np.int32
+    assert np.array_equal(verts, overts * np.float32(w.voxel_size) + w.origin)
+    assert colors.dtype == np.uint8 and colors.shape == verts.shape and norms.shape == verts.shape
+    # the surface lies on the rendered sphere (band scene): within a voxel of its radius
+    r = np.linalg.norm(verts - w.centre, axis=1)
+    assert np.abs(r - w.radius).max() < 1.5 * w.voxel_size
+    assert vol.get_canonical_model() is vol.canonical_model                     # cached (tsdf.py:813)

@@ -1,5 +1,5 @@
 """Generates occlusionfusion_b200/csrc/ofx_mc_tables.h: the marching-cubes case table used by the CUDA kernels
-(csrc/ofx_mc.cu) and by the CPU oracle (oracle/ofx_oracle_mc.c).  Usage: python tools/gen_mc_tables.py
+(csrc/ofx_mc.cu) and by the test-only CPU checker (which includes this header).  Usage: python tools/gen_mc_tables.py
 
 The table is DERIVED, not transcribed: for each of the 256 sign patterns of a cube's corners the isosurface polygons
 are built from the six faces.  On a face (seen from outside the cube, corners counter-clockwise) every maximal run of
@@ -146,8 +146,8 @@ def main():
         # every undirected polygon edge inside the cube is shared by two triangles or lies on a face
     max_tris = max(len(t) for t in table)
     assert max_tris <= 5, max_tris
-    lines = ["// GENERATED by tools/gen_mc_tables.py -- do not edit.  Marching-cubes case table shared by csrc/ofx_mc.cu and",
-             "// oracle/ofx_oracle_mc.c.  corner c = x + 2y + 4z; edge e = 4*axis + (b0 + 2*b1); case bit c = corner c inside",
+    lines = ["// GENERATED by tools/gen_mc_tables.py -- do not edit.  Marching-cubes case table shared by csrc/ofx_mc.cu and the",
+             "// test-only CPU checker.  corner c = x + 2y + 4z; edge e = 4*axis + (b0 + 2*b1); case bit c = corner c inside",
              "// (value < level).  OFX_MC_TRIS[case] = number of triangles, OFX_MC_EDGES[case][3*t + k] = edge of corner k of",
              "// triangle t (normal from inside to outside).",
              "#ifndef OFX_MC_TABLES_H", "#define OFX_MC_TABLES_H", f"#define OFX_MC_MAX_TRIS {max_tris}",
