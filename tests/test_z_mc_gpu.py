@@ -84,7 +84,7 @@ def test_get_mesh_of_integrated_volume(oracle):
     assert len(ofaces) > 200 and np.array_equal(faces, ofaces) and faces.dtype == np.int32
     assert np.array_equal(verts, overts * np.float32(w.voxel_size) + w.origin)
     assert colors.dtype == np.uint8 and colors.shape == verts.shape and norms.shape == verts.shape
-    # the surface lies on the rendered sphere (band scene): within a voxel of its radius
+    # the surface lies on the rendered sphere (band scene): projective TSDF: within a voxel or two of its radius, worst at the silhouette
     r = np.linalg.norm(verts - w.centre, axis=1)
-    assert np.abs(r - w.radius).max() < 1.5 * w.voxel_size
+    assert np.abs(r - w.radius).max() < 2.5 * w.voxel_size and np.median(np.abs(r - w.radius)) < 0.5 * w.voxel_size
     assert vol.get_canonical_model() is vol.canonical_model                     # cached (tsdf.py:813)
