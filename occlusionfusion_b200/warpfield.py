@@ -261,13 +261,21 @@ class WarpField:
             self.updating_warpfield = False
             return False
         old_num_nodes = self.graph.nodes.shape[0]
+        old_nodes = np.array(self.graph.nodes[:old_num_nodes], copy=True)
+        R_rel, t_rel = self.get_transformation_wrt_graph_node()      # relative to the nodes as they are now
         # ... and, as in the reference (warpfield.py:516), the indices -- positions within the non-eroded subset -- are
         # handed to EDGraph.update together with the FULL vertex array.  Kept for identical results.
         update = self.graph.update(verts, faces, new_verts_indices)
         if update:
             M = self.graph.nodes.shape[0]
-            R_rel, t_rel = self.get_transformation_wrt_graph_node()
-            if getattr(self, "model", None) is not None and hasattr(self.graph, "get_reduced_graph"):
+            kept = M >= old_num_nodes and np.array_equal(self.graph.nodes[:old_num_nodes], old_nodes)
+            if not kept:
+                # the edge rebuild dropped nodes with too few neighbours and renumbered the rest (edg.py:596): every node of
+                # the new table takes the transform of the nearest old node (an old node that survived finds itself)
+                nearest = np.argmin(np.linalg.norm(self.graph.nodes[:, None, :] - old_nodes[None, :, :], axis=2), axis=1)
+                R_new, t_new = np.asarray(R_rel)[nearest], np.asarray(t_rel)[nearest]
+                deformed = self.graph.nodes + t_new
+            elif getattr(self, "model", None) is not None and hasattr(self.graph, "get_reduced_graph"):
                 valid_nodes_mask = np.zeros(M, dtype=bool)
                 valid_nodes_mask[:old_num_nodes] = True
                 graph_data = self.graph.get_reduced_graph(valid_nodes_mask)

@@ -88,3 +88,46 @@ def test_get_mesh_of_integrated_volume(oracle):
     r = np.linalg.norm(verts - w.centre, axis=1)
     assert np.abs(r - w.radius).max() < 2.5 * w.voxel_size and np.median(np.abs(r - w.radius)) < 0.5 * w.voxel_size
     assert vol.get_canonical_model() is vol.canonical_model                     # cached (tsdf.py:813)
+
+
+def test_update_graph_standalone_from_the_volume(oracle):
+    """WarpField.update_graph() with no arguments (warpfield.py:487-582): the canonical mesh comes from the volume itself
+    (truncated region -> marching cubes), nodes are inserted where the graph does not reach, the volume is re-skinned, and the
+    following frames stay bit-identical to the oracle driven through the same stages."""
+    from occlusionfusion_b200 import EDGraph, TSDFVolume, WarpField
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload("tiny")
+    vol = TSDFVolume(w.bbox, w.max_depth, w.intr, w.fopt, None)
+    ov = oracle.OracleVolume(w.dims, w.origin, w.voxel_size, w.intr, w.trunc)
+    nodes = w.nodes[: int(0.6 * w.M)].copy()
+    wf = WarpField(EDGraph(nodes=nodes, graph_generation_parameters={"node_coverage": w.coverage}), vol, None)
+    wf.graph_neighbours = w.K
+    vol.warpfield = wf
+    ov.set_graph(nodes, w.coverage, w.K)
+    vol.integrate({"im": w.frame(0), "id": 0})
+    ov.integrate(w.frame(0), True)
+    # expected insertion, stage by stage on the oracle's volume
+    overts, ofaces, _ = oracle.marching_cubes(ov.tsdf, oracle.truncated_region(ov.tsdf, 1.2), 0.0)
+    verts = overts * np.float32(w.voxel_size) + w.origin
+    ne = oracle.erode_mesh(len(verts), ofaces, 1, 3)
+    d, _ = oracle.nearest_node(verts[ne], nodes)
+    cand = np.where(d > 2 * w.coverage)[0]
+    cand = cand[np.argsort(d[cand])[::-1]]
+    acc = oracle.greedy_update(verts, cand, nodes, w.coverage)
+    assert len(acc) > 3
+    assert wf.update_graph() is True
+    new_nodes = wf.graph.nodes
+    inserted = {tuple(p) for p in verts[acc].tolist()}
+    assert inserted.issuperset({tuple(p) for p in new_nodes.tolist()} - {tuple(p) for p in nodes.tolist()})
+    if len(new_nodes) == len(nodes) + len(acc):                     # no node lost in the edge rebuild: exactly the greedy result
+        assert np.array_equal(new_nodes, np.concatenate([nodes, verts[acc]]))
+    assert wf.rotations.shape == (len(new_nodes), 3, 3) and hasattr(wf.graph, "edges") and wf.graph.edges.shape[0] == len(new_nodes)
+    ov.set_graph(new_nodes, w.coverage, w.K)
+    for f in (1, 2):
+        est = w.estimate(f, new_nodes)
+        wf.update_transformations(est)
+        ov.set_transforms(est["node_rotations"], wf.translations)
+        vol.integrate({"im": w.frame(f), "id": f})
+        assert vol.last_stats()["updated"] == ov.integrate(w.frame(f), False)
+    t, c, wt = vol.get_volume()
+    assert np.array_equal(wt, ov.weight) and np.array_equal(c, ov.colour) and np.array_equal(t, ov.tsdf)
