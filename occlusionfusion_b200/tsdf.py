@@ -339,3 +339,21 @@ class TSDFVolume:
             return self.canonical_model
         self.canonical_model = self.get_mesh()
         return self.canonical_model
+
+    def get_deformed_model(self):
+        """The canonical mesh warped to the current frame (tsdf.py:830-849): (vertices, faces, normals, colors)."""
+        if hasattr(self, "deformed_model"):
+            return self.deformed_model
+        if self.frame_id != self.fopt.source_frame:
+            vertices, faces, normals, colors = self.get_canonical_model()
+            deformed = self.warpfield.deform_mesh(vertices, normals)
+            self.deformed_model = (deformed[0], faces, deformed[1], colors)
+        else:
+            self.deformed_model = self.get_canonical_model()
+        return self.deformed_model
+
+    def clear(self):
+        """Drops the per-frame caches so that the next frame recomputes them (tsdf.py:857-877)."""
+        for name in ("reduced_graph_dict", "deformed_model", "canonical_model"):
+            if hasattr(self, name):
+                delattr(self, name)

@@ -131,3 +131,25 @@ def test_update_graph_standalone_from_the_volume(oracle):
         assert vol.last_stats()["updated"] == ov.integrate(w.frame(f), False)
     t, c, wt = vol.get_volume()
     assert np.array_equal(wt, ov.weight) and np.array_equal(c, ov.colour) and np.array_equal(t, ov.tsdf)
+
+
+def test_deformed_model_and_clear(oracle):
+    """get_deformed_model (tsdf.py:830-849) = canonical mesh through WarpField.deform_mesh; clear() drops the caches."""
+    from occlusionfusion_b200 import TSDFVolume, WarpField
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload("tiny")
+    vol = TSDFVolume(w.bbox, w.max_depth, w.intr, w.fopt, None)
+    wf = WarpField(w.graph(), vol, None)
+    vol.warpfield = wf
+    vol.integrate({"im": w.frame(0), "id": 0})
+    assert vol.get_deformed_model() is vol.get_canonical_model()                # source frame: the canonical model itself
+    vol.clear()
+    assert not hasattr(vol, "canonical_model") and not hasattr(vol, "deformed_model")
+    est = w.estimate(1)
+    wf.update_transformations(est)
+    vol.integrate({"im": w.frame(1), "id": 1})
+    dv, df, dn, dc = vol.get_deformed_model()
+    cv, cf, cn, cc = vol.get_canonical_model()
+    a, wt, valid = oracle.skin(cv, w.nodes, w.K, w.coverage)
+    assert np.array_equal(dv, oracle.warp(cv, a, wt, valid, est["node_rotations"], wf.translations))
+    assert df is cf and dc is cc and dn.shape == cn.shape and valid.mean() > 0.9
