@@ -171,8 +171,8 @@ int ofx_truncated_region(const float *tsdf, int32_t Dx, int32_t Dy, int32_t Dz, 
 /* ---- marching cubes (the scikit-image call at fusion_with_occlusion/tsdf.py:794 and the colour unpack at :797-807) ----
  * Classic form with the case table of csrc/ofx_mc_tables.h.  vol / mask / colour are whole (Dx,Dy,Dz) volumes, C order;
  * cube i = (x*Dy + y)*Dz + z is processed when mask == NULL or mask[i] != 0; corners with value < level are inside.
- *   1. ofx_mc_count:    tri_count (N,) u8 = triangles of every cube.
- *   2. the caller forms tri_offset (N,) i32 = exclusive prefix sum of tri_count, T = total.
+ *   1. ofx_mc_count:    row_count (Dx*Dy,) i32 = triangles of every z-row of cubes (row = x*Dy + y).
+ *   2. the caller forms row_offset (Dx*Dy,) i32 = exclusive prefix sum of row_count, T = total.
  *   3. ofx_mc_emit:     keys (3T,) i64, three per triangle in cube order: a triangle corner is named by its grid edge,
  *                       key = 3 * (linear index of the edge's lower corner) + axis.
  *   4. the caller sorts the keys into unique vertices (faces = index of each key among the unique keys).
@@ -180,9 +180,9 @@ int ofx_truncated_region(const float *tsdf, int32_t Dx, int32_t Dy, int32_t Dz, 
  *                       axis, float32), optionally the unit gradient normal (towards increasing values) and the colour of
  *                       the nearest voxel unpacked to r, g, b bytes (tsdf.py:797-807; rgb needs colour). */
 int ofx_mc_count(const float *vol, const uint8_t *mask, int32_t Dx, int32_t Dy, int32_t Dz, float level,
-                 uint8_t *tri_count, void *stream);
+                 int32_t *row_count, void *stream);
 int ofx_mc_emit(const float *vol, const uint8_t *mask, int32_t Dx, int32_t Dy, int32_t Dz, float level,
-                const uint8_t *tri_count, const int32_t *tri_offset, int64_t *keys, void *stream);
+                const int32_t *row_count, const int32_t *row_offset, int64_t *keys, void *stream);
 int ofx_mc_vertices(const float *vol, const float *colour, int32_t Dx, int32_t Dy, int32_t Dz, float level,
                     const int64_t *keys, int64_t n, float *verts, float *normals, uint8_t *rgb, void *stream);
 

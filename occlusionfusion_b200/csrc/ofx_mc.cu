@@ -4,9 +4,11 @@
 // by tools/gen_mc_tables.py), vertices on the grid edges at the linear zero crossing.  scikit-image is absent here, so this
 // is checked against the CPU restatement of the same contract (the marching-cubes file of the test-only CPU checker), not against the reference's output.
 //   Three streaming passes, no atomics, deterministic output order:
-//     ofx_mc_count     per cube: number of triangles (u8)                      4 B read + 1 B mask + 1 B written per voxel
-//     [exclusive prefix sum of the counts: caller, e.g. torch.cumsum]
-//     ofx_mc_emit      per cube: its triangles as grid-edge keys (3 * lower-corner index + axis) at the cube's offset
+//     ofx_mc_count     per z-row (x*Dy + y): number of triangles (nothing per voxel is stored; 1 B of mask read per voxel,
+//                      the 8 corners only where the mask holds)
+//     [exclusive prefix sum over the Dx*Dy rows: caller, e.g. torch.cumsum]
+//     ofx_mc_emit      per row: recomputes the cases, block scan along z, writes the triangles as grid-edge keys
+//                      (3 * lower-corner index + axis) at row offset + in-row prefix
 //     [unique keys = vertices, inverse = faces: caller, e.g. torch.unique]
 //     ofx_mc_vertices  per unique key: position (voxel coordinates), gradient normal, unpacked colour
 // A block walks z-rows (row = x*Dy + y: one division per row), threads run along z (coalesced).
@@ -36,30 +38,57 @@ __device__ __forceinline__ int mc_case(const float *__restrict__ vol, const uint
     return c;
 }
 
-__global__ void __launch_bounds__(256) mc_count_kernel(const float *__restrict__ vol, const uint8_t *__restrict__ mask, int W, int H,
-                                                       int D, float level, uint8_t *__restrict__ count)
+// block-wide exclusive scan of one int per thread (256 threads); returns the exclusive prefix, *total = block sum
+__device__ __forceinline__ int block_exclusive_scan(int v, int *s_warp, int *total)
 {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+    __syncthreads();                       // s_warp may still be read by the previous call
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    int before = 0, sum = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) { const int t = s_warp[w]; if (w < warp) before += t; sum += t; }
+    *total = sum;
+    return before + incl - v;
+}
+
+// pass 1: triangles per z-row (row = x*Dy + y).  Nothing per voxel is stored: pass 2 recomputes the cases.
+__global__ void __launch_bounds__(256) mc_count_kernel(const float *__restrict__ vol, const uint8_t *__restrict__ mask, int W, int H,
+                                                       int D, float level, int32_t *__restrict__ row_count)
+{
+    __shared__ int s_warp[8];
     for (int r = blockIdx.x; r < W * H; r += gridDim.x) {
         const int x = r / H, y = r - x * H;
-        for (int z = threadIdx.x; z < D; z += blockDim.x) {
-            const int64_t i = (int64_t)r * D + z;
-            count[i] = OFX_MC_TRIS[mc_case(vol, mask, i, x, y, z, W, H, D, level)];
-        }
+        int mine = 0;
+        for (int z = threadIdx.x; z < D; z += blockDim.x)
+            mine += OFX_MC_TRIS[mc_case(vol, mask, (int64_t)r * D + z, x, y, z, W, H, D, level)];
+        int total;
+        block_exclusive_scan(mine, s_warp, &total);
+        if (threadIdx.x == 0) row_count[r] = total;
     }
 }
 
+// pass 2: a block per z-row writes the row's triangles at the row's offset, cubes in z order (block scan per 256-cube chunk)
 __global__ void __launch_bounds__(256) mc_emit_kernel(const float *__restrict__ vol, const uint8_t *__restrict__ mask, int W, int H,
-                                                      int D, float level, const uint8_t *__restrict__ count,
-                                                      const int32_t *__restrict__ offset, int64_t *__restrict__ keys)
+                                                      int D, float level, const int32_t *__restrict__ row_count,
+                                                      const int32_t *__restrict__ row_offset, int64_t *__restrict__ keys)
 {
+    __shared__ int s_warp[8];
     for (int r = blockIdx.x; r < W * H; r += gridDim.x) {
+        if (__ldg(row_count + r) == 0) continue;                      // uniform across the block
         const int x = r / H, y = r - x * H;
-        for (int z = threadIdx.x; z < D; z += blockDim.x) {
+        int carry = __ldg(row_offset + r);
+        for (int z0 = 0; z0 < D; z0 += blockDim.x) {
+            const int z = z0 + threadIdx.x;
             const int64_t i = (int64_t)r * D + z;
-            const int nt = __ldg(count + i);
-            if (!nt) continue;
-            const int c = mc_case(vol, mask, i, x, y, z, W, H, D, level);
-            int64_t *out = keys + 3 * (int64_t)__ldg(offset + i);
+            const int c = z < D ? mc_case(vol, mask, i, x, y, z, W, H, D, level) : 0;
+            const int nt = OFX_MC_TRIS[c];
+            int total;
+            const int before = block_exclusive_scan(nt, s_warp, &total);
+            int64_t *out = keys + 3 * (int64_t)(carry + before);
             for (int k = 0; k < 3 * nt; ++k) {
                 const int e = OFX_MC_EDGES[c][k], axis = e >> 2, b = e & 3;
                 // lower corner of edge e: offsets (b & 1, b >> 1) along the two other axes, in increasing axis order
@@ -67,6 +96,7 @@ __global__ void __launch_bounds__(256) mc_emit_kernel(const float *__restrict__ 
                 const int oy = axis == 0 ? (b & 1) : (axis == 1 ? 0 : (b >> 1));
                 out[k] = 3 * (i + ((int64_t)ox * H + oy) * D + oz) + axis;
             }
+            carry += total;
         }
     }
 }
@@ -129,25 +159,25 @@ static int mc_check(const float *vol, int32_t Dx, int32_t Dy, int32_t Dz, const 
 }
 
 extern "C" int ofx_mc_count(const float *vol, const uint8_t *mask, int32_t Dx, int32_t Dy, int32_t Dz, float level,
-                            uint8_t *tri_count, void *stream)
+                            int32_t *row_count, void *stream)
 {
     if (mc_check(vol, Dx, Dy, Dz, "ofx_mc_count")) return 1;
     if ((int64_t)Dx * Dy * Dz == 0) return 0;
-    OFX_REQUIRE(tri_count, "ofx_mc_count: null pointer");
+    OFX_REQUIRE(row_count, "ofx_mc_count: null pointer");
     const int rows = Dx * Dy, grid = rows < sm_count() * 8 ? rows : sm_count() * 8;
-    mc_count_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(vol, mask, Dx, Dy, Dz, level, tri_count);
+    mc_count_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(vol, mask, Dx, Dy, Dz, level, row_count);
     OFX_LAUNCH_CHECK();
     return 0;
 }
 
 extern "C" int ofx_mc_emit(const float *vol, const uint8_t *mask, int32_t Dx, int32_t Dy, int32_t Dz, float level,
-                           const uint8_t *tri_count, const int32_t *tri_offset, int64_t *keys, void *stream)
+                           const int32_t *row_count, const int32_t *row_offset, int64_t *keys, void *stream)
 {
     if (mc_check(vol, Dx, Dy, Dz, "ofx_mc_emit")) return 1;
     if ((int64_t)Dx * Dy * Dz == 0) return 0;
-    OFX_REQUIRE(tri_count && tri_offset && keys, "ofx_mc_emit: null pointer");
+    OFX_REQUIRE(row_count && row_offset && keys, "ofx_mc_emit: null pointer");
     const int rows = Dx * Dy, grid = rows < sm_count() * 8 ? rows : sm_count() * 8;
-    mc_emit_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(vol, mask, Dx, Dy, Dz, level, tri_count, tri_offset, keys);
+    mc_emit_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(vol, mask, Dx, Dy, Dz, level, row_count, row_offset, keys);
     OFX_LAUNCH_CHECK();
     return 0;
 }

@@ -305,12 +305,11 @@ class TSDFVolume:
         lvl = C.c_float(level)
         with torch.cuda.device(dev):
             S = _capi.stream_ptr(dev)
-            count = torch.empty(t.numel(), dtype=torch.uint8, device=dev)
+            count = torch.zeros(max(Dx * Dy, 1), dtype=torch.int32, device=dev)
             _capi.check(lib.ofx_mc_count(_capi.ptr(t), _capi.ptr(m), Dx, Dy, Dz, lvl, _capi.ptr(count), S))
-            incl = torch.cumsum(count, 0, dtype=torch.int32)                  # plumbing: prefix sum of the per-cube counts
-            T = int(incl[-1].item()) if incl.numel() else 0
-            offset = incl - count.to(torch.int32)
-            del incl
+            incl = torch.cumsum(count, 0, dtype=torch.int32)                  # plumbing: prefix sum over the Dx*Dy rows
+            T = int(incl[-1].item())
+            offset = (incl - count).contiguous()
             keys = torch.empty(3 * T, dtype=torch.int64, device=dev)
             if T:
                 _capi.check(lib.ofx_mc_emit(_capi.ptr(t), _capi.ptr(m), Dx, Dy, Dz, lvl, _capi.ptr(count), _capi.ptr(offset),
