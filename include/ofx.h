@@ -138,6 +138,13 @@ int ofx_check_visibility(const float *points, int64_t n, const float *depth, int
  * float32 distance to and index of the nearest node, ties -> lower index.  dist or idx may be NULL. */
 int ofx_nearest_node(const float *points, int64_t n, const float *nodes, int32_t M, float *dist,
                      int32_t *idx, void *stream);
+/* compute_pixel_anchors_euclidean (csrc/cpu/graph_proc.cpp:610-709, binding csrc/main.cpp:35): for every pixel of the
+ * (3,H,W) point image with z > 0 its 4 (GRAPH_K, graph_proc.h:8) nearest nodes by squared distance -- among equal distances
+ * the later node first -- and their Gaussian weights normalised by their sum; anchors (H,W,4) i32 (-1 = none), weights
+ * (H,W,4) f32.  The per-voxel skinning of the fusion path follows WarpField.skin instead (ofx_skin). */
+int ofx_pixel_anchors_euclidean(const float *nodes, int32_t M, const float *point_image, int32_t H,
+                                int32_t W, float node_coverage, int32_t *anchors, float *weights,
+                                void *stream);
 /* np.argmin(np.linalg.norm(points - q, axis=1)) for every query q (EDGraph.update re-anchoring the nodes on the new mesh,
  * fusion_with_occlusion/embedded_deformation_graph.py:545-547, which builds the dense (queries x points) matrix on the
  * host): float32 norms, first index among equal norms.  dist or idx may be NULL. */

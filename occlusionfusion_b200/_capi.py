@@ -22,7 +22,7 @@ SYMBOLS = [
     "ofx_volume_num_voxels", "ofx_set_graph", "ofx_set_transforms", "ofx_integrate", "ofx_prepare_frame",
     "ofx_volume_world_points", "ofx_volume_skin", "ofx_volume_deform", "ofx_pack_frame", "ofx_skin",
     "ofx_warp_points", "ofx_check_visibility", "ofx_peer_copy",
-    "ofx_nearest_node", "ofx_argmin_norm", "ofx_greedy_insert", "ofx_sample_nodes", "ofx_erode_mesh", "ofx_truncated_region",
+    "ofx_nearest_node", "ofx_pixel_anchors_euclidean", "ofx_argmin_norm", "ofx_greedy_insert", "ofx_sample_nodes", "ofx_erode_mesh", "ofx_truncated_region",
     "ofx_mc_count", "ofx_mc_emit", "ofx_mc_vertices",
     "ofx_compute_edges_geodesic_host", "ofx_node_and_edge_clean_up_host", "ofx_compute_clusters_host",
 ]
@@ -73,6 +73,7 @@ def load():
     lib.ofx_peer_copy.argtypes = [vp, vp, i64, i32, vp]
     lib.ofx_check_visibility.argtypes = [vp, i64, vp, i32, i32, C.POINTER(C.c_float), f64, vp, vp, vp]
     lib.ofx_nearest_node.argtypes = [vp, i64, vp, i32, vp, vp, vp]
+    lib.ofx_pixel_anchors_euclidean.argtypes = [vp, i32, vp, i32, i32, C.c_float, vp, vp, vp]
     lib.ofx_argmin_norm.argtypes = [vp, i64, vp, i32, vp, vp, vp]
     lib.ofx_greedy_insert.argtypes = [vp, i32, vp, i32, vp, i32, f64, vp, vp, vp]
     lib.ofx_sample_nodes.argtypes = [vp, i32, vp, C.c_float, i32, vp, vp, vp, vp]

@@ -103,6 +103,72 @@ __global__ void __launch_bounds__(256) nearest_node_kernel(const float *__restri
     }
 }
 
+// ---- pixel anchors (Euclidean) -------------------------------------------------------------------------------------
+// compute_pixel_anchors_euclidean (csrc/cpu/graph_proc.cpp:610-709): for every pixel of a (3,H,W) point image with z > 0 the
+// PIXEL_K = 4 nearest nodes by squared distance (Eigen order dx^2 + (dy^2 + dz^2)), kept sorted by insertion with <=, so that
+// among equal distances the later node comes first (:656), Gaussian weights exp(-d2 / (2 c^2)) normalised by their sum (no
+// 1e-6 here, :694-699).  One thread per pixel, node tiles in shared memory.  exp is evaluated in float64 and rounded once,
+// which is what glibc's float exp amounts to in all but ~1e-8 of the cases (the reference calls std::exp on a float).
+constexpr int PIXEL_K = 4;
+__global__ void __launch_bounds__(256) pixel_anchors_kernel(const float *__restrict__ nodes, int M, const float *__restrict__ img,
+                                                            int64_t npix, float coverage, int32_t *__restrict__ anchors,
+                                                            float *__restrict__ weights)
+{
+    __shared__ float s_nodes[GRAPH_NODE_TILE * 3];
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t n_round = ((npix + stride - 1) / stride) * stride;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n_round; i += stride) {
+        const bool live = i < npix;
+        float px = 0.f, py = 0.f, pz = 0.f;
+        if (live) { px = __ldg(img + i); py = __ldg(img + npix + i); pz = __ldg(img + 2 * npix + i); }
+        const bool use = live && pz > 0.0f;                                                   // :641
+        float bd[PIXEL_K];
+        int bi[PIXEL_K];
+        int cnt = 0;
+#pragma unroll
+        for (int k = 0; k < PIXEL_K; ++k) { bd[k] = 0.f; bi[k] = -1; }
+        for (int base = 0; base < M; base += GRAPH_NODE_TILE) {
+            const int tile = min(GRAPH_NODE_TILE, M - base);
+            __syncthreads();
+            for (int t = threadIdx.x; t < tile * 3; t += blockDim.x) s_nodes[t] = __ldg(nodes + (int64_t)base * 3 + t);
+            __syncthreads();
+            if (!use) continue;
+            for (int j = 0; j < tile; ++j) {
+                const float dx = px - s_nodes[3 * j], dy = py - s_nodes[3 * j + 1], dz = pz - s_nodes[3 * j + 2];
+                const float d2 = (dx * dx) + ((dy * dy) + (dz * dz));
+                // first position whose distance is >= d2 (:656); none: append while fewer than K are held (:663)
+                int pos = cnt;
+#pragma unroll
+                for (int k = PIXEL_K - 1; k >= 0; --k)
+                    if (k < cnt && d2 <= bd[k]) pos = k;
+                if (pos >= PIXEL_K) continue;
+#pragma unroll
+                for (int k = PIXEL_K - 1; k > 0; --k)
+                    if (k > pos) { bd[k] = bd[k - 1]; bi[k] = bi[k - 1]; }
+#pragma unroll
+                for (int k = 0; k < PIXEL_K; ++k)
+                    if (k == pos) { bd[k] = d2; bi[k] = base + j; }
+                if (cnt < PIXEL_K) ++cnt;
+            }
+        }
+        if (!live) continue;
+        float w[PIXEL_K], sum = 0.0f;
+        const float denom = 2.f * coverage * coverage;                                        // :148
+#pragma unroll
+        for (int k = 0; k < PIXEL_K; ++k) {
+            w[k] = k < cnt ? (float)exp((double)(-bd[k] / denom)) : 0.0f;
+            if (k < cnt) sum += w[k];
+        }
+#pragma unroll
+        for (int k = 0; k < PIXEL_K; ++k) {
+            float v = 0.0f;
+            if (k < cnt) v = sum > 0.0f ? w[k] / sum : 1.f / (float)cnt;                      // :694-699
+            anchors[PIXEL_K * i + k] = k < cnt ? bi[k] : -1;
+            weights[PIXEL_K * i + k] = v;
+        }
+    }
+}
+
 // ---- greedy selection: pre-filter --------------------------------------------------------------------------------
 // Bit i of `bits` = candidate i may still become a node:
 //   EDGraph.update   (mask == NULL): no existing node closer than node_coverage          edg.py:522
@@ -530,6 +596,19 @@ extern "C" int ofx_argmin_norm(const float *queries, int64_t n, const float *poi
     if (n == 0) return 0;
     OFX_REQUIRE(queries && points && (dist || idx), "ofx_argmin_norm: null pointer");
     nearest_node_kernel<true><<<graph_grid_for(n, 64, 16), 64, 0, (cudaStream_t)stream>>>(queries, n, points, M, dist, idx);
+    OFX_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int ofx_pixel_anchors_euclidean(const float *nodes, int32_t M, const float *point_image, int32_t H, int32_t W,
+                                           float node_coverage, int32_t *anchors, float *weights, void *stream)
+{
+    OFX_REQUIRE(M >= 0 && H >= 0 && W >= 0, "ofx_pixel_anchors_euclidean: bad sizes");
+    const int64_t npix = (int64_t)H * W;
+    if (npix == 0) return 0;
+    OFX_REQUIRE(point_image && anchors && weights && (M == 0 || nodes), "ofx_pixel_anchors_euclidean: null pointer");
+    pixel_anchors_kernel<<<graph_grid_for(npix, 256, 4), 256, 0, (cudaStream_t)stream>>>(nodes, M, point_image, npix, node_coverage,
+                                                                                        anchors, weights);
     OFX_LAUNCH_CHECK();
     return 0;
 }

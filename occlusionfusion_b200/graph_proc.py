@@ -61,3 +61,24 @@ def compute_clusters_c(graph_edges, graph_clusters):
     n = C.c_int32(0)
     _capi.check(_capi.load().ofx_compute_clusters_host(_p(e), e.shape[0], e.shape[1], _p(c), _p(sizes), C.byref(n)))
     return sizes[:n.value].tolist()
+
+
+def compute_pixel_anchors_euclidean_c(graph_nodes, point_image, node_coverage, pixel_anchors, pixel_weights):
+    """graph_proc.cpp:610-709 (binding csrc/main.cpp:35) on the device (ofx_pixel_anchors_euclidean): point_image (3,H,W) f32;
+    pixel_anchors (i32) / pixel_weights (f32) are resized in place to (H,W,4), as the reference's callee does, and filled."""
+    import torch
+    _capi.require_cuda()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    nodes = _capi.to_device(np.asarray(graph_nodes), torch.float32, dev).reshape(-1, 3)
+    img = _capi.to_device(np.asarray(point_image), torch.float32, dev)
+    assert img.dim() == 3 and img.shape[0] >= 3
+    H, W = int(img.shape[1]), int(img.shape[2])
+    a = torch.empty((H, W, 4), dtype=torch.int32, device=dev)
+    w = torch.empty((H, W, 4), dtype=torch.float32, device=dev)
+    _capi.check(_capi.load().ofx_pixel_anchors_euclidean(_capi.ptr(nodes) if nodes.shape[0] else None, nodes.shape[0],
+                                                         _capi.ptr(img[:3].contiguous()), H, W, C.c_float(node_coverage),
+                                                         _capi.ptr(a), _capi.ptr(w), _capi.stream_ptr(dev)))
+    for dst, src, dt in ((pixel_anchors, a, np.int32), (pixel_weights, w, np.float32)):
+        _inplace(dst, dt, "pixel_anchors / pixel_weights")
+        dst.resize((H, W, 4), refcheck=False)
+        dst[...] = src.cpu().numpy()

@@ -244,6 +244,20 @@ def main():
         pass
     out["upd2_cand"], out["upd2_nodes_after"] = cand2, g2.nodes
 
+    # ---- pixel anchors (reference C++, graph_proc.cpp:610-709): a point image of the height field with holes, and a node
+    #      set with exact duplicates so that the tie rule (later node first) decides ---------------------------------------
+    Hh, Ww = 40, 56
+    uu, vv = np.meshgrid(np.linspace(-0.5, 0.5, Ww), np.linspace(-0.4, 0.4, Hh))
+    zz = 1.0 + 0.15 * np.sin(5 * uu) * np.cos(4 * vv)
+    pimg = np.stack([uu, vv, zz]).astype(np.float32)
+    pimg[:, rng.random((Hh, Ww)) < 0.1] = 0.0                                  # invalid pixels (z <= 0)
+    pa_nodes = np.concatenate([out["sample_pos_1"][:120], out["sample_pos_1"][:15]]).astype(np.float32)
+    for name, nd in (("all", pa_nodes), ("three", pa_nodes[:3])):
+        pa, pw = np.zeros(0, np.int32), np.zeros(0, np.float32)
+        ref_graph.compute_pixel_anchors_euclidean(nd, pimg, coverage, pa, pw)
+        out[f"pix_{name}_anchors"], out[f"pix_{name}_weights"] = pa.copy(), pw.copy()
+    out["pix_image"], out["pix_nodes"] = pimg, pa_nodes
+
     # ---- f3: compute_truncated_region (reference numba) on the reference's own integrated volume ------------------
     g = np.load(os.path.join(GOLDEN_DIR, "ref_k4.npz"))
     for key in ("tsdf_0", "tsdf_2"):

@@ -12,4 +12,5 @@ PYBIND11_MODULE(ref_graph, m) {
     m.def("compute_edges_geodesic", &graph_proc::compute_edges_geodesic, "");   // graph_proc.cpp:155-300
     m.def("node_and_edge_clean_up", &graph_proc::node_and_edge_clean_up, "");   // graph_proc.cpp:388-438
     m.def("compute_clusters", &graph_proc::compute_clusters, "");               // graph_proc.cpp:440-481
+    m.def("compute_pixel_anchors_euclidean", &graph_proc::compute_pixel_anchors_euclidean, "");   // graph_proc.cpp:610-709
 }

@@ -319,3 +319,18 @@ def test_full_update_matches_reference(gg):
     assert sorted(g.pyd) == sorted(keys)
     for k in keys:
         assert np.array_equal(np.asarray(g.pyd[k]), gg["fullpyd_" + k]), k
+
+
+def test_pixel_anchors_euclidean_match_reference(gg):
+    """compute_pixel_anchors_euclidean (csrc/cpu/graph_proc.cpp:610-709) on the device against the reference's C++: anchors
+    identical (duplicated nodes exercise the later-node-first tie rule), weights within 1e-6 (std::exp on a float there,
+    float64 exp rounded once here)."""
+    from occlusionfusion_b200.graph_proc import compute_pixel_anchors_euclidean_c
+    for name, nodes in (("all", gg["pix_nodes"]), ("three", gg["pix_nodes"][:3])):
+        a, w = np.zeros(0, np.int32), np.zeros(0, np.float32)
+        compute_pixel_anchors_euclidean_c(nodes, gg["pix_image"], float(gg["coverage"]), a, w)
+        assert a.shape == gg[f"pix_{name}_anchors"].shape and np.array_equal(a, gg[f"pix_{name}_anchors"])
+        assert np.abs(w - gg[f"pix_{name}_weights"]).max() <= 1e-6
+        assert (w == gg[f"pix_{name}_weights"]).mean() > 0.99
+    assert (gg["pix_all_anchors"] >= 120).sum() > 50 and (gg["pix_all_anchors"][..., 0] == -1).mean() > 0.05
+    assert (gg["pix_three_anchors"][..., 3] == -1).all()                 # three nodes: the fourth slot stays empty
