@@ -10,6 +10,11 @@
  *   - the pykdtree query + numpy weights in `WarpField.skin`   fusion_with_occlusion/warpfield.py:83-129
  *   - the numpy/numba CPU branch of `TSDFVolume.integrate`     fusion_with_occlusion/tsdf.py:442-494
  *     (this branch defines the arithmetic: see DESIGN.md "contract arithmetic")
+ *   - the callers either side of that path (declared further down, each with its own citation):
+ *         graph maintenance      NeuralNRT._C (pybind11, csrc/main.cpp:7-40): erode_mesh, sample_nodes, compute_edges_geodesic,
+ *                                node_and_edge_clean_up, compute_clusters, compute_pixel_anchors_euclidean
+ *                                (csrc/cpu/graph_proc.cpp), the Python loops of EDGraph.update and find_unreachable_nodes
+ *         surface extraction     numba compute_truncated_region (tsdf.py:706-745), skimage marching cubes (tsdf.py:794)
  *
  * Conventions
  *   - plain C: opaque handle, raw pointers, sizes; no C++ or torch types; no exceptions.
