@@ -221,6 +221,12 @@ int ofx_node_and_edge_clean_up_host(const int32_t *edges_host, int32_t M, int32_
 int ofx_compute_clusters_host(const int32_t *edges_host, int32_t M, int32_t E, int32_t *clusters_host,
                               int32_t *sizes_host, int32_t *n_clusters_host);
 
+/* One level of EDGraph.create_graph_pyramid's greedy down-sampling (embedded_deformation_graph.py:279-298): down_idx
+ * (capacity M) = nodes kept for the coarser level, in order; up_idx (M,) = for every node the position, within the kept
+ * list, of the nearest node kept before it. */
+int ofx_downsample_nodes_host(const float *nodes_host, int32_t M, double coverage, int32_t *down_idx_host,
+                              int32_t *n_down_host, int32_t *up_idx_host);
+
 /* ---- multi-GPU plumbing ------------------------------------------------------------------------ */
 /* Copies `bytes` (a multiple of 16, both pointers 16-byte aligned) from `src` to `dst` with `ctas`
  * thread blocks.  `src` may be a PEER pointer (another GPU's buffer mapped into this process through

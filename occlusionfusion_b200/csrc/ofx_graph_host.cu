@@ -200,3 +200,34 @@ extern "C" int ofx_compute_clusters_host(const int32_t *edges_host, int32_t M, i
     *n_clusters_host = nc;
     return 0;
 }
+
+// One level of the node pyramid (fusion_with_occlusion/embedded_deformation_graph.py:279-298): nodes in index order; a node
+// joins the coarser level unless a node kept before it is closer than `coverage`; up_idx[i] = position (within the kept
+// list) of the kept node nearest to node i at the moment i is examined (0 for the first node).  float32 norms
+// sqrtf((dx^2+dy^2)+dz^2), first index among equal norms, float64 comparison with the bound.
+extern "C" int ofx_downsample_nodes_host(const float *nodes_host, int32_t M, double coverage, int32_t *down_idx_host,
+                                         int32_t *n_down_host, int32_t *up_idx_host)
+{
+    OFX_REQUIRE(M >= 0 && n_down_host, "ofx_downsample_nodes_host: bad arguments");
+    *n_down_host = 0;
+    if (M == 0) return 0;
+    OFX_REQUIRE(nodes_host && down_idx_host && up_idx_host, "ofx_downsample_nodes_host: null pointer");
+    int kept = 0;
+    for (int i = 0; i < M; ++i) {
+        if (kept == 0) { up_idx_host[i] = i; down_idx_host[kept++] = i; continue; }          // :280-283
+        const float *p = nodes_host + 3 * (int64_t)i;
+        float best = INFINITY;
+        int bi = 0;
+        for (int k = 0; k < kept; ++k) {
+            const float *q = nodes_host + 3 * (int64_t)down_idx_host[k];
+            const float dx = q[0] - p[0], dy = q[1] - p[1], dz = q[2] - p[2];
+            const float d = std::sqrt(((dx * dx) + (dy * dy)) + (dz * dz));
+            if (d < best) { best = d; bi = k; }
+        }
+        up_idx_host[i] = bi;                                                                // :290
+        if ((double)best < coverage) continue;                                              // :292
+        down_idx_host[kept++] = i;
+    }
+    *n_down_host = kept;
+    return 0;
+}

@@ -18,7 +18,7 @@ import numpy as np
 import torch
 
 from . import _capi
-from .graph_proc import compute_clusters_c, compute_edges_geodesic_c, node_and_edge_clean_up_c
+from .graph_proc import compute_clusters_c, compute_edges_geodesic_c, downsample_nodes, node_and_edge_clean_up_c
 
 DEFAULT_GRAPH_PARAMETERS = {           # embedded_deformation_graph.py:62-73
     "max_triangle_distance": 0.05,
@@ -127,23 +127,17 @@ class EDGraph:
             raise RuntimeError("No nodes left in the graph")                                  # the reference exit()s, :400-402
         if len(black) > 0:
             new_id = np.where(keep, np.cumsum(keep) - 1, -1).astype(np.int32)                 # old id -> new id, -1 = dropped
-            E = graph_edges.shape[1]
-            for r in range(num_nodes):
-                row = graph_edges[r].copy()
-                ok = ~np.isin(row, black)                                                     # -1 entries count as kept (:424)
-                k = int(ok.sum())
-                w_row, d_row = graph_edges_weights[r, ok].copy(), graph_edges_distances[r, ok].copy()
-                ids = row[ok]
-                graph_edges[r] = -1
-                graph_edges_weights[r] = 0
-                graph_edges_distances[r] = 0
-                graph_edges[r, :k] = np.where(ids == -1, -1, new_id[np.maximum(ids, 0)])
-                graph_edges_weights[r, :k] = w_row
-                graph_edges_distances[r, :k] = d_row
-                sum_weights = np.sum(graph_edges_weights[r])
-                if sum_weights > 0:
-                    graph_edges_weights[r] /= (sum_weights + 1e-6)                            # :452-454
-                assert k <= E
+            ok = ~np.isin(graph_edges, black)                                                 # -1 entries count as kept (:424)
+            order = np.argsort(~ok, axis=1, kind="stable")                                    # kept entries first, order kept
+            n_ok = ok.sum(axis=1, keepdims=True)
+            front = np.arange(graph_edges.shape[1])[None, :] < n_ok
+            ids = np.take_along_axis(graph_edges, order, axis=1)
+            graph_edges = np.where(front, np.where(ids == -1, -1, new_id[np.maximum(ids, 0)]), -1).astype(np.int32)
+            graph_edges_weights = np.where(front, np.take_along_axis(graph_edges_weights, order, axis=1), 0).astype(np.float32)
+            graph_edges_distances = np.where(front, np.take_along_axis(graph_edges_distances, order, axis=1), 0).astype(np.float32)
+            sum_weights = np.sum(graph_edges_weights, axis=1, keepdims=True)
+            graph_edges_weights = np.where(sum_weights > 0, graph_edges_weights / (sum_weights + 1e-6),
+                                           graph_edges_weights).astype(np.float32)             # :452-454
         return {
             "all_nodes_at_source": self.nodes.copy(), "valid_nodes_at_source": node_coords, "graph_edges": graph_edges,
             "graph_edges_weights": graph_edges_weights, "graph_edges_distances": graph_edges_distances,
@@ -162,18 +156,7 @@ class EDGraph:
         V = self.vertices.shape[0]
         for level in range(1, 4):
             node_coverage = node_coverage * 2
-            down_sample_idx, up_sample_idx = [], []
-            for i in range(old_nodes.shape[0]):
-                if not down_sample_idx:
-                    up_sample_idx.append(i)
-                    down_sample_idx.append(i)
-                    continue
-                nodes_dist = np.linalg.norm(old_nodes[down_sample_idx] - old_nodes[i], axis=1)
-                nearest = np.argmin(nodes_dist)
-                up_sample_idx.append(nearest)
-                if nodes_dist[nearest] < node_coverage:
-                    continue
-                down_sample_idx.append(i)
+            down_sample_idx, up_sample_idx = downsample_nodes(old_nodes, node_coverage)      # :279-298, native host loop
             E = num_neighbours_list[level]
             level_node_indices = level_node_indices[down_sample_idx]
             n = level_node_indices.shape[0]

@@ -63,6 +63,16 @@ def compute_clusters_c(graph_edges, graph_clusters):
     return sizes[:n.value].tolist()
 
 
+def downsample_nodes(nodes, node_coverage):
+    """One pyramid level (embedded_deformation_graph.py:279-298): (down_sample_idx, up_sample_idx) as Python lists."""
+    nd = np.ascontiguousarray(nodes, dtype=np.float32).reshape(-1, 3)
+    M = len(nd)
+    down, up = np.zeros(max(M, 1), np.int32), np.zeros(max(M, 1), np.int32)
+    n = C.c_int32(0)
+    _capi.check(_capi.load().ofx_downsample_nodes_host(_p(nd), M, float(node_coverage), _p(down), C.byref(n), _p(up)))
+    return down[:n.value].tolist(), up[:M].tolist()
+
+
 def compute_pixel_anchors_euclidean_c(graph_nodes, point_image, node_coverage, pixel_anchors, pixel_weights):
     """graph_proc.cpp:610-709 (binding csrc/main.cpp:35) on the device (ofx_pixel_anchors_euclidean): point_image (3,H,W) f32;
     pixel_anchors (i32) / pixel_weights (f32) are resized in place to (H,W,4), as the reference's callee does, and filled."""
