@@ -107,3 +107,61 @@ def test_reduced_graph_clusters_and_pyramid_match_reference(gg):
     assert sorted(pyd) == sorted(keys) and len(keys) == 10
     for k in keys:
         assert np.array_equal(np.asarray(pyd[k]), gg["pyd_" + k]), k
+
+
+def _ref_graph():
+    """The reference's own C++ (oracle/_ref/ref_graph.so, built by oracle/build_ref.sh where /root/reference exists)."""
+    import os
+    import sys
+    here = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref")
+    if not os.path.exists(os.path.join(here, "ref_graph.so")):
+        pytest.skip("oracle/_ref/ref_graph.so not built (needs /root/reference)")
+    import torch  # noqa: F401
+    sys.path.insert(0, here)
+    try:
+        import ref_graph
+    except Exception as e:      # noqa: BLE001
+        pytest.skip(f"ref_graph not loadable: {e}")
+    return ref_graph
+
+
+@pytest.mark.parametrize("jitter", [0.0, 1e-3])
+def test_geodesic_edges_against_the_compiled_reference_with_ties(oracle, jitter):
+    """A regular, un-jittered grid mesh makes equal path lengths the rule, so the order in which equal distances leave the heap
+    decides edges and visited sets: the host builder must agree with the reference's compiled C++ there too (and on the
+    jittered mesh), at a size the goldens do not carry (14 400 vertices, ~330 nodes)."""
+    from occlusionfusion_b200.graph_proc import compute_clusters_c, compute_edges_geodesic_c, node_and_edge_clean_up_c
+    ref = _ref_graph()
+    n = 120
+    rng = np.random.default_rng(4)
+    u, v = np.meshgrid(np.linspace(-0.6, 0.6, n), np.linspace(-0.6, 0.6, n), indexing="ij")
+    verts = (np.stack([u, v, np.ones_like(u)], -1).reshape(-1, 3) + rng.uniform(-jitter, jitter, (n * n, 3))).astype(np.float32)
+    ij = np.argwhere(rng.random((n - 1, n - 1)) > 0.03)
+    a = ij[:, 0] * n + ij[:, 1]
+    faces = np.concatenate([np.stack([a, a + 1, a + n], 1), np.stack([a + 1, a + n + 1, a + n], 1)]).astype(np.int32)
+    V = len(verts)
+    ne = oracle.erode_mesh(V, faces, 1, 3)
+    _, nidx = oracle.sample_nodes(verts, ne, 0.05, True)
+    nidx = nidx.reshape(-1, 1)
+    M = len(nidx)
+    for E, cov, only_valid, enforce, valid in ((8, 0.05, True, True, ne), (4, 0.1, False, True, np.ones(V, bool)),
+                                               (8, 0.05, True, False, ne)):
+        out = []
+        for impl in ("ours", "ref"):
+            e, w, d = -np.ones((M, E), np.int32), np.zeros((M, E), np.float32), np.zeros((M, E), np.float32)
+            n2v = -np.ones((M, V), np.float32)
+            if impl == "ours":
+                compute_edges_geodesic_c(verts, valid, faces, nidx, E, cov, e, w, d, n2v, only_valid, enforce)
+            else:
+                ref.compute_edges_geodesic(verts, valid.reshape(-1, 1), faces, nidx, E, cov, e, w, d, n2v, only_valid, enforce)
+            out.append((e, w, d, n2v))
+        for x, y in zip(*out):
+            assert np.array_equal(x, y)
+        e = out[0][0]
+        m1, m2 = np.ones((M, 1), bool), np.ones((M, 1), bool)
+        node_and_edge_clean_up_c(e, m1)
+        ref.node_and_edge_clean_up(e, m2)
+        assert np.array_equal(m1, m2)
+        c1, c2 = -np.ones((M, 1), np.int32), -np.ones((M, 1), np.int32)
+        assert compute_clusters_c(e, c1) == list(ref.compute_clusters(e, c2)) and np.array_equal(c1, c2)
+    assert M > 250
