@@ -14,6 +14,13 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
 
 
+@pytest.fixture(scope="session", autouse=True)
+def _libofx_built():
+    """The C-ABI library is built in-tree before any test needs it (a no-op when it is up to date)."""
+    from occlusionfusion_b200 import build
+    build.build()
+
+
 @pytest.fixture(scope="session")
 def oracle():
     import oracle as O
