@@ -247,14 +247,13 @@ def bench_workload(name, args, rank, world, device, with_e2e=True):
     gath = torch.empty(world * 4, dtype=torch.int64, device=device)
 
     def core(kev0=None, kev1=None):
-        """the per-frame device work: [broadcast] -> node transforms -> fused kernel -> [counter all-gather]"""
+        """the per-frame device work: [broadcast] -> frame preparation (+ node transforms) -> brick cull -> fused kernel -> [counter all-gather]"""
         if world > 1:
             dist.broadcast(sf.buf, src=0)
         v = sf.views
-        sf.be.set_transforms(v["R"], v["T"])
         if kev0 is not None:
             kev0.record(torch.cuda.current_stream(device))
-        st = sf.be.integrate(v["depth"], v["colour"], False, 1.0)
+        st = sf.be.integrate_warped(v["R"], v["T"], v["depth"], v["colour"], 1.0)
         if kev1 is not None:
             kev1.record(torch.cuda.current_stream(device))
         if world > 1:

@@ -98,6 +98,14 @@ int ofx_integrate(ofx_volume *v, const float *depth, const float *colour_packed,
                   int32_t W, const float *intr_host, double obs_weight, int32_t identity_warp,
                   uint64_t *stats, void *stream);
 
+/* ofx_set_transforms + ofx_integrate(identity_warp = 0) as ONE call: WarpField.update_transformations followed by
+ * TSDFVolume.integrate of the registered frame (fusion_with_occlusion/fusion.py:176-179).  The node transforms are
+ * written by the frame-preparation launch, so a warped frame costs three kernel launches instead of four; results
+ * are identical to the two separate calls. */
+int ofx_integrate_warped(ofx_volume *v, const float *rotations, const float *translations,
+                         const float *depth, const float *colour_packed, int32_t H, int32_t W,
+                         const float *intr_host, double obs_weight, uint64_t *stats, void *stream);
+
 /* Optional look-ahead for frame streams (new in this library; the reference integrates strictly frame by frame):
  * stages the NEXT warped frame's node transforms (as ofx_set_transforms) and its list of bricks inside the
  * camera frustum in a second per-frame set, so that it may run on another stream while the current frame

@@ -14,6 +14,7 @@ enum Mode { MODE_WARPED = 0, MODE_IDENTITY = 1, MODE_DEFORM = 2 };
 struct FrameArgs {
     const float *depth;
     const float *colour_im;
+    const float2 *dc;            // the same frame interleaved {depth, packed colour} (frame_prep_kernel); persistent kernel only
     Camera cam;
     FastCam fc;                  // the same intrinsics + the error terms of the certified float32 pixel
     double trunc;

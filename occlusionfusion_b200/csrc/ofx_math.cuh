@@ -236,6 +236,23 @@ __device__ __forceinline__ int project_fast(float qx, float qy, float qz, const 
     return dead ? 0 : ((ok_u && ok_v) ? 1 : 2);
 }
 
+// The same decision as two flags: in_certain = the pixel (u, v) is certain and inside the image; undecided = the
+// caller must evaluate project() (a superset of project_fast()'s state 2: a coordinate that is certainly outside
+// no longer short-cuts the other one -- a handful of predicate instructions less on the hot path, and project()
+// gives the exact answer for every voxel sent to it).
+__device__ __forceinline__ void project_fast2(float qx, float qy, float qz, const FastCam &fc, int &u, int &v, bool &in_certain,
+                                              bool &undecided)
+{
+    float rz;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rz) : "f"(qz));
+    bool in_u, in_v;
+    const bool ok_u = fast_pixel(qx, fc.fx, fc.cx, fc.eps0x, rz, fc.W, u, in_u);
+    const bool ok_v = fast_pixel(qy, fc.fy, fc.cy, fc.eps0y, rz, fc.H, v, in_v);
+    const bool pos = qz > 0.0f, ok = ok_u && ok_v;
+    in_certain = pos && ok && in_u && in_v;
+    undecided = pos && !ok;
+}
+
 // depth - z >= -trunc in float64 (tsdf.py:608-609), for the rare float32 ties
 __device__ __forceinline__ bool visible_exact(float d, float z, double trunc)
 {

@@ -12,16 +12,14 @@
 
 namespace ofx {
 
-static int g_sm_count = 0;
+// SM count of the CURRENT device (asked every time: the runtime caches device attributes, and a process may
+// hold handles on several devices)
 int sm_count()
 {
-    if (g_sm_count == 0) {
-        int dev = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess) return 148;
-        cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
-        if (g_sm_count <= 0) g_sm_count = 148;
-    }
-    return g_sm_count;
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) return 148;
+    return n;
 }
 
 static inline int grid_for(int64_t n, int block, int ctas_per_sm)

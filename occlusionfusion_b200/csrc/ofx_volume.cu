@@ -93,24 +93,27 @@ extern "C" int ofx_volume_create(ofx_volume **out, const ofx_volume_desc *d)
     std::memset(v, 0, sizeof(*v));
     v->desc = *d;
     OFX_CUDA(cudaGetDevice(&v->device));
+    v->sm_count = sm_count();
     const int nx = d->dims[0] / d->n_shards, Dy = d->dims[1], Dz = d->dims[2];
     v->n_voxels = (int64_t)nx * Dy * Dz;
 
     // vox2world tables: float32(float64(origin) + voxel_size * float64(float32(index)))  tsdf.py:345-348
-    std::vector<float> tab((size_t)nx + Dy + Dz);
+    // (each table starts on a 16-byte boundary: the fused kernel reads four z coordinates as one float4)
+    const size_t off_y = ((size_t)nx + 3) & ~(size_t)3, off_z = (off_y + Dy + 3) & ~(size_t)3;
+    std::vector<float> tab(off_z + Dz + 4, 0.0f);
     for (int lx = 0; lx < nx; ++lx) {
         const int gx = (lx / d->x_block) * d->x_block * d->n_shards + d->shard * d->x_block + lx % d->x_block;
         tab[lx] = (float)((double)d->origin[0] + d->voxel_size * (double)(float)gx);
     }
-    for (int iy = 0; iy < Dy; ++iy) tab[nx + iy] = (float)((double)d->origin[1] + d->voxel_size * (double)(float)iy);
-    for (int iz = 0; iz < Dz; ++iz) tab[nx + Dy + iz] = (float)((double)d->origin[2] + d->voxel_size * (double)(float)iz);
+    for (int iy = 0; iy < Dy; ++iy) tab[off_y + iy] = (float)((double)d->origin[1] + d->voxel_size * (double)(float)iy);
+    for (int iz = 0; iz < Dz; ++iz) tab[off_z + iz] = (float)((double)d->origin[2] + d->voxel_size * (double)(float)iz);
     OFX_CUDA(cudaMalloc(&v->tables, tab.size() * sizeof(float)));
     OFX_CUDA(cudaMemcpy(v->tables, tab.data(), tab.size() * sizeof(float), cudaMemcpyHostToDevice));
 
     VolumeGeom &g = v->geom;
     g.nx = nx; g.Dy = Dy; g.Dz = Dz;
     g.nbx = (nx + BX - 1) / BX; g.nby = (Dy + BY - 1) / BY; g.nbz = (Dz + BZ - 1) / BZ;
-    g.px = v->tables; g.py = v->tables + nx; g.pz = v->tables + nx + Dy;
+    g.px = v->tables; g.py = v->tables + off_y; g.pz = v->tables + off_z;
     const int64_t nb = (int64_t)g.nbx * g.nby * g.nbz;
     OFX_REQUIRE(nb < (1ll << 31), "ofx_volume_create: too many bricks");
     v->n_bricks = (int)nb;
@@ -138,7 +141,7 @@ extern "C" int ofx_volume_destroy(ofx_volume *v)
     cudaFree(v->tables); cudaFree(v->node_rec_set[0]); cudaFree(v->cache); cudaFree(v->brick_slot); cudaFree(v->brick_cnt);
     cudaFree(v->brick_off); cudaFree(v->brick_radius); cudaFree(v->cand); cudaFree(v->brick_nodes);
     cudaFree(v->active); cudaFree(v->scratch); cudaFree(v->stats_scratch);
-    cudaFree(v->live_set[0]); cudaFree(v->live_set[1]); cudaFree(v->stats_acc); cudaFree(v->active_desc); cudaFree(v->brick_box); cudaFree(v->depth_tiles);
+    cudaFree(v->live_set[0]); cudaFree(v->live_set[1]); cudaFree(v->stats_acc); cudaFree(v->active_desc); cudaFree(v->brick_box); cudaFree(v->depth_tiles); cudaFree(v->frame_dc);
     delete v;
     return 0;
 }

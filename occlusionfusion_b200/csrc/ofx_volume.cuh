@@ -88,8 +88,10 @@ struct ofx_volume {
     int prepared_hw[2];
     bool prepared;               // the other set holds the next frame's transforms + live list (ofx_prepare_frame)
     unsigned long long *stats_acc;   // 2 x OFX_N_STATS: per-set accumulators of the persistent kernel
-    float *depth_tiles;          // per frame: max depth of each DEPTH_TILE x DEPTH_TILE pixel tile
-    int depth_tiles_capacity;
+    float2 *frame_dc;            // per frame: the frame interleaved {depth, packed colour} (frame_prep_kernel)
+    float *depth_tiles;          // per frame: max valid depth of each DEPTH_TILE x DEPTH_TILE pixel tile (0 = none)
+    int64_t frame_capacity;      // pixels allocated for frame_dc / depth_tiles
+    int sm_count;                // of the handle's device
     int *scratch;                // small device scratch: [0]=total [1]=max [2]=error [8 + 4*set ..]: n_live, work counter, retired CTAs (all zero between launches)
     uint64_t *stats_scratch;     // OFX_N_STATS counters when the caller passes NULL
     bool graph_ready, transforms_ready;

@@ -122,9 +122,7 @@ class ShardedFusion:
         if self.world > 1:
             dist.broadcast(self.buf, src=0, group=self.group)
         v = self.views
-        if not identity_warp:
-            self.be.set_transforms(v["R"], v["T"])
-        stats = self.be.integrate(v["depth"], v["colour"], identity_warp, obs_weight)
+        stats = self._integrate(v, identity_warp, obs_weight)
         if not gather_stats:
             return stats
         if self.world == 1:
@@ -132,6 +130,18 @@ class ShardedFusion:
         out = torch.empty(self.world * N_STATS, dtype=torch.int64, device=self.device)
         dist.all_gather_into_tensor(out, stats.contiguous().view(-1), group=self.group)
         return out.view(self.world, N_STATS)
+
+    def _integrate(self, v, identity_warp, obs_weight, stats=None):
+        """node transforms + integrate of the packet views `v`: one library call where the backend has it
+        (ofx_integrate_warped: the transforms ride in the frame-preparation launch)."""
+        kw = {} if stats is None else {"stats": stats}
+        if identity_warp:
+            return self.be.integrate(v["depth"], v["colour"], True, obs_weight, **kw)
+        fused = getattr(self.be, "integrate_warped", None)
+        if fused is not None:
+            return fused(v["R"], v["T"], v["depth"], v["colour"], obs_weight, **kw)
+        self.be.set_transforms(v["R"], v["T"])
+        return self.be.integrate(v["depth"], v["colour"], False, obs_weight, **kw)
 
     # -- per frame, pipelined ----------------------------------------------------------------------
     # Two packets, two streams (SURVEY.md 8e "scaling risk"): while the shard integrates frame t the
@@ -243,9 +253,10 @@ class ShardedFusion:
         comp = torch.cuda.current_stream(self.device)
         comp.wait_event(self._ev_bcast[j])
         v = self._pviews[j]
-        if not self._lookahead:
-            self.be.set_transforms(v["R"], v["T"])
-        self.be.integrate(v["depth"], v["colour"], False, obs_weight, stats=self._pstats[j])
+        if self._lookahead:
+            self.be.integrate(v["depth"], v["colour"], False, obs_weight, stats=self._pstats[j])
+        else:
+            self._integrate(v, False, obs_weight, stats=self._pstats[j])
         self._ev_done[j].record(comp)
         # issued after integrate(t): the look-ahead stages frame t+1 in the frame set integrate(t) is not using
         out = self._exchange(t + 1, next_packet, prev=t - 1 if t > 0 else None, publish=not last)
@@ -320,6 +331,15 @@ class CudaShard:
         st = self.stats if stats is None else stats
         c.check(self.lib.ofx_integrate(self.vol._h, c.ptr(depth), c.ptr(colour), H, W, self.vol._intr4, float(obs_weight),
                                        int(identity_warp), c.ptr(st), self._s()))
+        return st
+
+    def integrate_warped(self, R, T, depth, colour, obs_weight, stats=None):
+        """set_transforms + integrate of a warped frame as one library call (ofx_integrate_warped)."""
+        c = self._capi
+        H, W = depth.shape
+        st = self.stats if stats is None else stats
+        c.check(self.lib.ofx_integrate_warped(self.vol._h, c.ptr(R), c.ptr(T), c.ptr(depth), c.ptr(colour), H, W, self.vol._intr4,
+                                              float(obs_weight), c.ptr(st), self._s()))
         return st
 
     def get_volume(self):

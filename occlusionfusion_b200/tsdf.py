@@ -203,15 +203,24 @@ class TSDFVolume:
         with torch.cuda.device(self.device):
             self.update(image_data["im"], image_data["id"])
             identity = self.frame_id == self.fopt.source_frame
+            H, W = self._depth_im_dev.shape
+            S = _capi.stream_ptr(self.device)
             if not identity:
                 wf = self.warpfield
                 assert wf.frame_id == self.frame_id, \
                     f"Warpfield maps to:{wf.frame_id}th frame but TSDF maps to:{self.frame_id}th frame"  # warpfield.py:374
-                wf._sync_device()
-            H, W = self._depth_im_dev.shape
+                wf._sync_graph()
+                if wf._transforms_dirty:
+                    # new node transforms ride in the frame-preparation launch (ofx_integrate_warped)
+                    R_dev, T_dev = wf._stage_transforms()
+                    _capi.check(self._lib.ofx_integrate_warped(self._h, _capi.ptr(R_dev), _capi.ptr(T_dev),
+                                                               _capi.ptr(self._depth_im_dev), _capi.ptr(self._color_im_dev),
+                                                               H, W, self._intr4, float(obs_weight), _capi.ptr(self._stats), S))
+                    wf._transforms_dirty = False
+                    return
             _capi.check(self._lib.ofx_integrate(self._h, _capi.ptr(self._depth_im_dev), _capi.ptr(self._color_im_dev),
                                                 H, W, self._intr4, float(obs_weight), int(identity),
-                                                _capi.ptr(self._stats), _capi.stream_ptr(self.device)))
+                                                _capi.ptr(self._stats), S))
 
     def last_stats(self):
         """Counters of the last integrate(): dict(updated, skin_valid, bricks, weight_sum). Synchronises."""

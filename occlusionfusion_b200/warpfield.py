@@ -61,42 +61,59 @@ class WarpField:
         return self.tsdf.device
 
     # ------------------------------------------------------------------ device sync
-    def _sync_device(self):
-        """Upload graph / transforms if they changed since the last integrate."""
+    def _sync_graph(self):
+        """Upload the node table and rebuild the anchor cache if the graph changed since the last upload."""
         nodes = self.graph.nodes
         key = (id(nodes), nodes.shape[0], int(self.graph_neighbours), float(self.node_coverage))
-        with torch.cuda.device(self.device):
-            if key != self._graph_key or self.updating_warpfield:
+        if key != self._graph_key or self.updating_warpfield:
+            with torch.cuda.device(self.device):
                 nd = _capi.to_device(nodes, torch.float32, self.device)
                 _capi.check(self._lib.ofx_set_graph(self.tsdf._h, _capi.ptr(nd), nodes.shape[0], float(self.node_coverage),
                                                     int(self.graph_neighbours), _capi.stream_ptr(self.device)))
-                self._graph_key = key
-                self._transforms_dirty = True
-                for a in ("world_anchors", "world_weights", "world_valid_pts"):
-                    if hasattr(self, a):
-                        delattr(self, a)
-            if self._transforms_dirty:
-                M = nodes.shape[0]
-                R = np.asarray(self.rotations)
-                T = np.asarray(self.translations)
-                assert R.shape[0] == M == T.shape[0], \
-                    f"Nodes mismatch between transformation data:{self.rotations.shape} and graph nodes:{nodes.shape}"
-                # one pinned staging buffer [R (9M) | T (3M)], one asynchronous upload
-                if self._RT_host is None or self._RT_host.numel() != 12 * M:
-                    self._RT_host = torch.empty(12 * M, dtype=torch.float32, pin_memory=True)
-                    self._RT_dev = torch.empty(12 * M, dtype=torch.float32, device=self.device)
-                    self._RT_done = torch.cuda.Event()
-                else:
-                    self._RT_done.synchronize()      # the previous upload has left the staging buffer
-                h = self._RT_host.numpy()
-                h[:9 * M] = R.reshape(-1)            # casts to float32 like the reference's device upload
-                h[9 * M:] = T.reshape(-1)
-                self._RT_dev.copy_(self._RT_host, non_blocking=True)
-                self._RT_done.record(torch.cuda.current_stream(self.device))
-                self._R_dev, self._T_dev = self._RT_dev[:9 * M], self._RT_dev[9 * M:]
-                _capi.check(self._lib.ofx_set_transforms(self.tsdf._h, _capi.ptr(self._R_dev), _capi.ptr(self._T_dev),
+            self._graph_key = key
+            self._transforms_dirty = True
+            for a in ("world_anchors", "world_weights", "world_valid_pts"):
+                if hasattr(self, a):
+                    delattr(self, a)
+
+    def _stage_transforms(self):
+        """Host R, T -> device [R (9M) | T (3M)] through one pinned staging buffer and one asynchronous upload on the
+        current stream.  Returns the two device views; the caller hands them to the library."""
+        nodes = self.graph.nodes
+        M = nodes.shape[0]
+        R = np.asarray(self.rotations)
+        T = np.asarray(self.translations)
+        assert R.shape[0] == M == T.shape[0], \
+            f"Nodes mismatch between transformation data:{self.rotations.shape} and graph nodes:{nodes.shape}"
+        with torch.cuda.device(self.device):
+            if self._RT_host is None or self._RT_host.shape[1] != 12 * M:
+                # two staging buffers used in turn: the upload of frame t+1 may be staged while frame t's is in flight
+                self._RT_host = torch.empty((2, 12 * M), dtype=torch.float32, pin_memory=True)
+                self._RT_dev = torch.empty((2, 12 * M), dtype=torch.float32, device=self.device)
+                self._RT_done = [torch.cuda.Event(), torch.cuda.Event()]
+                self._RT_used = [False, False]
+                self._RT_i = 0
+            i = self._RT_i = 1 - self._RT_i
+            if self._RT_used[i]:
+                self._RT_done[i].synchronize()   # the upload before last has left this staging buffer
+            h = self._RT_host[i].numpy()
+            h[:9 * M] = R.reshape(-1)            # casts to float32 like the reference's device upload
+            h[9 * M:] = T.reshape(-1)
+            self._RT_dev[i].copy_(self._RT_host[i], non_blocking=True)
+            self._RT_done[i].record(torch.cuda.current_stream(self.device))
+            self._RT_used[i] = True
+        self._R_dev, self._T_dev = self._RT_dev[i, :9 * M], self._RT_dev[i, 9 * M:]
+        return self._R_dev, self._T_dev
+
+    def _sync_device(self):
+        """Upload graph / transforms if they changed since the last integrate."""
+        self._sync_graph()
+        if self._transforms_dirty:
+            R_dev, T_dev = self._stage_transforms()
+            with torch.cuda.device(self.device):
+                _capi.check(self._lib.ofx_set_transforms(self.tsdf._h, _capi.ptr(R_dev), _capi.ptr(T_dev),
                                                          _capi.stream_ptr(self.device)))
-                self._transforms_dirty = False
+            self._transforms_dirty = False
 
     # ------------------------------------------------------------------ skinning
     def skin(self, points, nodes=None, ensure_num_neigbours=False):

@@ -40,6 +40,15 @@ def test_library_is_sm100a_with_tma():
     sass = subprocess.run(["cuobjdump", "-sass", lib_path], capture_output=True, text=True).stdout
     assert "UBLKCP" in sass, "the brick kernels should stage node records with TMA bulk copies"
     assert "SYNCS" in sass, "mbarrier pipeline missing"
+    # the running averages of the persistent kernel work on voxel pairs with the packed float32 instructions of sm_100
+    persistent = sass[sass.index("fused_warped_persistentILi4ELb1"):]
+    persistent = persistent[:persistent.index("Function :", 10)] if "Function :" in persistent[10:] else persistent
+    for op in ("FFMA2", "FADD2", "FMUL2"):
+        assert op in persistent, f"{op} missing from fused_warped_persistent<4, true>"
+    # ptxas contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 even under --fmad=false; the colour blend
+    # w*old + obs*new must keep the rounding of its products (ofx_fused.cuh: mul2_pos = FFMA2 with a zero addend)
+    assert re.search(r"FFMA2 R\d+, R\d+\.F32x2\.HI_LO, R\d+\.F32x2\.HI_LO, RZ", persistent), \
+        "the unfused product (FFMA2 ..., RZ) of the colour blend is gone: check for a contracted mul+add"
 
 
 def test_product_does_not_touch_oracle():

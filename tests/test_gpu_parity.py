@@ -175,6 +175,34 @@ def test_obs_weight_not_float32(oracle):
         assert st["updated"] == n
 
 
+def test_mixed_float32_obs_weights_on_the_packed_path(oracle):
+    """Observation weights that are float32 values but not integers (0.625, 1.75) followed by 1.0: the voxel weights
+    become non-integers, so w*old is inexact and the colour blend's two roundings (product, then sum) differ from a
+    fused multiply-add -- pins the unfused packed product of fuse_pair (ptxas would contract mul.rn.f32x2 +
+    add.rn.f32x2).  0.3 in the middle takes the generic kernel (not a float32 value)."""
+    from occlusionfusion_b200 import WarpField
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload("c1-dense", dim=[48, 40, 64], voxel=0.02, n_nodes=64, H=120, W=160)
+    vol = _mk_volume(w)
+    ov = oracle.OracleVolume(w.dims, w.origin, w.voxel_size, w.intr, w.trunc)
+    ov.set_graph(w.nodes, w.coverage, w.K)
+    wf = WarpField(w.graph(), vol, None)
+    wf.graph_neighbours = w.K
+    vol.warpfield = wf
+    for f, obs in enumerate([1.0, 0.625, 1.75, 0.3, 1.0, 1.0, 0.625]):
+        im = w.frame(f)
+        if f > 0:
+            est = w.estimate(f)
+            wf.update_transformations(est)
+            ov.set_transforms(est["node_rotations"], wf.translations)
+        vol.integrate({"im": im, "id": f}, obs)
+        n = ov.integrate(im, f == 0, obs)
+        assert vol.last_stats()["updated"] == n
+        _assert_bit_equal(vol, ov)
+    t, c, wt = vol.get_volume()
+    assert (wt != np.round(wt)).any() and (t < 1.0).any()
+
+
 def test_medium_dense_certified_paths(oracle):
     """393 k voxels, all skin-valid, three warped frames: large enough that the certified float32 pixel
     (about 1e-4 of the voxels are undecided and take the float64 original), the float32 visibility test
