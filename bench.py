@@ -39,6 +39,7 @@ def parse():
     ap.add_argument("--also", default="c2,c1", help="extra workloads reported under 'also' (N=1 only); '' = none")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of a CUDA graph replay")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end leg (investigation runs)")
     ap.add_argument("--no-pipeline", action="store_true", help="N > 1: broadcast -> kernel -> all-gather strictly in sequence")
     ap.add_argument("--cpu-planes", type=int, default=0, help="x-planes in the CPU sample (0 = auto)")
     ap.add_argument("--graph-ops", action="store_true",
@@ -391,7 +392,7 @@ def bench_workload(name, args, rank, world, device, with_e2e=True):
     res["kernel_ms_local"] = kern_ms_local(evs, K)
 
     # ---- e2e: public API, host buffers, H2D + D2H inside the timed region ------------------------
-    if with_e2e:
+    if with_e2e and not args.no_e2e:
         res["e2e"] = bench_e2e(w, vol, wf, sf, frames, ests, args, rank, world, device)
     del vol, wf, sf, packets, flush
     torch.cuda.empty_cache()
@@ -656,6 +657,7 @@ def main():
             dist.destroy_process_group()
         return
     main_res = bench_workload(args.workload, args, rank, world, device)
+    main_res.setdefault("e2e", None)
     also = {}
     if world == 1 and args.also:
         for name in [n for n in args.also.split(",") if n and n != args.workload]:

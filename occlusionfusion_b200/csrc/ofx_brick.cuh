@@ -89,8 +89,10 @@ __device__ __forceinline__ void warp_voxel(const uint32_t (&ids)[2], const float
 // the per-voxel work becomes q_k = fma(R_2, p_z, B): the same operations in the same order (bit-identical),
 // half the FMAs and half the shared-memory bytes per anchor (24 instead of 48) -- shared-memory wavefronts
 // are what bounds the kernel (profiles/: l1tex data pipe at 90 %).
-//   tab   float4 [4 rows][ROW_TAB_CAP]   {B_x, B_y, B_z, R_02}
-//   col   float2 [ROW_TAB_CAP]           {R_12, R_22}
+//   tab   float4 [4 rows][ROW_TAB_CAP]   {B_x, B_y, B_z, R_22}
+//   col   float2 [ROW_TAB_CAP]           {R_02, R_12}
+// ({B_x, B_y} and {R_02, R_12} sit in aligned register pairs after the loads: the x and y components of
+// fma(R_2, p_z, B) are ONE packed fma.rn.f32x2, FFMA2 in SASS.)
 // Bricks with more than ROW_TAB_CAP nodes take the record path (warp_voxel).
 constexpr int ROW_TAB_CAP = 32;
 constexpr int ROW_TAB_BYTES = 4 * ROW_TAB_CAP * 16 + ROW_TAB_CAP * 8;      // per warp
@@ -108,10 +110,10 @@ __device__ __forceinline__ void build_row_table(uint32_t rec_base, int n_used, f
         const float by = __fmaf_rn(a[4], py, __fmaf_rn(a[3], px, a[10]));
         const float bz = __fmaf_rn(a[7], py, __fmaf_rn(a[6], px, a[11]));
         const uint32_t ent = tab_base + (uint32_t)(r * ROW_TAB_CAP + n) * 16u;
-        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(ent), "f"(bx), "f"(by), "f"(bz), "f"(a[2]) : "memory");
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(ent), "f"(bx), "f"(by), "f"(bz), "f"(a[8]) : "memory");
         if (r == 0)
-            asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(tab_base + 4u * ROW_TAB_CAP * 16u + (uint32_t)n * 8u), "f"(a[5]),
-                         "f"(a[8])
+            asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(tab_base + 4u * ROW_TAB_CAP * 16u + (uint32_t)n * 8u), "f"(a[2]),
+                         "f"(a[5])
                          : "memory");
     }
     __syncwarp();
@@ -122,18 +124,21 @@ template <int K, int KP>
 __device__ __forceinline__ void warp_voxel_tab(const uint32_t (&ids)[2], const float (&w)[KP], uint32_t row_base,
                                                uint32_t col_base, float pz, float &qx, float &qy, float &qz)
 {
-    float ax = 0.f, ay = 0.f, az = 0.f;
+    // (a scalar operand of a packed instruction is broadcast to both lanes for free: FFMA2 ..., R.F32, ...)
+    float2 axy = make_float2(0.f, 0.f);
+    float az = 0.f;
+    const float2 pz2 = make_float2(pz, pz);
 #pragma unroll
     for (int k = 0; k < K; ++k) {
         const uint32_t id = __byte_perm(ids[k >> 2], 0u, 0x4440u + (k & 3));
-        float bx, by, bz, r02, r12, r22;
-        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(bx), "=f"(by), "=f"(bz), "=f"(r02) : "r"(id * 16u + row_base));
-        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(r12), "=f"(r22) : "r"(id * 8u + col_base));
-        ax = __fmaf_rn(w[k], __fmaf_rn(r02, pz, bx), ax);
-        ay = __fmaf_rn(w[k], __fmaf_rn(r12, pz, by), ay);
+        float bx, by, bz, r22, r02, r12;
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(bx), "=f"(by), "=f"(bz), "=f"(r22) : "r"(id * 16u + row_base));
+        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(r02), "=f"(r12) : "r"(id * 8u + col_base));
+        const float2 txy = __ffma2_rn(make_float2(r02, r12), pz2, make_float2(bx, by));     // fma(R_02, p_z, B_x), fma(R_12, p_z, B_y)
+        axy = __ffma2_rn(make_float2(w[k], w[k]), txy, axy);
         az = __fmaf_rn(w[k], __fmaf_rn(r22, pz, bz), az);
     }
-    qx = ax; qy = ay; qz = az;
+    qx = axy.x; qy = axy.y; qz = az;
 }
 
 // ---- brick-level frustum culling -------------------------------------------------------------------

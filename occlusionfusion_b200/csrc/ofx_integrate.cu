@@ -160,26 +160,27 @@ frame_prep_kernel(const float *__restrict__ depth, const float *__restrict__ col
 //     > 0.996 (warpfield.py:114-121: every cached anchor lies inside 4 * coverage).
 // Survivors are appended to live[] (one atomic per CTA); the fused kernel then sees only bricks that do arithmetic,
 // so its dynamic scheduler balances equal-cost units.
-#ifndef OFX_CULL_LANES
-#define OFX_CULL_LANES 4
-#endif
 #ifndef OFX_CULL_THREADS
 #define OFX_CULL_THREADS 128
 #endif
 #ifndef OFX_DEPTH_CULL
 #define OFX_DEPTH_CULL 1
 #endif
-constexpr int CULL_LANES = OFX_CULL_LANES;
 constexpr int CULL_THREADS = OFX_CULL_THREADS;
-constexpr int CULL_BRICKS_PER_CTA = CULL_THREADS / CULL_LANES;
 constexpr int CULL_MAX_TILES = 256;      // larger pixel boxes (bricks next to the camera) skip the depth test
 
+// CULL_LANES lanes share a brick: its node list is a chain of dependent loads (list entry -> node record), so the
+// kernel's duration is (nodes per lane) x (memory latency) until the grid fills the machine.  Small active lists
+// (the band workloads: a few thousand bricks) take a whole warp per brick -- one round of loads --, large ones
+// four lanes per brick (profiles/: 16 us -> 6 us at 256^3, unchanged at 512^3 dense).
+template <int CULL_LANES>
 __global__ void __launch_bounds__(CULL_THREADS)
 brick_cull_kernel(GraphArgs ga, const int4 *__restrict__ active_desc, int n_active, Camera cam, const float *__restrict__ tiles,
                   int tw, float trunc, int *__restrict__ live, int *__restrict__ n_live, unsigned long long *__restrict__ acc)
 {
     __shared__ int s_mask[CULL_THREADS / 32];
     __shared__ int s_base;
+    constexpr int CULL_BRICKS_PER_CTA = CULL_THREADS / CULL_LANES;
     const int slot = threadIdx.x / CULL_LANES, sub = threadIdx.x % CULL_LANES;
     const int idx = blockIdx.x * CULL_BRICKS_PER_CTA + slot;
     grid_dep_launch();           // the fused kernel's CTAs may move in as this grid drains (they wait for it to finish)
@@ -364,10 +365,20 @@ static int launch_cull(ofx_volume *v, int set, const Camera &cam, const float *t
     v->counters_dirty[set] = true;
     GraphArgs ga = graph_args(v);
     ga.node_rec = v->node_rec_set[set];
-    PdlLaunch L(v, (v->n_active + CULL_BRICKS_PER_CTA - 1) / CULL_BRICKS_PER_CTA, CULL_THREADS, 0, s);
-    OFX_CUDA(cudaLaunchKernelEx(&L.cfg, brick_cull_kernel, ga, (const int4 *)v->active_desc, v->n_active, cam, tiles,
-                                (cam.W + DEPTH_TILE - 1) / DEPTH_TILE, (float)v->desc.trunc_margin, v->live_set[set], counters,
-                                v->stats_acc + set * OFX_N_STATS));
+    const int tw = (cam.W + DEPTH_TILE - 1) / DEPTH_TILE;
+    const float trunc = (float)v->desc.trunc_margin;
+    int *live = v->live_set[set];
+    unsigned long long *acc = v->stats_acc + set * OFX_N_STATS;
+    const int4 *desc = (const int4 *)v->active_desc;
+    // lanes per brick by the size of the active list (see brick_cull_kernel)
+    const int lanes = v->n_active <= 8192 ? 32 : (v->n_active <= 32768 ? 16 : (v->n_active <= 98304 ? 8 : 4));
+    PdlLaunch L(v, (int)(((int64_t)v->n_active * lanes + CULL_THREADS - 1) / CULL_THREADS), CULL_THREADS, 0, s);
+    switch (lanes) {
+    case 32: OFX_CUDA(cudaLaunchKernelEx(&L.cfg, brick_cull_kernel<32>, ga, desc, v->n_active, cam, tiles, tw, trunc, live, counters, acc)); break;
+    case 16: OFX_CUDA(cudaLaunchKernelEx(&L.cfg, brick_cull_kernel<16>, ga, desc, v->n_active, cam, tiles, tw, trunc, live, counters, acc)); break;
+    case 8: OFX_CUDA(cudaLaunchKernelEx(&L.cfg, brick_cull_kernel<8>, ga, desc, v->n_active, cam, tiles, tw, trunc, live, counters, acc)); break;
+    default: OFX_CUDA(cudaLaunchKernelEx(&L.cfg, brick_cull_kernel<4>, ga, desc, v->n_active, cam, tiles, tw, trunc, live, counters, acc)); break;
+    }
     return 0;
 }
 
@@ -502,6 +513,15 @@ extern "C" int ofx_integrate_warped(ofx_volume *v, const float *rotations, const
     if (!rc) v->transforms_ready = true;
     return rc;
 }
+
+#if OFX_TIMING
+extern "C" int ofx_debug_cta(unsigned long long *out_host)
+{
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out_host, ofx::g_cta, sizeof(unsigned long long) * 2048 * 8);
+    return 0;
+}
+#endif
 
 extern "C" int ofx_volume_deform(ofx_volume *v, float *out_pts, uint8_t *valid, void *stream)
 {

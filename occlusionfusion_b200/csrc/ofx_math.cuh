@@ -243,13 +243,23 @@ __device__ __forceinline__ int project_fast(float qx, float qy, float qz, const 
 __device__ __forceinline__ void project_fast2(float qx, float qy, float qz, const FastCam &fc, int &u, int &v, bool &in_certain,
                                               bool &undecided)
 {
+    // fast_pixel() on (u, v) as one pair of packed float32 lanes (FMUL2 / FADD2).  Whether ptxas contracts the second
+    // product with the following sum does not matter here: the certificate only needs the float32 value within eps of
+    // the float64 one, and a fused multiply-add is closer to it, not farther.
     float rz;
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rz) : "f"(qz));
-    bool in_u, in_v;
-    const bool ok_u = fast_pixel(qx, fc.fx, fc.cx, fc.eps0x, rz, fc.W, u, in_u);
-    const bool ok_v = fast_pixel(qy, fc.fy, fc.cy, fc.eps0y, rz, fc.H, v, in_v);
-    const bool pos = qz > 0.0f, ok = ok_u && ok_v;
-    in_certain = pos && ok && in_u && in_v;
+    const float2 m2 = __fmul2_rn(__fmul2_rn(make_float2(qx, qy), make_float2(fc.fx, fc.fy)), make_float2(rz, rz));
+    const float2 u2 = __fadd2_rn(m2, make_float2(fc.cx, fc.cy));
+    const float2 tm2 = __fadd2_rn(u2, make_float2(12582912.0f, 12582912.0f));     // 1.5 * 2^23: the sum rounds u half-to-even
+    const float2 n2 = __fadd2_rn(tm2, make_float2(-12582912.0f, -12582912.0f));   // rint(u) for |u| < 2^22
+    const float2 fr2 = __fadd2_rn(u2, make_float2(-n2.x, -n2.y));                 // exact
+    const float eps_u = __fmaf_rn(fabsf(m2.x), 3.2e-7f, fc.eps0x), eps_v = __fmaf_rn(fabsf(m2.y), 3.2e-7f, fc.eps0y);
+    u = __float_as_int(tm2.x) - 0x4B400000;
+    v = __float_as_int(tm2.y) - 0x4B400000;
+    const bool in = (unsigned)u < (unsigned)fc.W && (unsigned)v < (unsigned)fc.H;
+    const bool ok = fabsf(fr2.x) + eps_u < 0.5f && fabsf(fr2.y) + eps_v < 0.5f;      // false for NaN
+    const bool pos = qz > 0.0f;
+    in_certain = pos && ok && in;
     undecided = pos && !ok;
 }
 

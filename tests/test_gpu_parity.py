@@ -340,7 +340,11 @@ def test_pipelined_driver_equals_sequential(lookahead, oracle, monkeypatch):
         counters.append([g.cpu().numpy() for g in got])
     for a, b in zip(vols[0], vols[1]):
         assert np.array_equal(a, b)
-    assert np.array_equal(counters[0][-1], counters[1][-1]) and np.array_equal(counters[0][-2], counters[1][-2])
+    # (the look-ahead cull runs before the depth image exists, so it keeps the bricks behind the surface: more bricks
+    # and skin-valid voxels VISITED, the same voxels updated)
+    cols = [0, 3] if lookahead else [0, 1, 2, 3]
+    assert np.array_equal(counters[0][-1][:, cols], counters[1][-1][:, cols])
+    assert np.array_equal(counters[0][-2][:, cols], counters[1][-2][:, cols])
     ov = oracle.OracleVolume(w.dims, w.origin, w.voxel_size, w.intr, w.trunc)
     ov.set_graph(w.nodes, w.coverage, w.K)
     ov.integrate(w.frame(0), True)
@@ -558,8 +562,10 @@ def test_prepare_frame_lookahead_equals_set_transforms():
     for vols, stats in results[1:]:
         for a, b in zip(results[0][0], vols):
             assert np.array_equal(a, b)
+        # updated voxels and weight sums agree frame by frame; bricks / skin-valid voxels VISITED may be larger for a
+        # prepared frame (its cull ran before the depth image existed: frustum only, no depth-range test)
         for a, b in zip(results[0][1], stats):
-            assert np.array_equal(a, b)
+            assert a[0] == b[0] and a[3] == b[3] and b[1] >= a[1] and b[2] >= a[2]
     assert results[0][1][-1][0] > 1000
 
 

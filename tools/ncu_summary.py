@@ -10,7 +10,13 @@ nvox = float(sys.argv[2]) if len(sys.argv) > 2 else None
 
 
 def ncu(*args):
-    return subprocess.run(["ncu", "-i", rep, *args], capture_output=True, text=True).stdout
+    """ncu's CSV for the FIRST captured launch only (a report with several launches repeats the tables)."""
+    out = subprocess.run(["ncu", "-i", rep, *args], capture_output=True, text=True).stdout
+    if "--page" in args and args[args.index("--page") + 1] == "source":
+        parts = out.split('"Kernel Name"')
+        if len(parts) > 2:
+            out = '"Kernel Name"' + parts[1]
+    return out
 
 
 rows = list(csv.reader(io.StringIO(ncu("--page", "raw", "--csv"))))

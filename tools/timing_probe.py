@@ -1,32 +1,32 @@
-"""Investigation only: runs bench.py's c2-dense frames with the OFX_TIMING build and prints where the
-persistent kernel's warps wait.  tools/timing_probe.py (on the GPU box, after building libofx_timing.so)."""
-import ctypes, os, subprocess, sys, json
+"""Investigation only: runs one bench workload with the OFX_TIMING build (libofx_timing.so) and prints, per CTA of the LAST
+fused_warped_persistent launch, where the time goes: python tools/timing_probe.py [workload]
+(build first: python -m occlusionfusion_b200.build --out=occlusionfusion_b200/lib/libofx_timing.so -DOFX_TIMING=1 ...)."""
+import ctypes, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-lib = os.path.join(ROOT, "occlusionfusion_b200", "lib", "libofx_timing.so")
+lib = os.environ.get("OFX_LIB") or os.path.join(ROOT, "occlusionfusion_b200", "lib", "libofx_timing.so")
 os.environ["OFX_LIB"] = lib
+wl = sys.argv[1] if len(sys.argv) > 1 else "c1"
 sys.path.insert(0, ROOT)
-sys.argv = ["bench.py", "--steps", "10", "--warmup", "3", "--no-cpu-baseline", "--also", "", "--no-graph"]
+sys.argv = ["bench.py", "--workload", wl, "--steps", "6", "--warmup", "3", "--no-cpu-baseline", "--also", "", "--no-graph", "--no-e2e"]
 import bench
 bench.main()
+import numpy as np
 from occlusionfusion_b200 import _capi
 L = _capi.load()
-out = (ctypes.c_ulonglong * 8)()
-L.ofx_debug_timing(out, 0)
-v = list(out)
-print("producer: empty-wait ns total %d, count %d, avg %.0f ns" % (v[0], v[1], v[0] / max(v[1], 1)))
-print("consumer: data-wait ns total %d, count %d, avg %.0f ns" % (v[2], v[3], v[2] / max(v[3], 1)))
-print("consumer: brick work ns total %d, avg %.0f ns" % (v[4], v[4] / max(v[3], 1)))
-print("producer: TMA issue->landed ns total %d, count %d, avg %.0f ns" % (v[5], v[6], v[5] / max(v[6], 1)))
-
-import numpy as np
-buf = (ctypes.c_ulonglong * 4096)()
+buf = (ctypes.c_ulonglong * (2048 * 8))()
 L.ofx_debug_cta(buf)
-a = np.array(list(buf), dtype=np.int64).reshape(1024, 4)
+a = np.array(list(buf), dtype=np.int64).reshape(2048, 8)
 a = a[a[:, 0] > 0]
 t0 = a[:, 0].min()
-print("CTAs", len(a), "kernel span us", (a[:, 2].max() - t0) / 1e3)
-print("entry  us: min %.1f med %.1f max %.1f" % tuple(np.percentile((a[:, 0] - t0) / 1e3, [0, 50, 100])))
-print("first data us after entry: min %.1f med %.1f max %.1f" % tuple(np.percentile((a[:, 1] - a[:, 0]) / 1e3, [0, 50, 100])))
-print("end    us: min %.1f p10 %.1f med %.1f p90 %.1f max %.1f" % tuple(np.percentile((a[:, 2] - t0) / 1e3, [0, 10, 50, 90, 100])))
-print("bricks per CTA: min %d med %d max %d" % tuple(np.percentile(a[:, 3], [0, 50, 100])))
-print("us per brick per CTA: min %.2f med %.2f max %.2f" % tuple(np.percentile((a[:, 2] - a[:, 1]) / 1e3 / np.maximum(a[:, 3], 1), [0, 50, 100])))
+pc = lambda x: "min %.1f med %.1f p90 %.1f max %.1f" % tuple(np.percentile(x, [0, 50, 90, 100]))
+print(f"[{wl}] CTAs {len(a)}; kernel span {(a[:, 5].max() - t0) / 1e3:.1f} us (first entry -> last consumer exit)")
+print("  entry (us after first entry):            ", pc((a[:, 0] - t0) / 1e3))
+print("  wait for the cull  (entry -> past wait):  ", pc((a[:, 1] - a[:, 0]) / 1e3))
+w = a[a[:, 2] > 0]
+print("  first data landed (after the wait):      ", pc((w[:, 2] - w[:, 1]) / 1e3))
+w = a[a[:, 3] > 0]
+print(f"  CTAs with a brick: {len(w)}")
+print("  first brick phase 1 (table + blend):     ", pc((w[:, 3] - w[:, 2]) / 1e3))
+print("  first brick phases 2+3:                  ", pc((w[:, 4] - w[:, 3]) / 1e3))
+print("  rest (more bricks, end marker):          ", pc((w[:, 5] - w[:, 4]) / 1e3))
+print("  consumer exit (us after first entry):    ", pc((a[:, 5] - t0) / 1e3))
