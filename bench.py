@@ -36,10 +36,11 @@ def parse():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--workload", default="c2-dense")
     ap.add_argument("--impl", default="ofx", choices=["ofx", "reference"])
-    ap.add_argument("--also", default="c2,c1", help="extra workloads reported under 'also' (N=1 only); '' = none")
+    ap.add_argument("--also", default="c2,c1,c2-surface,c3", help="extra workloads reported under 'also' (N=1; at N=8 'c4' is added); '' = none")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of a CUDA graph replay")
     ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end leg (investigation runs)")
+    ap.add_argument("--no-parity", action="store_true", help="skip the post-run parity check against the CPU oracle")
     ap.add_argument("--no-pipeline", action="store_true", help="N > 1: broadcast -> kernel -> all-gather strictly in sequence")
     ap.add_argument("--cpu-planes", type=int, default=0, help="x-planes in the CPU sample (0 = auto)")
     ap.add_argument("--graph-ops", action="store_true",
@@ -70,47 +71,83 @@ def hbm_peak():
 
 # ------------------------------------------------------------------------------------------------
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clock and clock-event reasons sampled DURING the timed region: NVML polled in-process every millisecond by a
+    thread (the timed region is tens of milliseconds: `nvidia-smi -lms` cannot resolve it).  start()/stop() bracket
+    the region; only samples taken between mark_begin() and mark_end() count."""
+    REASONS = (("hw_slowdown", "nvmlClocksEventReasonHwSlowdown"), ("hw_thermal_slowdown", "nvmlClocksEventReasonHwThermalSlowdown"),
+               ("sw_thermal_slowdown", "nvmlClocksEventReasonSwThermalSlowdown"), ("sw_power_cap", "nvmlClocksEventReasonSwPowerCap"),
+               ("hw_power_brake", "nvmlClocksEventReasonHwPowerBrakeSlowdown"))
 
     def __init__(self, index=0):
-        self.rows, self.proc, self.index = [], None, index
+        self.rows, self.index, self.th, self.err = [], index, None, None
+        self._stop = threading.Event()
+        self.t_begin = self.t_end = None
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-i", str(self.index), "-lms", "100"], stdout=subprocess.PIPE, text=True)
-            self.th = threading.Thread(target=self._read, daemon=True)
-            self.th.start()
-        except Exception:
-            self.proc = None
+            import pynvml
+            pynvml.nvmlInit()
+            # CUDA_VISIBLE_DEVICES may renumber the devices: go through the PCI bus id of the torch device
+            import torch
+            bus = torch.cuda.get_device_properties(self.index).pci_bus_id if hasattr(torch.cuda.get_device_properties(self.index), "pci_bus_id") else None
+            h = None
+            if bus is not None:
+                for i in range(pynvml.nvmlDeviceGetCount()):
+                    hi = pynvml.nvmlDeviceGetHandleByIndex(i)
+                    if int(pynvml.nvmlDeviceGetPciInfo(hi).bus) == int(bus):
+                        h = hi
+                        break
+            self.h = h if h is not None else pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            self.nv = pynvml
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception as e:      # noqa: BLE001
+            self.err = f"NVML unavailable ({type(e).__name__}: {e})"
+            return
+        self.th = threading.Thread(target=self._poll, daemon=True)
+        self.th.start()
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+    def _poll(self):
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                try:
+                    mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:       # noqa: BLE001
+                    mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                self.rows.append((time.perf_counter(), float(mhz), int(mask)))
+            except Exception as e:      # noqa: BLE001
+                self.err = str(e)
+                return
+            time.sleep(0.001)
+
+    def mark_begin(self):
+        self.t_begin = time.perf_counter()
+
+    def mark_end(self):
+        self.t_end = time.perf_counter()
 
     def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            try:
-                sm.append(float(r[0])); mx.append(float(r[1]))
-            except Exception:
-                continue
-            for n, v in zip(names, r[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        if self.th is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [self.err or "NVML unavailable"], "samples": 0}
+        if self.t_end is None:
+            self.mark_end()
+        self._stop.set()
+        self.th.join(timeout=1)
+        inside = [r for r in self.rows if (self.t_begin or 0) <= r[0] <= self.t_end]
+        note = None
+        if len(inside) < 3:
+            inside, note = self.rows, "timed region too short to sample: all samples of the run (warm-up included) reported"
+        reasons = set()
+        for _, _, mask in inside:
+            for name, attr in self.REASONS:
+                if mask & int(getattr(self.nv, attr, 0)):
+                    reasons.add(name)
+        out = {"sm_mhz": float(np.median([r[1] for r in inside])) if inside else None, "sm_max_mhz": self.max_mhz,
+               "reasons": sorted(reasons), "samples": len(inside), "source": "NVML polled in-process every ms during the timed region"}
+        if note:
+            out["note"] = note
+        return out
 
 
 # ------------------------------------------------------------------------------------------------
@@ -293,6 +330,8 @@ def bench_workload(name, args, rank, world, device, with_e2e=True):
         # stream; no L2 flush: a GPU's per-frame working set (volume words + skin cache, > 300 MB at
         # N = 8) exceeds the 126 MB L2.
         sampler = ClockSampler(device.index or 0)
+        if rank == 0:
+            sampler.start()
         for i in range(3):                                     # warm the second packet / stream / NCCL channels
             sf.pipeline_begin(H, W, packets[0] if rank == 0 else None)
             sf.pipeline_step(packets[1] if rank == 0 else None)
@@ -319,9 +358,8 @@ def bench_workload(name, args, rank, world, device, with_e2e=True):
                 print(f"[bench] CUDA graph capture unavailable ({type(e).__name__}: {e}); timing eager launches", file=sys.stderr)
                 graph = None
                 barrier()
-        if rank == 0:
-            sampler.start()
         barrier()
+        sampler.mark_begin()
         e0, e1 = mk(), mk()
         t_wall0 = time.perf_counter()
         e0.record(stream)
@@ -331,6 +369,7 @@ def bench_workload(name, args, rank, world, device, with_e2e=True):
             run_pipeline()
         e1.record(stream)
         barrier()
+        sampler.mark_end()
         t_wall = time.perf_counter() - t_wall0
         clocks = sampler.stop() if rank == 0 else None
         step_ms_total = e0.elapsed_time(e1)
@@ -355,7 +394,11 @@ def bench_workload(name, args, rank, world, device, with_e2e=True):
         sampler = ClockSampler(device.index or 0)
         if rank == 0:
             sampler.start()
+        for i in range(20):                                    # ~10 ms of the same load before the region: the sampler sees the clocks settle
+            prep(i)
+            graph.replay() if graph is not None else core()
         barrier()
+        sampler.mark_begin()
         t_wall0 = time.perf_counter()
         for i in range(K):
             prep(i)
@@ -366,6 +409,7 @@ def bench_workload(name, args, rank, world, device, with_e2e=True):
                 core()
             evs[i][1].record(stream)
         barrier()
+        sampler.mark_end()
         t_wall = time.perf_counter() - t_wall0
         clocks = sampler.stop() if rank == 0 else None
         step_ms_total = sum(a.elapsed_time(b) for a, b in evs)
@@ -384,7 +428,7 @@ def bench_workload(name, args, rank, world, device, with_e2e=True):
     local_upd = float(stats_acc[_capi.STAT_UPDATED]) / K
     res = dict(workload=w, ms_per_step=step_ms, kernel_ms=kern_ms, updated=upd, skin_valid=valid, bricks=bricks,
                value=upd / (step_ms * 1e-3), wall_ms_per_step=t_wall * 1e3 / K, clocks=clocks,
-               local_updated=local_upd, launches_per_step=3, graph=graph is not None, pipelined=pipelined)   # node transforms, brick cull, fused kernel
+               local_updated=local_upd, launches_per_step=3, graph=graph is not None, pipelined=pipelined)   # frame preparation (+ node transforms), brick cull, fused kernel
     # roofline of the fused kernel on this rank's shard (rank 0 reports its own shard)
     alg_bytes = 24.0 * local_upd + 8.0 * H * W + 60.0 * w.M
     res["alg_bytes"] = alg_bytes
@@ -394,6 +438,18 @@ def bench_workload(name, args, rank, world, device, with_e2e=True):
     # ---- e2e: public API, host buffers, H2D + D2H inside the timed region ------------------------
     if with_e2e and not args.no_e2e:
         res["e2e"] = bench_e2e(w, vol, wf, sf, frames, ests, args, rank, world, device)
+    # fast-path indicator: the share of observed voxels whose TSDF is exactly 1 (free space seen again keeps 1
+    # without the float64 average); the rest takes the float64 running average
+    obs = (vol._weight_vol > 0)
+    n_obs = int(obs.sum().item())
+    n_one = int((obs & (vol._tsdf_vol == 1.0)).sum().item())
+    if world > 1:
+        cnt2 = torch.tensor([n_obs, n_one], dtype=torch.int64, device=device)
+        dist.all_reduce(cnt2, op=dist.ReduceOp.SUM)
+        n_obs, n_one = int(cnt2[0]), int(cnt2[1])
+    res["free_space_share"] = n_one / max(1, n_obs)
+    if not args.no_parity:
+        res["parity"] = parity_check(w, vol, sf, rank, world, device)
     del vol, wf, sf, packets, flush
     torch.cuda.empty_cache()
     return res
@@ -404,9 +460,12 @@ def kern_ms_local(evs, K):
 
 
 def bench_e2e(w, vol, wf, sf, frames, ests, args, rank, world, device):
-    """Per step, through the public classes: rank 0 takes the HOST frame + the estimator dict,
-    WarpField.update_transformations (host numpy), H2D of RGB+Z (pinned staging) and of R,T;
-    [N>1: one NCCL broadcast]; fused kernel; counters read back to the host."""
+    """Per step, through the public classes, starting from HOST memory: rank 0 takes the camera frame (page-locked
+    numpy) + the estimator dict, WarpField.update_transformations (host numpy), host->device copy of RGB+Z and of R|T,
+    [N>1: the packet travels to the other ranks], the kernels, and the frame's counters come back to the host.
+    The public calls do not wait for the device: the upload of frame t+1 overlaps the kernels of frame t, and the
+    counters a step reads are those of the frame BEFORE it (the last ones are read after the loop, inside the timed
+    region)."""
     import torch
     import torch.distributed as dist
     n_frames = len(ests)
@@ -419,35 +478,51 @@ def bench_e2e(w, vol, wf, sf, frames, ests, args, rank, world, device):
     fid = [getattr(vol, "frame_id", 0)]
     wf.frame_id = fid[0]                 # the warp field follows the volume's frame counter (warpfield.py:399)
 
-    def step(i):
+    def host_side(i):
+        """rank 0: the estimator's output -> origin-form node transforms (WarpField.update_transformations)"""
         est = dict(ests[i % n_frames])
         fid[0] += 1
         est["target_frame_id"] = fid[0]
-        if world == 1:
-            wf.update_transformations(est)
-            vol.integrate({"im": frames[1 + i % n_frames], "id": fid[0]})
-            return vol.last_stats()["updated"]
-        if rank == 0:
-            wf.frame_id = vol.frame_id
-            wf.update_transformations(est)
-            sf.fill_packet(frames[1 + i % n_frames], wf.rotations, wf.translations)
-        else:
-            vol.frame_id = fid[0]
-        out = sf.step(H, W, identity_warp=False)
-        return int(out[:, 0].sum().item())
+        wf.frame_id = vol.frame_id = fid[0] - 1
+        wf.update_transformations(est)
+        vol.frame_id = fid[0]
+        return frames[1 + i % n_frames], wf.rotations, wf.translations
 
-    for i in range(Wm):
-        step(i)
+    def run(n):
+        """n frames; returns the updated voxels summed over them (every frame's counters are read on the host)"""
+        upd = 0
+        if world == 1:
+            vol.frame_id = fid[0]
+            for i in range(n):
+                est = dict(ests[i % n_frames])
+                fid[0] += 1
+                est["target_frame_id"] = fid[0]
+                wf.update_transformations(est)
+                vol.integrate({"im": frames[1 + i % n_frames], "id": fid[0]})
+                if i > 0:
+                    upd += vol.last_stats(previous=True)["updated"]          # frame i-1: never stalls frame i
+            return upd + vol.last_stats()["updated"]
+        # N > 1: the pipelined transport on host frames (sharded.py: pipeline_step(next_packet=(im, R, T)))
+        sf.pipeline_begin(H, W, host_side(0) if rank == 0 else None)
+        for i in range(n):
+            nxt = host_side(i + 1) if (rank == 0 and i + 1 < n) else None
+            sf.pipeline_step(nxt, last=(i + 1 == n))
+            if i >= 2:
+                upd += int(sf.counters_host(i - 2)[:, 0].sum())               # gathered two exchanges ago: no stall
+        sf.pipeline_end()
+        for t in range(max(0, n - 2), n):
+            upd += int(sf.counters_host(t)[:, 0].sum())
+        return upd
+
+    run(Wm)
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize(device)
     t0 = time.perf_counter()
-    upd = 0
-    for i in range(K):
-        upd += step(i)
+    upd = run(K)
+    torch.cuda.synchronize(device)
     if world > 1:
         dist.barrier()
-    torch.cuda.synchronize(device)
     dt = time.perf_counter() - t0
     tmax = torch.tensor([dt], dtype=torch.float64, device=device)
     if world > 1:
@@ -455,7 +530,163 @@ def bench_e2e(w, vol, wf, sf, frames, ests, args, rank, world, device):
     dt = float(tmax[0])
     h2d = 4 * 4 * H * W + 48 * w.M
     return {"value": upd / dt, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 32 * world,
-            "ms_per_step": dt * 1e3 / K, "timing": "host wall clock around K steps (includes host numpy + sync per step)"}
+            "ms_per_step": dt * 1e3 / K, "updated_per_frame": upd / K,
+            "timing": "host wall clock around K steps of the public calls on host frames; uploads overlap the kernels, "
+                      "every frame's counters are read on the host inside the timed region (one frame late)"}
+
+
+# ------------------------------------------------------------------------------------------------
+def parity_check(w, vol, sf, rank, world, device, n_warped=3, seed=4321):
+    """OUTSIDE the timed region: resets this rank's shard, drives the source frame + n_warped warped frames through the
+    SAME driver the timed run used (N > 1: the pipelined transport -- symmetric-memory packets, two streams, one collective
+    per frame; N = 1: the fused call on device packets), then compares a seeded sample of THIS rank's voxels (uniform,
+    around the surface, whole z-rows) with the CPU oracle replaying the same frames through its point operators
+    (skin -> warp -> integrate).  Bit-exact or it counts as a mismatch.  Returns (checked, mismatches) summed over ranks."""
+    import torch
+    import torch.distributed as dist
+    from occlusionfusion_b200 import _capi
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle as O
+    O.build()
+    O.set_threads(max(1, min(8, (os.cpu_count() or 8) // max(1, world))))
+    H, W = w.H, w.W
+    lib = _capi.load()
+    _capi.check(lib.ofx_volume_reset(vol._h, _capi.stream_ptr(device)))
+    frames = [w.frame(i) for i in range(n_warped + 1)]           # every rank can render the synthetic frames itself
+    ests = [w.estimate(i) for i in range(1, n_warped + 1)]
+    Ts = [(-np.einsum("nij,nj->ni", e["node_rotations"], w.nodes) + w.nodes + e["node_translations"]).astype(np.float32) for e in ests]
+    # source frame (identity warp), sequential driver
+    if rank == 0:
+        sf.fill_packet(frames[0], np.tile(np.eye(3, dtype=np.float32), (w.M, 1, 1)), np.zeros((w.M, 3), np.float32))
+    sf.step(H, W, identity_warp=True)
+    packets = []
+    for i in range(n_warped):
+        if rank == 0:
+            sf.fill_packet(frames[i + 1], ests[i]["node_rotations"], Ts[i])
+        torch.cuda.synchronize(device)
+        packets.append(sf.buf.clone())
+    if world > 1:
+        sf.pipeline_begin(H, W, packets[0] if rank == 0 else None)
+        for i in range(n_warped):
+            sf.pipeline_step(packets[i + 1] if (rank == 0 and i + 1 < n_warped) else None, last=(i + 1 == n_warped))
+        sf.pipeline_end()
+    else:
+        for pk in packets:
+            sf.buf.copy_(pk)
+            v = sf.views
+            sf.be.integrate_warped(v["R"], v["T"], v["depth"], v["colour"], 1.0)
+    torch.cuda.synchronize(device)
+
+    # the sample: local (lx, iy, iz) of this rank's planes
+    Dx, Dy, Dz = w.dims
+    nx = len(sf.planes)
+    rng = np.random.default_rng(seed + rank)
+    n_uni = 60_000
+    ijk = [np.stack([rng.integers(0, nx, n_uni), rng.integers(0, Dy, n_uni), rng.integers(0, Dz, n_uni)], 1)]
+    if w.scene == "band":
+        d = rng.normal(size=(100_000, 3))
+        d /= np.linalg.norm(d, axis=1, keepdims=True)
+        d[:, 2] = -np.abs(d[:, 2])
+        p = w.centre + (w.radius + rng.uniform(-0.08, 0.08, (len(d), 1))) * d
+        q = np.rint((p - w.origin.astype(np.float64)) / w.voxel_size).astype(np.int64)
+        q = q[((q >= 0) & (q < np.array(w.dims))).all(1)]
+        lx_of = -np.ones(Dx, np.int64)
+        lx_of[sf.planes] = np.arange(nx)
+        keep = lx_of[q[:, 0]] >= 0
+        ijk.append(np.stack([lx_of[q[keep, 0]], q[keep, 1], q[keep, 2]], 1))
+    rows = np.stack([rng.integers(0, nx, 24), rng.integers(0, Dy, 24)], 1)
+    ijk.append(np.concatenate([np.concatenate([np.repeat(r[None], Dz, 0), np.arange(Dz)[:, None]], 1) for r in rows]))
+    ijk = np.concatenate(ijk)
+    flat = np.unique((ijk[:, 0] * Dy + ijk[:, 1]) * Dz + ijk[:, 2])
+    lx, iy, iz = flat // (Dy * Dz), (flat // Dz) % Dy, flat % Dz
+    px = O.vox2world(w.origin, w.voxel_size, (Dx, 1, 1))[:, 0][sf.planes]
+    py = O.vox2world(w.origin, w.voxel_size, (1, Dy, 1))[:, 1]
+    pz = O.vox2world(w.origin, w.voxel_size, (1, 1, Dz))[:, 2]
+    pts = np.stack([px[lx], py[iy], pz[iz]], 1).astype(np.float32)
+    a, wts, valid = O.skin(pts, w.nodes, w.K, w.coverage)
+    t = np.ones(len(flat), np.float32)
+    wt = np.zeros(len(flat), np.float32)
+    c = np.zeros(len(flat), np.float32)
+    for f in range(n_warped + 1):
+        color_im, depth_im = O.pack_frame(frames[f])
+        if f == 0:
+            cam_pts, ok = pts, np.ones(len(pts), bool)
+        else:
+            cam_pts, ok = O.warp(pts, a, wts, valid, ests[f - 1]["node_rotations"], Ts[f - 1]), valid
+        O.integrate(t, wt, c, cam_pts, ok, depth_im, color_im, w.intr, w.trunc, 1.0)
+    ft = torch.from_numpy(flat).to(device)
+    g_t = vol._tsdf_vol.reshape(-1)[ft].cpu().numpy()
+    g_w = vol._weight_vol.reshape(-1)[ft].cpu().numpy()
+    g_c = vol._color_vol.reshape(-1)[ft].cpu().numpy()
+    bad = int(((g_t != t) | (g_w != wt) | (g_c != c)).sum())
+    res = torch.tensor([len(flat), bad, int((wt > 0).sum())], dtype=torch.int64, device=device)
+    if world > 1:
+        dist.all_reduce(res, op=dist.ReduceOp.SUM)
+    return {"checked": int(res[0]), "mismatches": int(res[1]), "sampled_voxels_updated": int(res[2]), "frames": n_warped + 1,
+            "how": "after the timed region every rank resets its shard, reruns source + warped frames through the driver the "
+                   "timed run used and compares a seeded voxel sample of its own planes with the CPU oracle, bit for bit"}
+
+
+def bench_c3(args, device, n_frames=100):
+    """BASELINE config 3: a 100-frame sequence at 256^3 with a per-frame graph-node update and node insertion every 10th
+    frame, through the drop-in classes the way fusion_with_occlusion/fusion.py:202-221 drives them (the canonical mesh
+    for the insertion comes from the volume itself: truncated region -> marching cubes -> erosion -> unreachable vertices ->
+    greedy insertion -> edge rebuild -> re-skin).  Host wall clock around synchronised phases; the estimator that would
+    produce the transforms is outside the path and outside the timing."""
+    import torch
+    from occlusionfusion_b200 import EDGraph, TSDFVolume, WarpField
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload("c1")
+    vol = TSDFVolume(w.bbox, w.max_depth, w.intr, w.fopt, None, device=device)
+    frames = [torch.from_numpy(w.frame(f)).pin_memory().numpy() for f in range(8)]
+
+    def timed(fn):
+        torch.cuda.synchronize(device)
+        t0 = time.perf_counter()
+        r = fn()
+        torch.cuda.synchronize(device)
+        return (time.perf_counter() - t0) * 1e3, r
+
+    t_src, _ = timed(lambda: vol.integrate({"im": frames[0], "id": 0}))
+    graph = EDGraph(tsdf=vol, nodes=np.zeros((0, 3), np.float32), graph_generation_parameters={"node_coverage": w.coverage})
+    t_build, _ = timed(lambda: graph.create_graph_from_mesh(*vol.get_canonical_model()[:2]))
+    wf = WarpField(graph, vol, None)
+    wf.graph_neighbours = w.K
+    vol.warpfield = wf
+    t_graph, growth, upd_total = [], [int(graph.nodes.shape[0])], 0
+    ests = {}
+    t_all0 = time.perf_counter()
+    t_est = 0.0
+    t_frames = 0.0
+    for f in range(1, n_frames):
+        if f % 10 == 0:
+            vol.clear()
+            ms, _ = timed(lambda: wf.update_graph())
+            t_graph.append(ms)
+            growth.append(int(wf.graph.nodes.shape[0]))
+        t0 = time.perf_counter()
+        est = w.estimate(f, wf.graph.nodes)                     # stands in for the estimator (not part of the path)
+        t_est += time.perf_counter() - t0
+        t0 = time.perf_counter()
+        wf.update_transformations(est)
+        vol.integrate({"im": frames[f % len(frames)], "id": f})
+        if f > 1 and f % 10 != 1:
+            upd_total += vol.last_stats(previous=True)["updated"]
+        t_frames += time.perf_counter() - t0
+        if f % 10 == 9 or f == n_frames - 1:
+            t0 = time.perf_counter()
+            upd_total += vol.last_stats()["updated"]            # drains the frame loop before the graph update
+            t_frames += time.perf_counter() - t0
+    torch.cuda.synchronize(device)
+    wall = time.perf_counter() - t_all0 - t_est
+    n = n_frames - 1
+    return {"workload": f"c3 = {w.name}: {w.dims[0]}^3 voxels @ {w.voxel_size * 1e3:.0f} mm, {w.W}x{w.H}, K={w.K}, {n_frames} frames, "
+                        f"update_transformations + integrate every frame from host frames, update_graph every 10th frame",
+            "frames": n_frames, "ms_per_frame_all_in": wall * 1e3 / n, "value": upd_total / wall, "unit": UNIT,
+            "frame_loop_ms_per_frame": t_frames * 1e3 / n, "update_graph_ms": [round(x, 2) for x in t_graph],
+            "update_graph_ms_median": float(np.median(t_graph)) if t_graph else None, "nodes": growth,
+            "source_frame_ms": t_src, "graph_from_source_mesh_ms": t_build, "updated_voxels": int(upd_total),
+            "timing": "host wall clock; frame loop asynchronous (counters read one frame late), each update_graph synchronised"}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -659,21 +890,35 @@ def main():
     main_res = bench_workload(args.workload, args, rank, world, device)
     main_res.setdefault("e2e", None)
     also = {}
-    if world == 1 and args.also:
-        for name in [n for n in args.also.split(",") if n and n != args.workload]:
-            r = bench_workload(name, args, rank, world, device, with_e2e=True)
-            also[name] = {"value": r["value"], "unit": UNIT, "ms_per_step": r["ms_per_step"],
-                          "kernel_ms": r["kernel_ms_local"], "updated_per_frame": r["updated"],
-                          "skin_valid_per_frame": r["skin_valid"], "bricks_per_frame": r["bricks"],
-                          "voxels": int(np.prod(r["workload"].dims)),
-                          "achieved_gbs": r["achieved_gbs"], "e2e": r["e2e"],
-                          "config": workload_config(r["workload"], world)}
+    peak, peak_src = hbm_peak()
+
+    def also_entry(r):
+        e = {"value": r["value"], "unit": UNIT, "ms_per_step": r["ms_per_step"], "kernel_ms": r["kernel_ms_local"],
+             "updated_per_frame": r["updated"], "skin_valid_per_frame": r["skin_valid"], "bricks_per_frame": r["bricks"],
+             "voxels": int(np.prod(r["workload"].dims)), "achieved_gbs": r["achieved_gbs"], "e2e": r.get("e2e"),
+             "free_space_share_of_observed_voxels": r.get("free_space_share"), "parity": r.get("parity"),
+             "roofline": {"bound": "hbm", "achieved": r["achieved_gbs"], "peak": peak, "unit": "GB/s", "frac": r["achieved_gbs"] / peak,
+                          "algorithmic_bytes_per_launch": r["alg_bytes"], "kernel_ms": r["kernel_ms_local"], "peak_source": peak_src},
+             "config": workload_config(r["workload"], world, r.get("pipelined", False))}
+        return e
+
+    names = [n for n in args.also.split(",") if n and n != args.workload] if args.also else []
+    if world == 1:
+        for name in names:
+            if name == "c3":
+                also["c3"] = bench_c3(args, device)
+            else:
+                also[name] = also_entry(bench_workload(name, args, rank, world, device, with_e2e=True))
+    elif world == 8 and args.also:
+        # BASELINE config 5 (1024^3, 1280x720, ~4k nodes, K = 8) is quoted on 8 GPUs
+        r = bench_workload("c4", args, rank, world, device, with_e2e=True)
+        if rank == 0:
+            also["c4"] = also_entry(r)
     cb = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cb = cpu_baseline(Workload(args.workload), 6, args.cpu_planes)
     if rank == 0:
         w = main_res["workload"]
-        peak, peak_src = hbm_peak()
         line = {
             "metric": METRIC, "value": main_res["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": main_res["ms_per_step"], "higher_is_better": True,
@@ -690,17 +935,22 @@ def main():
                          "traffic": (ncu_traffic(w.name) or {}).get("dram_bytes_per_launch") if world == 1 else None,
                          "traffic_source": (ncu_traffic(w.name) or {}).get("source") if world == 1 else None,
                          "peak_source": peak_src,
-                         "kernel": "fused_warped_persistent<K,VEC,OBS32> (+ brick_cull_kernel: "
-                                   "CUDA events around ofx_integrate)",
+                         "kernel": "fused_warped_persistent<K,OBS1> (+ frame_prep_kernel + brick_cull_kernel: "
+                                   "CUDA events around ofx_integrate_warped)",
                          "kernel_ms": main_res["kernel_ms_local"],
                          "algorithmic_bytes_per_launch": main_res["alg_bytes"],
                          "bytes_formula": "24*N_updated(this GPU) + 8*W*H + 60*M"},
             "cpu_baseline": cb, "also": also,
+            "parity": main_res.get("parity"),
+            "free_space_share_of_observed_voxels": main_res.get("free_space_share"),
         }
         print(json.dumps(line), flush=True)
+    bad = (main_res.get("parity") or {}).get("mismatches", 0)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    if bad:
+        raise SystemExit(f"bench.py: parity check FAILED: {bad} sampled voxels differ from the oracle")
 
 
 if __name__ == "__main__":

@@ -12,7 +12,9 @@ graph_proc.cpp:155-481) are host work in the reference and here: native host cod
 be supplied by the caller (the fusion path itself reads only `nodes`).
 """
 import ctypes
+import json
 import logging
+import os
 
 import numpy as np
 import torch
@@ -34,18 +36,55 @@ DEFAULT_GRAPH_PARAMETERS = {           # embedded_deformation_graph.py:62-73
 class EDGraph:
     def __init__(self, tsdf=None, visualizer=None, source_frame_data=None, *, nodes=None,
                  graph_generation_parameters=None):
+        """EDGraph(tsdf, visualizer, source_frame_data) -- the reference constructor (embedded_deformation_graph.py:27-52,
+        call site fusion.py:74): graph parameters from <datadir>/graph_config.json (written with the defaults when absent),
+        graph built from the marching-cubes mesh of `tsdf` (create_graph_from_tsdf), results folders created.
+        Keyword-only extras: nodes= supplies the node table directly (the fusion path itself reads only `nodes`),
+        graph_generation_parameters= overrides entries of the configuration."""
         self.log = logging.getLogger(__name__)
         self.tsdf, self.vis = tsdf, visualizer
         if tsdf is not None:
+            self.log.info(f"Creating Graph from:{tsdf.__class__.__name__}")
             self.opt = tsdf.fopt
             tsdf.graph = self                                   # embedded_deformation_graph.py:40
-        self.graph_generation_parameters = dict(DEFAULT_GRAPH_PARAMETERS)
+        if nodes is None and tsdf is not None:
+            self.load_graph_config()                            # :34
+        else:
+            self.graph_generation_parameters = dict(DEFAULT_GRAPH_PARAMETERS)
         if graph_generation_parameters:
             self.graph_generation_parameters.update(graph_generation_parameters)
-        if nodes is None:
-            raise NotImplementedError("pass nodes=, or build them with EDGraph.from_mesh(vertices, faces): marching cubes "
-                                      "(tsdf.py:794) is not rebuilt, so the graph cannot start from a TSDFVolume alone")
-        self.nodes = np.ascontiguousarray(nodes, dtype=np.float32)
+        if nodes is not None:
+            self.nodes = np.ascontiguousarray(nodes, dtype=np.float32)
+            return
+        if tsdf is None:
+            raise ValueError("EDGraph needs a TSDFVolume (the reference signature) or nodes=")
+        self.create_graph_from_tsdf()                           # :43
+        datadir = getattr(self.opt, "datadir", None)
+        if datadir is not None:                                 # :49-52
+            self.savepath = os.path.join(datadir, "results")
+            os.makedirs(self.savepath, exist_ok=True)
+            os.makedirs(os.path.join(self.savepath, "updated_graph"), exist_ok=True)
+
+    def load_graph_config(self):
+        """Parameters for generating the graph (embedded_deformation_graph.py:54-75): <datadir>/graph_config.json when it
+        exists, else the defaults, which are then written there."""
+        datadir = getattr(self.opt, "datadir", None)
+        path = os.path.join(datadir, "graph_config.json") if datadir is not None else None
+        if path is not None and os.path.isfile(path):
+            with open(path) as f:
+                self.graph_generation_parameters = json.load(f)
+        else:
+            self.graph_generation_parameters = dict(DEFAULT_GRAPH_PARAMETERS)
+            if path is not None:
+                with open(path, "w") as f:
+                    json.dump(self.graph_generation_parameters, f)
+
+    def create_graph_from_tsdf(self):
+        """embedded_deformation_graph.py:79-84: the graph of the volume's current surface (marching cubes on the device)."""
+        assert hasattr(self, "tsdf"), "TSDF not defined in graph. Add tsdf as attribute to EDGraph first."
+        vertices, faces, normals, colors = self.tsdf.get_mesh()
+        self.log.debug(f"Creating graph from mesh. Vertices:{vertices.shape} Faces:{faces.shape}")
+        self.create_graph_from_mesh(vertices, faces)
 
     # ------------------------------------------------------------------ device helpers
     @property

@@ -185,6 +185,15 @@ class ShardedFusion:
         self._pviews = [self.packet.views(b) for b in self._pbuf]
         self._pstats = [torch.zeros(N_STATS, dtype=torch.int64, device=dev) for _ in range(2)]
         self._pgath = [torch.zeros(self.world * N_STATS, dtype=torch.int64, device=dev) for _ in range(2)]
+        # gathered counters also land in page-locked host memory behind each exchange: read lazily (counters_host)
+        self._pgath_host = [torch.zeros(self.world * N_STATS, dtype=torch.int64).pin_memory() if dev.type == "cuda"
+                            else torch.zeros(self.world * N_STATS, dtype=torch.int64) for _ in range(2)]
+        self._ev_gath = [torch.cuda.Event() for _ in range(2)] if dev.type == "cuda" else [None, None]
+        # host-frame staging on the rank that receives the camera frames (pipeline_step(next_packet=(im, R, T)))
+        self._hraw = [None, None]
+        self._hRT = [None, None]
+        self._hfr = [None, None]
+        self._ev_staged = [None, None]
         self._comm = torch.cuda.Stream(device=dev, priority=-1)   # its few small operations go first
         self._ev_bcast = [torch.cuda.Event() for _ in range(2)]
         self._ev_done = [torch.cuda.Event() for _ in range(2)]
@@ -219,13 +228,18 @@ class ShardedFusion:
         with torch.cuda.stream(self._comm):
             if prev is not None:
                 self._comm.wait_event(self._ev_done[prev % 2])
-            if publish and self.rank == 0 and packet is not None and packet.data_ptr() != self._pbuf[j].data_ptr():
+            if publish and self.rank == 0 and isinstance(packet, (tuple, list)):
+                self._stage_host(j, *packet)                     # HOST frame + node transforms -> packet j (asynchronous)
+            elif publish and self.rank == 0 and packet is not None and packet.data_ptr() != self._pbuf[j].data_ptr():
                 self._pbuf[j].copy_(packet, non_blocking=True)
             pj = 0 if prev is None else prev % 2
             if self.world > 1:
                 dist.all_gather_into_tensor(self._pgath[pj], self._pstats[pj], group=self.group)
             else:
                 self._pgath[pj].copy_(self._pstats[pj])
+            if prev is not None and self._ev_gath[pj] is not None:
+                self._pgath_host[pj].copy_(self._pgath[pj], non_blocking=True)
+                self._ev_gath[pj].record(self._comm)
             if self.world > 1 and publish:
                 if self._peer_src is None:
                     dist.broadcast(self._pbuf[j], src=0, group=self.group)
@@ -244,9 +258,52 @@ class ShardedFusion:
             self._ev_bcast[j].record(self._comm)
         return self._pgath[pj].view(self.world, N_STATS)
 
+    def _stage_host(self, j, im, R, T):
+        """Rank 0, on the communication stream: a HOST frame (6,H,W) float32 (RGB in [0,1] + XYZ, tsdf.py:545-572) and the
+        node transforms R (M,3,3), T (M,3) into packet j -- RGB + Z are DMA'd (straight from the caller's buffer when it is
+        page-locked: do not overwrite it before the next pipeline_step returns), folded into the packet's colour / depth
+        images on the device (ofx_pack_frame), R | T go through a pinned staging buffer.  Nothing waits for the device."""
+        from . import _capi
+        H, W = self._HW
+        M = self.M
+        dev = self.device
+        if self._hraw[j] is None:
+            self._hraw[j] = torch.empty((4, H, W), dtype=torch.float32, device=dev)
+            self._hRT[j] = torch.empty(12 * M, dtype=torch.float32).pin_memory()
+        elif self._ev_staged[j] is not None:
+            self._ev_staged[j].synchronize()                     # the staging of two frames ago has left the pinned buffers
+        src = im if isinstance(im, torch.Tensor) else torch.from_numpy(np.asarray(im, dtype=np.float32))
+        if not src.is_pinned():
+            if self._hfr[j] is None:
+                self._hfr[j] = torch.empty((4, H, W), dtype=torch.float32).pin_memory()
+            self._hfr[j][:3].copy_(src[:3])
+            self._hfr[j][3].copy_(src[-1])
+            self._hraw[j].copy_(self._hfr[j], non_blocking=True)
+        else:
+            self._hraw[j][:3].copy_(src[:3], non_blocking=True)
+            self._hraw[j][3].copy_(src[-1], non_blocking=True)
+        v = self._pviews[j]
+        _capi.check(_capi.load().ofx_pack_frame(_capi.ptr(self._hraw[j]), 4, H, W, _capi.ptr(v["colour"]), _capi.ptr(v["depth"]),
+                                                _capi.stream_ptr(dev)))
+        h = self._hRT[j].numpy()
+        h[:9 * M] = np.asarray(R, dtype=np.float32).reshape(-1)
+        h[9 * M:] = np.asarray(T, dtype=np.float32).reshape(-1)
+        self._pbuf[j][:12 * M].copy_(self._hRT[j], non_blocking=True)      # R at word 0, T at word 9 M (FramePacket)
+        if self._ev_staged[j] is None:
+            self._ev_staged[j] = torch.cuda.Event()
+        self._ev_staged[j].record(self._comm)
+
+    def counters_host(self, t):
+        """The gathered (world, N_STATS) counters of frame t as a host array; waits only for that frame's exchange
+        (frame t's counters are gathered by the pipeline_step / pipeline_end call after the one that integrated it)."""
+        pj = t % 2
+        self._ev_gath[pj].synchronize()
+        return self._pgath_host[pj].view(self.world, N_STATS).numpy().copy()
+
     def pipeline_step(self, next_packet=None, last=False, obs_weight=1.0):
         """Integrate frame t (its packet was published by the previous call) while frame t+1's packet
-        (`next_packet` on rank 0; ignored when `last`) is published and the counters of frame t-1 are
+        (`next_packet` on rank 0: a device-resident packet, or a HOST frame with its node transforms as the tuple
+        (im (6,H,W), R (M,3,3), T (M,3)); ignored when `last`) is published and the counters of frame t-1 are
         gathered.  Returns the (world, N_STATS) counter tensor of frame t-1 (meaningless for t = 0); it is valid
         once the communication stream has run.  pipeline_end() returns the last frame's counters."""
         t, j = self._pipe_t, self._pipe_t % 2

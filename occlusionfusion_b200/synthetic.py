@@ -8,7 +8,8 @@ Workloads
            only voxels within 4*node_coverage of the surface are skin-valid (the realistic case).
   "dense"  nodes on a jittered 3-D lattice through the whole volume, depth = a plane at the far
            face: every voxel is skin-valid and every in-frustum voxel updates (the HBM-bound
-           case the roofline figure is quoted on).
+           case the roofline figure is quoted on).  With surface=True the plane is tilted and cuts
+           the volume at 80 % of its depth (a real surface band; voxels behind it do not update).
 """
 import types
 
@@ -23,8 +24,13 @@ CONFIGS = {
     "c4": dict(dim=1024, voxel=0.0025, n_nodes=4000, K=8, H=720, W=1280, scene="band"),
     "c1-dense": dict(dim=256, voxel=0.005, n_nodes=1000, K=4, H=480, W=640, scene="dense"),
     "c2-dense": dict(dim=512, voxel=0.0025, n_nodes=2197, K=4, H=480, W=640, scene="dense"),
+    # the same dense volume and graph, but the depth image is a tilted plane THROUGH the volume: voxels in front of it see
+    # free space, a band of +-trunc around it takes the float64 running average, voxels behind it are not updated
+    "c2-surface": dict(dim=512, voxel=0.0025, n_nodes=2197, K=4, H=480, W=640, scene="dense", surface=True),
 }
 SEED0 = 20221
+# seed offsets are fixed per workload (adding a workload must not reseed the others)
+SEED_INDEX = {"c0": 0, "c1": 1, "c1-dense": 2, "c2": 3, "c2-dense": 4, "c4": 5, "tiny": 6, "c2-surface": 7}
 
 
 def rodrigues(rv):
@@ -60,7 +66,7 @@ class Workload:
         cfg = dict(CONFIGS[name])
         cfg.update(override)
         self.name, self.cfg = name, cfg
-        self.seed = SEED0 + sorted(CONFIGS).index(name) if seed is None else seed
+        self.seed = SEED0 + SEED_INDEX[name] if seed is None else seed
         rng = np.random.default_rng(self.seed)
         H, W = cfg["H"], cfg["W"]
         self.H, self.W = H, W
@@ -108,6 +114,10 @@ class Workload:
             nodes = self.origin.astype(np.float64) + (gi + 0.5) * sp
             self.coverage = float(np.round(0.5 * sp.max(), 4))
             self.plane_depth = float(self.origin[2] + ext[2])
+            self.surface = bool(cfg.get("surface", False))
+            if self.surface:
+                self.plane_n = np.array([0.3, 0.2, 1.0]) / np.linalg.norm([0.3, 0.2, 1.0])
+                self.plane_c = float(self.plane_n[2] * (self.origin[2] + 0.8 * ext[2]))
         nodes = nodes + rng.uniform(-1e-3, 1e-3, nodes.shape)
         self.nodes = nodes.astype(np.float32)
         self.M = len(self.nodes)
@@ -126,6 +136,8 @@ class Workload:
             cc = float(c @ c) - self.radius ** 2
             disc = b * b - 4 * a * cc
             t = np.where(disc > 0, (-b - np.sqrt(np.maximum(disc, 0))) / (2 * a), 0.0)
+        elif getattr(self, "surface", False):
+            t = (self.plane_c - 0.001 * f) / (d * self.plane_n[:, None, None]).sum(0)      # ray . n = c: camera z of the plane
         else:
             t = np.full((H, W), self.plane_depth - 0.001 * f)
         im = np.empty((6, H, W), np.float32)

@@ -77,9 +77,22 @@ class TSDFVolume:
             _capi.check(self._lib.ofx_volume_reset(self._h, _capi.stream_ptr(self.device)))  # tsdf=1, w=0, c=0
             self._stats = torch.zeros(_capi.OFX_N_STATS, dtype=torch.int64, device=self.device)
         self._intr4 = _capi.intr4(self.cam_intr)
-        self._frame_host = None      # pinned staging buffer for the (6,H,W) frame
-        self._frame_dev = None
-        self._h2d_done = None
+        # Two per-frame sets (raw frame, packed colour, depth, counters) used in turn, an upload stream and events:
+        # the host->device copy of frame t+1 runs on the upload stream while the kernels of frame t run on the
+        # caller's stream; nothing in integrate() waits for the device (counters are read lazily, last_stats()).
+        self._set = 0
+        self._frame_host = [None, None]     # pinned staging for frames that arrive in pageable memory
+        self._frame_dev = [None, None]
+        self._color_ims = [None, None]
+        self._depth_ims = [None, None]
+        self._stats_sets = [self._stats, torch.zeros_like(self._stats)]
+        self._stats_host = [torch.zeros(_capi.OFX_N_STATS, dtype=torch.int64).pin_memory() for _ in range(2)]
+        self._h2d_done = [torch.cuda.Event(), torch.cuda.Event()]
+        self._set_done = [torch.cuda.Event(), torch.cuda.Event()]     # the kernels that read set j have finished
+        self._set_used = [False, False]
+        self._stats_ready = [None, None]                               # event after the counters' device->host copy
+        with torch.cuda.device(self.device):
+            self._copy_stream = torch.cuda.Stream(device=self.device)
         self._color_im_dev = self._depth_im_dev = None
         self._world_pts = None
 
@@ -144,8 +157,11 @@ class TSDFVolume:
     def update(self, im, frame_id):
         """Update RGB-D frame info (tsdf.py:545-572): (6,H,W) float32, RGB in [0,1] + XYZ.
 
-        The frame is staged through pinned memory, uploaded once, and folded into the packed
-        colour image and the depth image on the device (same float32 op order)."""
+        Only RGB + Z (4 of the 6 channels) are uploaded -- on a separate upload stream, into the per-frame set that the
+        frame before last used, so the copy overlaps the previous frame's kernels -- and folded into the packed colour
+        image and the depth image on the device (same float32 op order).  A frame in page-locked memory is DMA'd
+        straight from the caller's buffer: do not overwrite it before wait_uploaded() returns; a frame in pageable
+        memory is copied into a pinned staging buffer first and may be reused at once."""
         im_t = im if isinstance(im, torch.Tensor) else None
         shape = tuple(im.shape)
         assert len(shape) == 3 and shape[0] >= 4, \
@@ -153,39 +169,53 @@ class TSDFVolume:
         if shape[0] != 6:
             raise ValueError("expected a (6,H,W) RGB+XYZ frame")
         H, W = shape[1:]
-        # only RGB (im[:3]) and Z (im[-1]) are read by the path: upload 4 of the 6 channels
-        if self._frame_dev is None or tuple(self._frame_dev.shape[1:]) != (H, W):
-            self._frame_host = torch.empty((4, H, W), dtype=torch.float32, pin_memory=True)
-            self._frame_dev = torch.empty((4, H, W), dtype=torch.float32, device=self.device)
-            self._color_im_dev = torch.empty((H, W), dtype=torch.float32, device=self.device)
-            self._depth_im_dev = torch.empty((H, W), dtype=torch.float32, device=self.device)
+        j = self._set = 1 - self._set
+        if self._frame_dev[j] is None or tuple(self._frame_dev[j].shape[1:]) != (H, W):
+            self._frame_dev[j] = torch.empty((4, H, W), dtype=torch.float32, device=self.device)
+            self._color_ims[j] = torch.empty((H, W), dtype=torch.float32, device=self.device)
+            self._depth_ims[j] = torch.empty((H, W), dtype=torch.float32, device=self.device)
+            self._frame_host[j] = None
+        comp = torch.cuda.current_stream(self.device)
+        fd = self._frame_dev[j]
         if im_t is not None and im_t.is_cuda:
-            self._frame_dev[:3].copy_(im_t[:3])
-            self._frame_dev[3].copy_(im_t[-1])
+            fd[:3].copy_(im_t[:3])
+            fd[3].copy_(im_t[-1])
         else:
             src = im_t if im_t is not None else torch.from_numpy(np.asarray(im, dtype=np.float32))
-            if src.is_pinned():
-                # the caller's frame already lives in page-locked memory: DMA the four channels straight
-                # from it (the caller must not overwrite the frame before this integrate has finished)
-                self._frame_dev[:3].copy_(src[:3], non_blocking=True)
-                self._frame_dev[3].copy_(src[-1], non_blocking=True)
+            if not src.is_pinned():
+                if self._frame_host[j] is None:
+                    self._frame_host[j] = torch.empty((4, H, W), dtype=torch.float32, pin_memory=True)
+                elif self._set_used[j]:
+                    self._h2d_done[j].synchronize()       # the DMA of two frames ago has left this staging buffer
+                self._frame_host[j][:3].copy_(src[:3])
+                self._frame_host[j][3].copy_(src[-1])
+                src4 = self._frame_host[j]
             else:
-                if self._h2d_done is not None:
-                    self._h2d_done.synchronize()     # the previous frame's DMA must have left the staging buffer
-                self._frame_host[:3].copy_(src[:3])
-                self._frame_host[3].copy_(src[-1])
-                self._frame_dev.copy_(self._frame_host, non_blocking=True)
-                if self._h2d_done is None:
-                    self._h2d_done = torch.cuda.Event()
-                self._h2d_done.record(torch.cuda.current_stream(self.device))
-        self.h2d_bytes_last_frame = self._frame_dev.numel() * 4
-        _capi.check(self._lib.ofx_pack_frame(_capi.ptr(self._frame_dev), 4, H, W, _capi.ptr(self._color_im_dev),
+                src4 = None
+            cs = self._copy_stream
+            if self._set_used[j]:
+                cs.wait_event(self._set_done[j])          # the kernels of two frames ago are done with this set
+            with torch.cuda.stream(cs):
+                if src4 is not None:
+                    fd.copy_(src4, non_blocking=True)
+                else:
+                    fd[:3].copy_(src[:3], non_blocking=True)
+                    fd[3].copy_(src[-1], non_blocking=True)
+                self._h2d_done[j].record(cs)
+            comp.wait_event(self._h2d_done[j])
+        self.h2d_bytes_last_frame = fd.numel() * 4
+        self._color_im_dev, self._depth_im_dev, self._stats = self._color_ims[j], self._depth_ims[j], self._stats_sets[j]
+        _capi.check(self._lib.ofx_pack_frame(_capi.ptr(fd), 4, H, W, _capi.ptr(self._color_im_dev),
                                              _capi.ptr(self._depth_im_dev), _capi.stream_ptr(self.device)))
         self.im = im
         if hasattr(self, "frame_id"):                                        # tsdf.py:569-570
             assert self.frame_id + self.fopt.skip_rate == frame_id, \
                 f"Updating image data failed. Previous frame:{self.frame_id}, current frame:{frame_id} not integrated."
         self.frame_id = frame_id
+
+    def wait_uploaded(self):
+        """Blocks until the most recent frame has left the caller's (page-locked) buffer."""
+        self._h2d_done[self._set].synchronize()
 
     @property
     def color_im(self):
@@ -199,12 +229,14 @@ class TSDFVolume:
         """Integrate an RGB-D frame into the TSDF volume (tsdf.py:378-494).
 
         image_data: {"im": (6,H,W) float32, "id": int}.  Source frame -> identity warp
-        (tsdf.py:395-398); any other frame is warped by self.warpfield (tsdf.py:401)."""
+        (tsdf.py:395-398); any other frame is warped by self.warpfield (tsdf.py:401).
+        Returns once the work is enqueued; last_stats() (or any read of the volume) waits for it."""
         with torch.cuda.device(self.device):
             self.update(image_data["im"], image_data["id"])
             identity = self.frame_id == self.fopt.source_frame
             H, W = self._depth_im_dev.shape
             S = _capi.stream_ptr(self.device)
+            done = False
             if not identity:
                 wf = self.warpfield
                 assert wf.frame_id == self.frame_id, \
@@ -217,14 +249,32 @@ class TSDFVolume:
                                                                _capi.ptr(self._depth_im_dev), _capi.ptr(self._color_im_dev),
                                                                H, W, self._intr4, float(obs_weight), _capi.ptr(self._stats), S))
                     wf._transforms_dirty = False
-                    return
-            _capi.check(self._lib.ofx_integrate(self._h, _capi.ptr(self._depth_im_dev), _capi.ptr(self._color_im_dev),
-                                                H, W, self._intr4, float(obs_weight), int(identity),
-                                                _capi.ptr(self._stats), S))
+                    done = True
+            if not done:
+                _capi.check(self._lib.ofx_integrate(self._h, _capi.ptr(self._depth_im_dev), _capi.ptr(self._color_im_dev),
+                                                    H, W, self._intr4, float(obs_weight), int(identity),
+                                                    _capi.ptr(self._stats), S))
+            # the frame's counters go to page-locked host memory behind the kernels; nobody waits here
+            j = self._set
+            comp = torch.cuda.current_stream(self.device)
+            self._stats_host[j].copy_(self._stats, non_blocking=True)
+            self._set_done[j].record(comp)
+            self._set_used[j] = True
+            self._stats_ready[j] = self._set_done[j]
 
-    def last_stats(self):
-        """Counters of the last integrate(): dict(updated, skin_valid, bricks, weight_sum). Synchronises."""
-        s = self._stats.cpu().tolist()
+    def last_stats(self, previous=False):
+        """Counters of the last integrate(): dict(updated, skin_valid, bricks, weight_sum); waits for that frame.
+        previous=True: the counters of the frame BEFORE the last one (None when there is none) -- in a frame loop
+        that read never stalls the device, since the last frame is still free to run."""
+        j = 1 - self._set if previous else self._set
+        ev = self._stats_ready[j]
+        if ev is None:
+            if previous:
+                return None
+            s = self._stats.cpu().tolist()
+        else:
+            ev.synchronize()
+            s = self._stats_host[j].tolist()
         return dict(updated=s[_capi.STAT_UPDATED], skin_valid=s[_capi.STAT_SKIN_VALID],
                     bricks=s[_capi.STAT_BRICKS], weight_sum=s[_capi.STAT_WEIGHT_SUM])
 

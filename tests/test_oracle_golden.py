@@ -76,3 +76,27 @@ def test_expf_close_to_libm(oracle):
     y = oracle.expf(x)
     ref = np.exp(x.astype(np.float64))
     assert np.max(np.abs(y - ref) / ref) < 3e-7
+
+
+def test_misc_golden_normals_visibility_and_pickle(oracle):
+    """tests/golden/ref_misc.npz (the reference's own run): the oracle's warp reproduces deform_normals (rotation only,
+    renormalised, warpfield.py:312-345) to 1e-6, its visibility test get_visible_nodes exactly, and the reference-written
+    volume pickle is the (3,Dx,Dy,Dz) float32 stack [tsdf, colour, weight] (tsdf.py:682-687)."""
+    import io
+    import pickle
+    from conftest import load_golden
+    g = load_golden("ref_misc")
+    n = len(g["dn_points"])
+    raw = oracle.warp(g["dn_normals"], g["dn_anchors"], g["dn_weights"], np.ones(n, bool), g["R"], np.zeros_like(g["T"], dtype=np.float32))
+    dn = raw / np.linalg.norm(raw, axis=1, keepdims=True)
+    assert np.abs(dn - g["dn_out"]).max() <= 1e-6
+    _, depth = oracle.pack_frame(g["frames"][1])
+    vis, _ = oracle.check_visibility(g["nodes"] + g["t"], depth, g["intr"], 0.04)
+    assert np.array_equal(vis, g["visible_nodes"])
+    assert np.array_equal(np.load(io.BytesIO(g["visible_nodes_npy"].tobytes())), g["visible_nodes"])
+    assert np.array_equal(np.load(io.BytesIO(g["deformed_nodes_npy"].tobytes())), g["nodes"] + g["t"])
+    data = pickle.loads(g["volume_pickle"].tobytes())
+    assert data.dtype == np.float32 and data.shape == (3,) + tuple(int(d) for d in g["voxel_dim"])
+    assert np.array_equal(data[0], g["tsdf"]) and np.array_equal(data[1], g["colour"]) and np.array_equal(data[2], g["weight"])
+    T = oracle.origin_translations(g["R"], g["t"], g["nodes"])
+    assert np.array_equal(T.astype(g["T"].dtype), g["T"])

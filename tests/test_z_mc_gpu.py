@@ -153,3 +153,56 @@ def test_deformed_model_and_clear(oracle):
     a, wt, valid = oracle.skin(cv, w.nodes, w.K, w.coverage)
     assert np.array_equal(dv, oracle.warp(cv, a, wt, valid, est["node_rotations"], wf.translations))
     assert df is cf and dc is cc and dn.shape == cn.shape and valid.mean() > 0.9
+
+
+def test_fusion_py_call_sequence_against_the_drop_ins(oracle, tmp_path):
+    """The calls DynamicFusion makes on the three classes, in its order and with its argument order
+    (fusion_with_occlusion/fusion.py:57-83 create_tsdf, :176-179 register_frame): TSDFVolume(bbox, max_depth, intrinsics,
+    opt, vis) -> integrate(source_data) -> EDGraph(tsdf, vis, source_data) -> WarpField(graph, tsdf, vis) ->
+    update_transformations(estimated) -> integrate(target_frame_data).  The graph comes from the volume's own mesh and
+    <datadir>/graph_config.json; the warped frames stay bit-identical to the oracle given the same node table."""
+    import json
+    import os
+    import types
+    from occlusionfusion_b200 import EDGraph, TSDFVolume, WarpField
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload("tiny", dim=[64, 64, 96], voxel=0.0125)
+    opt = types.SimpleNamespace(voxel_dim=w.fopt.voxel_dim, source_frame=0, skip_rate=1, datadir=str(tmp_path), gpu=True)
+    vis = None
+    source_data = {"im": w.frame(0), "id": 0, "intrinsics": w.intr}
+    tsdf = TSDFVolume(w.bbox, w.max_depth, source_data["intrinsics"], opt, vis)          # fusion.py:57
+    tsdf.integrate(source_data)                                                           # fusion.py:71
+    graph = EDGraph(tsdf, vis, source_data)                                               # fusion.py:74
+    tsdf.graph = graph                                                                    # fusion.py:76
+    warpfield = WarpField(graph, tsdf, vis)                                               # fusion.py:83
+    tsdf.warpfield = warpfield                                                            # fusion.py:86
+    # what the constructor left behind (embedded_deformation_graph.py:34-52)
+    cfg = json.load(open(os.path.join(str(tmp_path), "graph_config.json")))
+    assert cfg["node_coverage"] == 0.05 and cfg["num_neighbours"] == 8 and graph.graph_generation_parameters == cfg
+    assert os.path.isdir(os.path.join(str(tmp_path), "results", "updated_graph"))
+    assert graph.tsdf is tsdf and tsdf.graph is graph
+    M = graph.nodes.shape[0]
+    assert M > 20 and graph.nodes.dtype == np.float32 and graph.edges.shape == (M, 8) and "nn_index_l3" in graph.pyd
+    # nodes lie on the surface mesh, node_coverage apart
+    verts = tsdf.get_canonical_model()[0]
+    assert np.array_equal(graph.nodes, verts[graph.node_indices.reshape(-1)])
+    d = np.linalg.norm(graph.nodes[:, None] - graph.nodes[None], axis=2) + 10 * np.eye(M)
+    assert d.min() > 0.05
+    # a graph_config.json that is already there is read, not overwritten
+    cfg["node_coverage"] = 0.08
+    json.dump(cfg, open(os.path.join(str(tmp_path), "graph_config.json"), "w"))
+    assert EDGraph(tsdf, vis, source_data).nodes.shape[0] < M
+    tsdf.graph = graph
+    # registered frames (fusion.py:176-179)
+    ov = oracle.OracleVolume(w.dims, w.origin, w.voxel_size, w.intr, w.trunc)
+    ov.integrate(w.frame(0), True)
+    ov.set_graph(graph.nodes, warpfield.node_coverage, warpfield.graph_neighbours)
+    for f in (1, 2):
+        estimated_transformations = w.estimate(f, graph.nodes)
+        warpfield.update_transformations(estimated_transformations)                       # fusion.py:176
+        target_frame_data = {"im": w.frame(f), "id": f, "intrinsics": w.intr}
+        tsdf.integrate(target_frame_data)                                                 # fusion.py:179
+        ov.set_transforms(estimated_transformations["node_rotations"], warpfield.translations)
+        assert tsdf.last_stats()["updated"] == ov.integrate(w.frame(f), False) > 0
+    t, c, wt = tsdf.get_volume()
+    assert np.array_equal(wt, ov.weight) and np.array_equal(c, ov.colour) and np.array_equal(t, ov.tsdf)
