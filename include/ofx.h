@@ -206,6 +206,38 @@ int ofx_mc_emit(const float *vol, const uint8_t *mask, int32_t Dx, int32_t Dy, i
 int ofx_mc_vertices(const float *vol, const float *colour, int32_t Dx, int32_t Dy, int32_t Dz, float level,
                     const int64_t *keys, int64_t n, float *verts, float *normals, uint8_t *rgb, void *stream);
 
+/* ---- the edge half of the graph builder on the device ---------------------------------------------------------
+ * compute_edges_geodesic (csrc/cpu/graph_proc.cpp:155-300, binding csrc/main.cpp:30; callers
+ * embedded_deformation_graph.py:226-233, 313-320, 575-582): for every node (node_idx: its mesh vertex, < 0 = skip) the
+ * first max_neighbours OTHER nodes in order of geodesic distance over the mesh.  DEVICE pointers: verts (V,3) f32, valid
+ * (V,) u8 (may be NULL unless only_valid), faces (F,3) i32, node_idx (M,) i32; outputs edges (M, max_neighbours) i32 and
+ * distances (same shape, f32) are filled for the neighbours found (pre-fill -1 / 0 as the reference's callers do),
+ * n_found (M,) i32 their number.  enforce_total == 0 limits the walk to 2 * node_coverage.  Identical to the reference's
+ * search, ties included (nodes whose answer depends on the order of equal distances are replayed with the reference's
+ * heap, step by step).  Synchronises the stream.  status_host (2 ints, may be NULL): [0] 0 = ok, [1] nodes replayed.
+ * The edge WEIGHTS follow from the distances on the host: ofx_edge_weights_host. */
+int ofx_compute_edges_geodesic(const float *verts, const uint8_t *valid, int32_t V, const int32_t *faces, int32_t F,
+                               const int32_t *node_idx, int32_t M, int32_t max_neighbours, float node_coverage,
+                               int32_t *edges, float *distances, int32_t *n_found, int32_t only_valid,
+                               int32_t enforce_total, int32_t *status_host, void *stream);
+/* exp(-d^2 / (2 c^2)) normalised per node (graph_proc.cpp:150-152, 281-296) from the distances above: HOST arrays (the
+ * reference's weights go through the C library's expf; so do these). */
+int ofx_edge_weights_host(const float *distances_host, const int32_t *n_found_host, int32_t M, int32_t E,
+                          float node_coverage, float *weights_host);
+/* node_and_edge_clean_up (graph_proc.cpp:388-438, binding main.cpp:32) on DEVICE arrays: clears valid_mask (M,) u8 of every
+ * node left with at most one neighbour, repeatedly (the fixed point does not depend on the sweep order). */
+int ofx_node_and_edge_clean_up(const int32_t *edges, int32_t M, int32_t E, uint8_t *valid_mask, void *stream);
+/* compute_clusters (graph_proc.cpp:440-481, binding main.cpp:33) on DEVICE arrays: connected components of the undirected
+ * edge set, numbered by their smallest node; clusters (M,) i32, sizes (M,) i32 (first *n_clusters entries), *n_clusters
+ * (device).  Synchronises the stream (error check). */
+int ofx_compute_clusters(const int32_t *edges, int32_t M, int32_t E, int32_t *clusters, int32_t *sizes,
+                         int32_t *n_clusters, void *stream);
+/* up_sample_idx of one pyramid level (embedded_deformation_graph.py:279-298) on DEVICE arrays: for every node the position,
+ * within down_idx (the kept nodes, ascending: ofx_greedy_insert over the nodes in index order), of the nearest node kept
+ * before it. */
+int ofx_upsample_index(const float *nodes, int32_t M, const int32_t *down_idx, int32_t n_down, int32_t *up_idx,
+                       void *stream);
+
 /* ---- host half of the graph builder (HOST pointers; no device work) ------------------------------------------ */
 /* compute_edges_geodesic (csrc/cpu/graph_proc.cpp:155-300, binding csrc/main.cpp:30; callers
  * embedded_deformation_graph.py:226-233, 313-320): for every node (node_idx: its mesh vertex, < 0 = skip) walk the mesh

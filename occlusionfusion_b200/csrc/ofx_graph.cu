@@ -53,6 +53,8 @@ static int scratch_alloc(void **p, size_t bytes, cudaStream_t s)
     return 0;
 }
 
+int graph_scratch_alloc(void **p, size_t bytes, cudaStream_t s) { return scratch_alloc(p, bytes, s); }   // for ofx_graph_edges.cu
+
 // largest float a with (double)a <= x: for every float v, ((double)v > x) == (v > a)
 static float float_at_most(double x)
 {

@@ -308,8 +308,8 @@ static int launch_brick(ofx_volume *v, int grid, const GraphArgs &ga, const Fram
 #define OFX_PDL 1
 #endif
 #ifndef OFX_PDL_SHARDS
-#define OFX_PDL_SHARDS 0      // shards of a multi-GPU volume: measured slower with it in round 1
-#endif
+#define OFX_PDL_SHARDS 1      // shards of a multi-GPU volume too: 0.0903 vs 0.0915 ms/frame on 8 B200 (round 2; in round 1, with a
+#endif                        // separate node-transform kernel in front, it was slower: DESIGN.md section 6)
 struct PdlLaunch {
     cudaLaunchAttribute attr;
     cudaLaunchConfig_t cfg;

@@ -20,7 +20,8 @@ import numpy as np
 import torch
 
 from . import _capi
-from .graph_proc import compute_clusters_c, compute_edges_geodesic_c, downsample_nodes, node_and_edge_clean_up_c
+from .graph_proc import (DeviceMesh, compute_clusters_d, compute_edges_geodesic_d, downsample_nodes_d,
+                         node_and_edge_clean_up_d)
 
 DEFAULT_GRAPH_PARAMETERS = {           # embedded_deformation_graph.py:62-73
     "max_triangle_distance": 0.05,
@@ -118,8 +119,9 @@ class EDGraph:
         graph_edges_weights = np.zeros((num_nodes, num_neighbours), dtype=np.float32)
         graph_edges_distances = np.zeros((num_nodes, num_neighbours), dtype=np.float32)
         # node_to_vertex_distances (num_nodes x num_vertices) is only scratch in the reference (:221, 247): not materialised
-        compute_edges_geodesic_c(vertices, np.ones_like(valid_vertices), faces, node_indices, num_neighbours, node_coverage,
-                                 graph_edges, graph_edges_weights, graph_edges_distances, None, True, True)   # :224-233
+        self._mesh = DeviceMesh(vertices, faces, np.ones_like(valid_vertices), self.device)   # uploaded once, reused by the pyramid
+        compute_edges_geodesic_d(self._mesh, node_indices, num_neighbours, node_coverage, graph_edges, graph_edges_weights,
+                                 graph_edges_distances, True, True)                           # :224-233
         self.vertices, self.faces = vertices, faces
         self.nodes, self.node_indices = node_coords, node_indices
         self.edges, self.edges_weights, self.edges_distances = graph_edges, graph_edges_weights, graph_edges_distances
@@ -132,7 +134,7 @@ class EDGraph:
         """embedded_deformation_graph.py:334-368: nodes left with at most one neighbour go (repeatedly), the others are
         renumbered."""
         valid_nodes_mask = np.ones((self.nodes.shape[0], 1), dtype=bool)
-        node_and_edge_clean_up_c(self.edges, valid_nodes_mask)
+        node_and_edge_clean_up_d(self.edges, valid_nodes_mask, self.device)
         reduced = self.get_reduced_graph(valid_nodes_mask)
         self.nodes = reduced["valid_nodes_at_source"]
         self.edges = reduced["graph_edges"]
@@ -143,7 +145,7 @@ class EDGraph:
 
     def compute_clusters(self):
         """Connected components of the node graph into self.clusters (embedded_deformation_graph.py:371-380)."""
-        clusters_size_list = compute_clusters_c(self.edges, self.clusters)
+        clusters_size_list = compute_clusters_d(self.edges, self.clusters, self.device)
         for i, cluster_size in enumerate(clusters_size_list):
             if cluster_size <= 2:
                 self.log.error(f"Cluster is too small {clusters_size_list}")
@@ -192,18 +194,20 @@ class EDGraph:
         num_neighbours_list = [8, 6, 4, 3]
         pyd = {"nn_index_l0": self.edges}
         old_nodes, level_node_indices = self.nodes, self.node_indices
-        V = self.vertices.shape[0]
+        mesh = getattr(self, "_mesh", None)
+        if mesh is None or mesh.V != self.vertices.shape[0] or mesh.F != np.shape(self.faces)[0]:
+            mesh = self._mesh = DeviceMesh(self.vertices, self.faces, np.ones(self.vertices.shape[0], dtype=bool), self.device)
         for level in range(1, 4):
             node_coverage = node_coverage * 2
-            down_sample_idx, up_sample_idx = downsample_nodes(old_nodes, node_coverage)      # :279-298, native host loop
+            down_sample_idx, up_sample_idx = downsample_nodes_d(old_nodes, node_coverage, self.device)   # :279-298, on the device
             E = num_neighbours_list[level]
             level_node_indices = level_node_indices[down_sample_idx]
             n = level_node_indices.shape[0]
             graph_edges = -np.ones((n, E), dtype=np.int32)
             graph_edges_weights = np.zeros((n, E), dtype=np.float32)
             graph_edges_distances = np.zeros((n, E), dtype=np.float32)
-            compute_edges_geodesic_c(self.vertices, np.ones(V, dtype=bool), self.faces, level_node_indices, E, node_coverage,
-                                     graph_edges, graph_edges_weights, graph_edges_distances, None, False, True)   # :313-320
+            compute_edges_geodesic_d(mesh, level_node_indices, E, node_coverage, graph_edges, graph_edges_weights,
+                                     graph_edges_distances, False, True)                      # :313-320
             pyd["down_sample_idx" + str(level)] = down_sample_idx
             pyd["up_sample_idx" + str(level)] = up_sample_idx
             pyd["nn_index_l" + str(level)] = graph_edges
@@ -299,9 +303,9 @@ class EDGraph:
         graph_edges = -np.ones((num_nodes, num_neighbours), dtype=np.int32)
         graph_edges_weights = np.zeros((num_nodes, num_neighbours), dtype=np.float32)
         graph_edges_distances = np.zeros((num_nodes, num_neighbours), dtype=np.float32)
-        compute_edges_geodesic_c(verts_np, np.ones(verts_np.shape[0], dtype=bool), canonical_model_faces, self.node_indices,
-                                 num_neighbours, node_coverage, graph_edges, graph_edges_weights, graph_edges_distances, None,
-                                 True, True)                                                     # :575-582
+        self._mesh = DeviceMesh(verts_np, canonical_model_faces, np.ones(verts_np.shape[0], dtype=bool), dev)
+        compute_edges_geodesic_d(self._mesh, self.node_indices, num_neighbours, node_coverage, graph_edges, graph_edges_weights,
+                                 graph_edges_distances, True, True)                              # :575-582
         self.vertices, self.faces = canonical_model_vertices, canonical_model_faces
         self.edges, self.edges_weights, self.edges_distances = graph_edges, graph_edges_weights, graph_edges_distances
         self.clusters = -np.ones((num_nodes, 1), dtype=np.int32)

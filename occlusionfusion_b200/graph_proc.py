@@ -92,3 +92,124 @@ def compute_pixel_anchors_euclidean_c(graph_nodes, point_image, node_coverage, p
         _inplace(dst, dt, "pixel_anchors / pixel_weights")
         dst.resize((H, W, 4), refcheck=False)
         dst[...] = src.cpu().numpy()
+
+
+# ---- the same four on the DEVICE (ofx_graph_edges.cu): what EDGraph uses ---------------------------------------------------
+class DeviceMesh:
+    """A mesh's vertices / faces (and optional vertex mask) uploaded once and reused by the edge builder of every pyramid
+    level (embedded_deformation_graph.py:226-233, 313-320: four searches over the same mesh)."""
+
+    def __init__(self, vertices, faces, valid_vertices=None, device=None):
+        import torch
+        _capi.require_cuda()
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else device
+        self.verts = _capi.to_device(np.ascontiguousarray(vertices, dtype=np.float32), torch.float32, self.device).reshape(-1, 3)
+        self.faces = _capi.to_device(np.ascontiguousarray(faces, dtype=np.int32), torch.int32, self.device).reshape(-1, 3)
+        self.valid = None if valid_vertices is None else \
+            _capi.to_device(np.ascontiguousarray(np.asarray(valid_vertices).reshape(-1), dtype=np.uint8), torch.uint8, self.device)
+        self.V, self.F = int(self.verts.shape[0]), int(self.faces.shape[0])
+
+
+def compute_edges_geodesic_d(mesh, node_indices, num_neighbours, node_coverage, graph_edges, graph_edges_weights,
+                             graph_edges_distances, allow_only_valid_vertices, enforce_total_num_neighbors):
+    """compute_edges_geodesic (graph_proc.cpp:155-300) on the device: `mesh` is a DeviceMesh; graph_edges (M,E) i32 /
+    weights / distances (M,E) f32 are filled in place for the neighbours found (pre-filled by the caller, as in the reference).
+    Returns the number of nodes whose answer depended on equal distances (replayed with the reference's heap)."""
+    import torch
+    ni = np.ascontiguousarray(node_indices, dtype=np.int32).reshape(-1)
+    M, E = len(ni), int(num_neighbours)
+    e = _inplace(graph_edges, np.int32, "graph_edges")
+    w = _inplace(graph_edges_weights, np.float32, "graph_edges_weights")
+    d = _inplace(graph_edges_distances, np.float32, "graph_edges_distances")
+    assert e.shape == (M, E) and w.shape == (M, E) and d.shape == (M, E)
+    if M == 0:
+        return 0
+    if ni.max(initial=-1) >= mesh.V:
+        raise _capi.OfxError(f"compute_edges_geodesic: node vertex {int(ni.max())} out of range")
+    dev = mesh.device
+    with torch.cuda.device(dev):
+        ni_d = torch.from_numpy(ni).to(dev)
+        e_d = torch.from_numpy(e).to(dev)
+        d_d = torch.from_numpy(d).to(dev)
+        n_d = torch.zeros(M, dtype=torch.int32, device=dev)
+        status = (C.c_int32 * 2)()
+        only_valid = int(bool(allow_only_valid_vertices))
+        if only_valid and mesh.valid is None:
+            raise _capi.OfxError("compute_edges_geodesic: allow_only_valid_vertices needs the vertex mask")
+        _capi.check(_capi.load().ofx_compute_edges_geodesic(_capi.ptr(mesh.verts), _capi.ptr(mesh.valid), mesh.V, _capi.ptr(mesh.faces),
+                                                            mesh.F, _capi.ptr(ni_d), M, E, C.c_float(node_coverage), _capi.ptr(e_d),
+                                                            _capi.ptr(d_d), _capi.ptr(n_d), only_valid,
+                                                            int(bool(enforce_total_num_neighbors)), status,
+                                                            _capi.stream_ptr(dev)))
+        e[...] = e_d.cpu().numpy()
+        d[...] = d_d.cpu().numpy()
+        found = n_d.cpu().numpy()
+    _capi.check(_capi.load().ofx_edge_weights_host(_p(d), _p(found), M, E, C.c_float(node_coverage), _p(w)))
+    return int(status[1])
+
+
+def node_and_edge_clean_up_d(graph_edges, valid_nodes_mask, device=None):
+    """node_and_edge_clean_up (graph_proc.cpp:388-438) on the device; valid_nodes_mask (M,1) bool is updated in place."""
+    import torch
+    _capi.require_cuda()
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else device
+    e = np.ascontiguousarray(graph_edges, dtype=np.int32)
+    m = _inplace(valid_nodes_mask, np.bool_, "valid_nodes_mask")
+    assert e.ndim == 2 and m.size == e.shape[0]
+    if e.shape[0] == 0:
+        return
+    with torch.cuda.device(dev):
+        e_d = torch.from_numpy(e).to(dev)
+        m_d = torch.from_numpy(m.view(np.uint8).reshape(-1).copy()).to(dev)
+        _capi.check(_capi.load().ofx_node_and_edge_clean_up(_capi.ptr(e_d), e.shape[0], e.shape[1], _capi.ptr(m_d),
+                                                            _capi.stream_ptr(dev)))
+        m.reshape(-1)[...] = m_d.cpu().numpy().astype(bool)
+
+
+def compute_clusters_d(graph_edges, graph_clusters, device=None):
+    """compute_clusters (graph_proc.cpp:440-481) on the device; graph_clusters (M,1) i32 is filled in place; returns the
+    list of cluster sizes."""
+    import torch
+    _capi.require_cuda()
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else device
+    e = np.ascontiguousarray(graph_edges, dtype=np.int32)
+    c = _inplace(graph_clusters, np.int32, "graph_clusters")
+    assert e.ndim == 2 and c.size == e.shape[0]
+    M = e.shape[0]
+    if M == 0:
+        return []
+    with torch.cuda.device(dev):
+        e_d = torch.from_numpy(e).to(dev)
+        c_d = torch.empty(M, dtype=torch.int32, device=dev)
+        s_d = torch.empty(M, dtype=torch.int32, device=dev)
+        n_d = torch.zeros(1, dtype=torch.int32, device=dev)
+        _capi.check(_capi.load().ofx_compute_clusters(_capi.ptr(e_d), M, e.shape[1], _capi.ptr(c_d), _capi.ptr(s_d), _capi.ptr(n_d),
+                                                      _capi.stream_ptr(dev)))
+        c.reshape(-1)[...] = c_d.cpu().numpy()
+        return s_d[: int(n_d.item())].cpu().numpy().tolist()
+
+
+def downsample_nodes_d(nodes, node_coverage, device=None):
+    """One pyramid level (embedded_deformation_graph.py:279-298) on the device: the greedy rule is ofx_greedy_insert over the
+    nodes in index order (no existing nodes), up_sample_idx is ofx_upsample_index.  Returns (down_sample_idx, up_sample_idx)
+    as Python lists."""
+    import torch
+    _capi.require_cuda()
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else device
+    nd = np.ascontiguousarray(nodes, dtype=np.float32).reshape(-1, 3)
+    M = len(nd)
+    if M == 0:
+        return [], []
+    lib = _capi.load()
+    with torch.cuda.device(dev):
+        nd_d = torch.from_numpy(nd).to(dev)
+        cand = torch.arange(M, dtype=torch.int32, device=dev)
+        acc = torch.empty(M, dtype=torch.int32, device=dev)
+        n_d = torch.zeros(1, dtype=torch.int32, device=dev)
+        S = _capi.stream_ptr(dev)
+        _capi.check(lib.ofx_greedy_insert(_capi.ptr(nd_d), M, _capi.ptr(cand), M, None, 0, float(node_coverage), _capi.ptr(acc),
+                                          _capi.ptr(n_d), S))
+        k = int(n_d.item())
+        up = torch.empty(M, dtype=torch.int32, device=dev)
+        _capi.check(lib.ofx_upsample_index(_capi.ptr(nd_d), M, _capi.ptr(acc), k, _capi.ptr(up), S))
+        return acc[:k].cpu().numpy().tolist(), up.cpu().numpy().tolist()

@@ -85,9 +85,11 @@ def test_graph_host_argument_errors(gg):
         compute_edges_geodesic_c(v, valid, gg["mesh_faces"], np.array([3, 9], np.int32), 4, 0.05, e, w, d, None, True, True)
 
 
+@pytest.mark.gpu
 def test_reduced_graph_clusters_and_pyramid_match_reference(gg):
     """remove_nodes_with_not_enough_neighbours / get_reduced_graph / compute_clusters / create_graph_pyramid
-    (embedded_deformation_graph.py:261-480) against the reference's own Python + C++ run on the same hand-filled graph."""
+    (embedded_deformation_graph.py:261-480) against the reference's own Python + C++ run on the same hand-filled graph.
+    (EDGraph runs these on the device: ofx_graph_edges.cu.)"""
     from occlusionfusion_b200 import EDGraph
     g = EDGraph(nodes=gg["sample_pos_1"].copy(), graph_generation_parameters={"node_coverage": float(gg["coverage"])})
     g.vertices, g.faces = gg["mesh_verts"], gg["mesh_faces"]

@@ -1,11 +1,12 @@
-"""Investigation only: one GPU plays shard 0 of N (c2-dense) and reports the per-frame device times of the
-node-transform kernel, the cull and the fused kernel, plus (OFX_TIMING build) the per-CTA timeline.
-  tools/shard_probe.py N [name of an OFX_TIMING build]"""
+"""Investigation only: one GPU plays shard 0 of N (c2-dense by default) and reports the per-frame device time of the
+per-frame launch sequence (frame preparation + node transforms, brick cull, fused kernel) and, with an OFX_TIMING build,
+the per-CTA timeline of the fused kernel.
+  tools/shard_probe.py N [name of an OFX_TIMING build: libofx_<name>.so]"""
 import ctypes, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 N = int(sys.argv[1]) if len(sys.argv) > 1 else 8
-timing = len(sys.argv) > 2          # name of an OFX_TIMING build: libofx_<name>.so
+timing = len(sys.argv) > 2
 if timing:
     os.environ["OFX_LIB"] = os.path.join(ROOT, "occlusionfusion_b200", "lib", f"libofx_{sys.argv[2]}.so")
 import numpy as np
@@ -28,29 +29,29 @@ for i in range(1, 5):
     T = (-np.einsum("nij,nj->ni", e["node_rotations"], w.nodes) + w.nodes + e["node_translations"]).astype(np.float32)
     colour, depth = be.pack_frame(w.frame(i))
     frames.append((torch.from_numpy(e["node_rotations"]).to(dev).contiguous(), torch.from_numpy(T).to(dev), depth.clone(), colour.clone()))
-ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
-tt, ti = [], []
+flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+ti = []
 for s in range(24):
     R, T, depth, colour = frames[s % 4]
+    if os.environ.get("FLUSH", "1") == "1":
+        flush.fill_(s & 0xFF)
     ev[0].record()
-    be.set_transforms(R, T)
+    st = be.integrate_warped(R, T, depth, colour, 1.0)
     ev[1].record()
-    st = be.integrate(depth, colour, False, 1.0)
-    ev[2].record()
     torch.cuda.synchronize()
     if s >= 4:
-        tt.append(ev[0].elapsed_time(ev[1])); ti.append(ev[1].elapsed_time(ev[2]))
-print(f"shard 0 of {N}: transforms {np.median(tt) * 1e3:.1f} us, cull+fused {np.median(ti) * 1e3:.1f} us, stats {st.tolist()}")
+        ti.append(ev[0].elapsed_time(ev[1]))
+print(f"shard 0 of {N} ({w.name}): prep+cull+fused {np.median(ti) * 1e3:.1f} us (min {np.min(ti) * 1e3:.1f}), stats {st.tolist()}")
 if timing:
     L = _capi.load()
-    buf = (ctypes.c_ulonglong * 4096)()
+    buf = (ctypes.c_ulonglong * (2048 * 8))()
     L.ofx_debug_cta(buf)
-    a = np.array(list(buf), dtype=np.int64).reshape(1024, 4)
+    a = np.array(list(buf), dtype=np.int64).reshape(2048, 8)
     a = a[a[:, 0] > 0]
     t0 = a[:, 0].min()
-    print("CTAs", len(a), "kernel span us", (a[:, 2].max() - t0) / 1e3)
-    print("entry  us: min %.1f med %.1f max %.1f" % tuple(np.percentile((a[:, 0] - t0) / 1e3, [0, 50, 100])))
-    print("first data us after entry: min %.1f med %.1f max %.1f" % tuple(np.percentile((a[:, 1] - a[:, 0]) / 1e3, [0, 50, 100])))
-    print("end    us: min %.1f p10 %.1f med %.1f p90 %.1f max %.1f" % tuple(np.percentile((a[:, 2] - t0) / 1e3, [0, 10, 50, 90, 100])))
-    print("bricks per CTA: min %d med %d max %d" % tuple(np.percentile(a[:, 3], [0, 50, 100])))
-    print("us per brick per CTA: min %.2f med %.2f max %.2f" % tuple(np.percentile((a[:, 2] - a[:, 1]) / 1e3 / np.maximum(a[:, 3], 1), [0, 50, 100])))
+    pc = lambda x: "min %.1f med %.1f p90 %.1f max %.1f" % tuple(np.percentile(x, [0, 50, 90, 100]))
+    print(f"  CTAs {len(a)}; fused kernel span {(a[:, 5].max() - t0) / 1e3:.1f} us")
+    print("  entry (us after first entry):        ", pc((a[:, 0] - t0) / 1e3))
+    print("  first data landed (after the wait):  ", pc((a[:, 2] - a[:, 1]) / 1e3))
+    print("  consumer exit (us after first entry):", pc((a[:, 5] - t0) / 1e3))
