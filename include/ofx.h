@@ -220,6 +220,15 @@ int ofx_compute_edges_geodesic(const float *verts, const uint8_t *valid, int32_t
                                const int32_t *node_idx, int32_t M, int32_t max_neighbours, float node_coverage,
                                int32_t *edges, float *distances, int32_t *n_found, int32_t only_valid,
                                int32_t enforce_total, int32_t *status_host, void *stream);
+/* The same for several searches over ONE mesh in one launch (the levels of EDGraph.create_graph_pyramid,
+ * embedded_deformation_graph.py:300-320: their node sets, neighbour counts and radii differ, the mesh does not): job j owns
+ * job_count_host[j] consecutive entries of node_idx and the next job_count_host[j] * job_neighbours_host[j] entries of edges /
+ * distances; job_flags_host[j]: bit 0 = only_valid, bit 1 = enforce_total.  At most 8 jobs. */
+int ofx_compute_edges_geodesic_batch(const float *verts, const uint8_t *valid, int32_t V, const int32_t *faces, int32_t F,
+                                     const int32_t *node_idx, int32_t n_jobs, const int32_t *job_count_host,
+                                     const int32_t *job_neighbours_host, const float *job_coverage_host,
+                                     const int32_t *job_flags_host, int32_t *edges, float *distances, int32_t *n_found,
+                                     int32_t *status_host, void *stream);
 /* exp(-d^2 / (2 c^2)) normalised per node (graph_proc.cpp:150-152, 281-296) from the distances above: HOST arrays (the
  * reference's weights go through the C library's expf; so do these). */
 int ofx_edge_weights_host(const float *distances_host, const int32_t *n_found_host, int32_t M, int32_t E,

@@ -105,6 +105,40 @@ __global__ void __launch_bounds__(256) nearest_node_kernel(const float *__restri
     }
 }
 
+// np.argmin(np.linalg.norm(points - q, axis=1)) for FEW queries against MANY points (EDGraph.update re-anchors a few hundred
+// nodes on a mesh of 10^4..10^6 vertices): one CTA per query, the threads stride over the points, (norm, index) pairs are
+// reduced keeping the first index among equal norms.  (One thread per query took 1.1 ms for 381 x 14.5 k.)
+__global__ void __launch_bounds__(256) argmin_norm_wide_kernel(const float *__restrict__ queries, const float *__restrict__ pts, int M,
+                                                               float *__restrict__ dist, int32_t *__restrict__ idx)
+{
+    __shared__ float s_d[8];
+    __shared__ int s_i[8];
+    const int q = blockIdx.x;
+    const float qx = __ldg(queries + 3 * q), qy = __ldg(queries + 3 * q + 1), qz = __ldg(queries + 3 * q + 2);
+    float best = __int_as_float(0x7f800000);
+    int bi = 0x7fffffff;
+    for (int j = threadIdx.x; j < M; j += blockDim.x) {
+        const float d = sqrtf(dist2(qx, qy, qz, __ldg(pts + 3 * (int64_t)j), __ldg(pts + 3 * (int64_t)j + 1), __ldg(pts + 3 * (int64_t)j + 2)));
+        if (d < best) { best = d; bi = j; }              // ascending j per thread: the first index among equal norms
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float od = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (od < best || (od == best && oi < bi)) { best = od; bi = oi; }
+    }
+    if ((threadIdx.x & 31) == 0) { s_d[threadIdx.x >> 5] = best; s_i[threadIdx.x >> 5] = bi; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w)
+            if (s_d[w] < best || (s_d[w] == best && s_i[w] < bi)) { best = s_d[w]; bi = s_i[w]; }
+        // (dist2 is the squared distance with numpy's summation order; NaN points never win, as in np.argmin... of a row
+        // without NaN: meshes carry none)
+        if (dist) dist[q] = best;
+        if (idx) idx[q] = bi == 0x7fffffff ? 0 : bi;
+    }
+}
+
 // ---- pixel anchors (Euclidean) -------------------------------------------------------------------------------------
 // compute_pixel_anchors_euclidean (csrc/cpu/graph_proc.cpp:610-709): for every pixel of a (3,H,W) point image with z > 0 the
 // PIXEL_K = 4 nearest nodes by squared distance (Eigen order dx^2 + (dy^2 + dz^2)), kept sorted by insertion with <=, so that
@@ -597,7 +631,10 @@ extern "C" int ofx_argmin_norm(const float *queries, int64_t n, const float *poi
     OFX_REQUIRE(n >= 0 && M >= 1, "ofx_argmin_norm: need n >= 0 and M >= 1 (n=%lld, M=%d)", (long long)n, M);
     if (n == 0) return 0;
     OFX_REQUIRE(queries && points && (dist || idx), "ofx_argmin_norm: null pointer");
-    nearest_node_kernel<true><<<graph_grid_for(n, 64, 16), 64, 0, (cudaStream_t)stream>>>(queries, n, points, M, dist, idx);
+    if (n <= 16384 && M >= 2048)
+        argmin_norm_wide_kernel<<<(int)n, 256, 0, (cudaStream_t)stream>>>(queries, points, M, dist, idx);
+    else
+        nearest_node_kernel<true><<<graph_grid_for(n, 64, 16), 64, 0, (cudaStream_t)stream>>>(queries, n, points, M, dist, idx);
     OFX_LAUNCH_CHECK();
     return 0;
 }

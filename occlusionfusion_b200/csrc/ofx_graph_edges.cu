@@ -153,11 +153,11 @@ __global__ void adj_sort_unique_kernel(int V, const int *__restrict__ off, int *
     cnt[v] = m;
 }
 
-__global__ void vertex_node_kernel(const int *__restrict__ node_idx, int M, int *__restrict__ vertex_node)
+__global__ void vertex_node_kernel(const int *__restrict__ node_idx, int first, int count, int *__restrict__ vertex_node)
 {
     // mapVertexToNode (graph_proc.cpp:192-199): the LAST node that names a vertex wins -> atomicMax of the node id
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
-    if (n < M && node_idx[n] >= 0) atomicMax(vertex_node + node_idx[n], n);
+    if (n < count && node_idx[first + n] >= 0) atomicMax(vertex_node + node_idx[first + n], n);
 }
 
 __device__ __forceinline__ float edge_length(const float *__restrict__ verts, int a, int b)
@@ -166,49 +166,86 @@ __device__ __forceinline__ float edge_length(const float *__restrict__ verts, in
     return sqrtf((dx * dx) + ((dy * dy) + (dz * dz)));          // Eigen's unrolled (a - b).norm()
 }
 
+// One launch serves several searches over the same mesh (the pyramid levels of create_graph_pyramid: different node
+// sets, neighbour counts and radii): a job = a run of consecutive entries of node_idx with its own parameters.
+constexpr int GEO_MAX_JOBS = 8;
+struct GeoJob {
+    int first, count;      // nodes [first, first + count) of the concatenated node list
+    int E;                 // neighbours wanted
+    int only_valid, enforce_total;
+    float coverage, max_influence;
+    int out_off;           // offset of the job's (count, E) block in edges / dists
+};
 struct GeoArgs {
     const float *verts;
     const uint8_t *valid;
-    const int *off, *cnt, *adj, *vertex_node, *node_idx;
-    int V, M, E;
-    float coverage, max_influence;
-    int only_valid, enforce_total;
-    int *edges;            // (M, E), pre-filled by the caller
-    float *dists;          // (M, E)
+    const int *off, *cnt, *adj, *vertex_node, *node_idx;   // vertex_node: one map of V entries per job
+    int V, M, n_jobs;
+    GeoJob jobs[GEO_MAX_JOBS];
+    int *edges;            // per job (count, E), pre-filled by the caller
+    float *dists;          // same shape
     int *n_found;          // (M,)
     uint8_t *need_exact;   // (M,) 1 = a tie touches the answer: redo with geodesic_exact_kernel
     int *error;            // [0]: vertex reached although not valid (+1), 0 = none
     // per-CTA scratch, V entries each
     int *dist_bits;        // initialised to INF_BITS, restored after every node
     int *lists;            // 4 lists: touched, frontier A, frontier B, deferred
-    int *flags;            // per vertex: bit 0 = queued in a frontier list, bit 1 = in the deferred list
+    unsigned *flags;       // per vertex two bits, 16 vertices per word: queued in a frontier list / in the deferred list
 };
 
 constexpr int GEO_THREADS = 256;
 constexpr int GEO_CAND_CAP = 1024;
 
+__device__ __forceinline__ int job_of(const GeoArgs &g, int node)
+{
+    int j = 0;
+    while (j + 1 < g.n_jobs && node >= g.jobs[j + 1].first) ++j;
+    return j;
+}
+
+__device__ __forceinline__ unsigned flag_test_and_set(unsigned *w, int v, unsigned bit)
+{
+    const unsigned m = bit << (2 * (v & 15));
+    return atomicOr(w + (v >> 4), m) & m;
+}
+__device__ __forceinline__ void flag_clear(unsigned *w, int v, unsigned bit) { atomicAnd(w + (v >> 4), ~(bit << (2 * (v & 15)))); }
+
+// SMEM: the per-vertex distances and flags of the CTA's search live in shared memory (meshes up to ~52 k vertices: the
+// relaxation is a chain of dependent atomics, 10x faster there than through L2); else in global scratch.
+template <bool SMEM>
 __global__ void __launch_bounds__(GEO_THREADS) geodesic_relax_kernel(GeoArgs g)
 {
+    extern __shared__ int s_geo[];
     __shared__ int s_n_touched, s_n_front, s_n_next, s_n_def, s_n_cand, s_tie;
     __shared__ float s_cd[GEO_CAND_CAP];
     __shared__ int s_cn[GEO_CAND_CAP];
-    int *dist = g.dist_bits + (size_t)blockIdx.x * g.V;
+    const int n_words = (g.V + 15) >> 4;
+    int *dist = SMEM ? s_geo : g.dist_bits + (size_t)blockIdx.x * g.V;
+    unsigned *flag = SMEM ? reinterpret_cast<unsigned *>(s_geo + g.V) : g.flags + (size_t)blockIdx.x * n_words;
     int *touched = g.lists + (size_t)blockIdx.x * 4 * g.V;
     int *front = touched + g.V, *next = front + g.V, *deferred = next + g.V;
-    int *flag = g.flags + (size_t)blockIdx.x * g.V;
     const int tid = threadIdx.x;
+    if (SMEM) {
+        for (int i = tid; i < g.V; i += GEO_THREADS) dist[i] = INF_BITS;
+        for (int i = tid; i < n_words; i += GEO_THREADS) flag[i] = 0u;
+        __syncthreads();
+    }
 
     for (int node = blockIdx.x; node < g.M; node += gridDim.x) {
         const int v0 = g.node_idx[node];
+        const int jb = job_of(g, node);
+        const GeoJob job = g.jobs[jb];
+        const int self = node - job.first;                        // the node's id within its job
+        const int *vnode = g.vertex_node + (size_t)jb * g.V;
         if (tid == 0) { g.need_exact[node] = 0; g.n_found[node] = 0; }
         if (v0 < 0) continue;                                                                 // graph_proc.cpp:215
-        if (g.only_valid && !g.valid[v0]) { if (tid == 0) atomicExch(g.error, v0 + 1); continue; }   // the reference exit(0)s, :233-236
+        if (job.only_valid && !g.valid[v0]) { if (tid == 0) atomicExch(g.error, v0 + 1); continue; }   // the reference exit(0)s, :233-236
         if (tid == 0) {
             dist[v0] = 0;
             touched[0] = v0; front[0] = v0;
             s_n_touched = 1; s_n_front = 1; s_n_next = 0; s_n_def = 0;
         }
-        float T = g.enforce_total ? 2.0f * g.coverage : g.max_influence;
+        float T = job.enforce_total ? 2.0f * job.coverage : job.max_influence;
         __syncthreads();
         for (;;) {
             // ---- relax inside the radius T until nothing changes ----
@@ -216,24 +253,24 @@ __global__ void __launch_bounds__(GEO_THREADS) geodesic_relax_kernel(GeoArgs g)
                 const int nf = s_n_front;
                 for (int i = tid; i < nf; i += GEO_THREADS) {
                     const int u = front[i];
-                    atomicAnd(flag + u, ~1);                                  // leaves the queue BEFORE its distance is read: a later
+                    flag_clear(flag, u, 1u);                                  // leaves the queue BEFORE its distance is read: a later
                     __threadfence_block();                                    // improvement of u queues it again
                     const float du = __int_as_float(*reinterpret_cast<volatile int *>(dist + u));
                     if (du > T) {
-                        if (!(atomicOr(flag + u, 2) & 2)) deferred[atomicAdd(&s_n_def, 1)] = u;
+                        if (!flag_test_and_set(flag, u, 2u)) deferred[atomicAdd(&s_n_def, 1)] = u;
                         continue;
                     }
                     const int o = g.off[u], c = g.cnt[u];
                     for (int k = 0; k < c; ++k) {
                         const int nb = g.adj[o + k];
-                        if (g.only_valid && !g.valid[nb]) continue;                           // :258-261
+                        if (job.only_valid && !g.valid[nb]) continue;                         // :258-261
                         const float nd = du + edge_length(g.verts, u, nb);                    // :264
-                        if (!g.enforce_total && nd > g.max_influence) continue;               // :266-274
+                        if (!job.enforce_total && nd > job.max_influence) continue;           // :266-274
                         const int nbits = __float_as_int(nd);
                         const int old = atomicMin(dist + nb, nbits);
                         if (nbits < old) {
                             if (old == INF_BITS) touched[atomicAdd(&s_n_touched, 1)] = nb;
-                            if (!(atomicOr(flag + nb, 1) & 1)) next[atomicAdd(&s_n_next, 1)] = nb;
+                            if (!flag_test_and_set(flag, nb, 1u)) next[atomicAdd(&s_n_next, 1)] = nb;
                         }
                     }
                 }
@@ -248,15 +285,15 @@ __global__ void __launch_bounds__(GEO_THREADS) geodesic_relax_kernel(GeoArgs g)
             const int nt = s_n_touched;
             for (int i = tid; i < nt; i += GEO_THREADS) {
                 const int v = touched[i];
-                const int other = g.vertex_node[v];
+                const int other = vnode[v];
                 const float d = __int_as_float(dist[v]);
-                if (other >= 0 && other != node && d <= T) {                                  // :239
+                if (other >= 0 && other != self && d <= T) {                                  // :239
                     const int j = atomicAdd(&s_n_cand, 1);
                     if (j < GEO_CAND_CAP) { s_cd[j] = d; s_cn[j] = other; }
                 }
             }
             __syncthreads();
-            const bool done = !g.enforce_total || s_n_cand >= g.E || s_n_def == 0;
+            const bool done = !job.enforce_total || s_n_cand >= job.E || s_n_def == 0;
             if (done) break;
             // not enough nodes yet: widen the radius; the vertices that waited outside it go back to work
             T *= 1.7f;
@@ -264,7 +301,8 @@ __global__ void __launch_bounds__(GEO_THREADS) geodesic_relax_kernel(GeoArgs g)
             for (int i = tid; i < nd; i += GEO_THREADS) {
                 const int u = deferred[i];
                 front[i] = u;
-                flag[u] = 1;                                                  // queued again, no longer deferred
+                flag_clear(flag, u, 2u);                                      // no longer deferred ...
+                flag_test_and_set(flag, u, 1u);                               // ... queued again
             }
             __syncthreads();
             if (tid == 0) { s_n_front = nd; s_n_def = 0; }
@@ -288,12 +326,15 @@ __global__ void __launch_bounds__(GEO_THREADS) geodesic_relax_kernel(GeoArgs g)
                 if (ties) {
                     int first = 0;
                     for (int j = 0; j < nc; ++j) first += s_cd[j] < d;
-                    if (first < g.E) s_tie = 1;
+                    if (first < job.E) s_tie = 1;
                 }
-                if (rank < g.E) { g.edges[(size_t)node * g.E + rank] = s_cn[i]; g.dists[(size_t)node * g.E + rank] = d; }
+                if (rank < job.E) {
+                    g.edges[job.out_off + (size_t)self * job.E + rank] = s_cn[i];
+                    g.dists[job.out_off + (size_t)self * job.E + rank] = d;
+                }
             }
             __syncthreads();
-            if (tid == 0) { g.n_found[node] = min(nc, g.E); g.need_exact[node] = (uint8_t)s_tie; }
+            if (tid == 0) { g.n_found[node] = min(nc, job.E); g.need_exact[node] = (uint8_t)s_tie; }
         }
         // ---- restore the scratch ----
         __syncthreads();
@@ -301,7 +342,7 @@ __global__ void __launch_bounds__(GEO_THREADS) geodesic_relax_kernel(GeoArgs g)
         for (int i = tid; i < nt; i += GEO_THREADS) {
             const int v = touched[i];
             dist[v] = INF_BITS;
-            flag[v] = 0;
+            flag_clear(flag, v, 3u);
         }
         __syncthreads();
     }
@@ -362,25 +403,29 @@ __global__ void __launch_bounds__(32) geodesic_exact_kernel(GeoArgs g, const int
     for (int t = blockIdx.x; t < n_todo; t += gridDim.x) {
         const int node = todo[t];
         const int v0 = g.node_idx[node];
+        const int jb = job_of(g, node);
+        const GeoJob job = g.jobs[jb];
+        const int self = node - job.first;
+        const int *vnode = g.vertex_node + (size_t)jb * g.V;
         int n = 0, cnt = 0;
         heap_push(h, n, HeapItem{v0, 0.f});
         while (n > 0) {
             const HeapItem cur = heap_pop(h, n);
             if (stamp[cur.v] == node + 1) continue;                                           // :231 (stamps start at 0)
-            if (g.only_valid && !g.valid[cur.v]) { atomicExch(g.error, cur.v + 1); break; }
-            const int other = g.vertex_node[cur.v];
-            if (other >= 0 && other != node) {                                                // :239-245
-                g.edges[(size_t)node * g.E + cnt] = other;
-                g.dists[(size_t)node * g.E + cnt] = cur.d;
-                if (++cnt >= g.E) break;
+            if (job.only_valid && !g.valid[cur.v]) { atomicExch(g.error, cur.v + 1); break; }
+            const int other = vnode[cur.v];
+            if (other >= 0 && other != self) {                                                // :239-245
+                g.edges[job.out_off + (size_t)self * job.E + cnt] = other;
+                g.dists[job.out_off + (size_t)self * job.E + cnt] = cur.d;
+                if (++cnt >= job.E) break;
             }
             stamp[cur.v] = node + 1;
             const int o = g.off[cur.v], c = g.cnt[cur.v];
             for (int k = 0; k < c; ++k) {
                 const int nb = g.adj[o + k];
-                if (g.only_valid && !g.valid[nb]) continue;
+                if (job.only_valid && !g.valid[nb]) continue;
                 const float d = cur.d + edge_length(g.verts, cur.v, nb);
-                if (g.enforce_total || d <= g.max_influence) {
+                if (job.enforce_total || d <= job.max_influence) {
                     if (n >= heap_cap) { atomicExch(g.error, -1); n = 0; cnt = 0; break; }     // cannot happen: capacity = all mesh edges + 1
                     heap_push(h, n, HeapItem{nb, d});
                 }
@@ -505,58 +550,79 @@ __global__ void upsample_index_kernel(const float *__restrict__ nodes, int M, co
 
 using namespace ofx;
 
-extern "C" int ofx_compute_edges_geodesic(const float *verts, const uint8_t *valid, int32_t V, const int32_t *faces, int32_t F,
-                                          const int32_t *node_idx, int32_t M, int32_t max_neighbours, float node_coverage,
-                                          int32_t *edges, float *distances, int32_t *n_found, int32_t only_valid,
-                                          int32_t enforce_total, int32_t *status_host, void *stream)
+extern "C" int ofx_compute_edges_geodesic_batch(const float *verts, const uint8_t *valid, int32_t V, const int32_t *faces, int32_t F,
+                                                const int32_t *node_idx, int32_t n_jobs, const int32_t *job_count_host,
+                                                const int32_t *job_neighbours_host, const float *job_coverage_host,
+                                                const int32_t *job_flags_host, int32_t *edges, float *distances, int32_t *n_found,
+                                                int32_t *status_host, void *stream)
 {
-    OFX_REQUIRE(V >= 0 && F >= 0 && M >= 0 && max_neighbours >= 1, "ofx_compute_edges_geodesic: bad sizes");
+    OFX_REQUIRE(V >= 0 && F >= 0 && n_jobs >= 1 && n_jobs <= GEO_MAX_JOBS, "ofx_compute_edges_geodesic: bad sizes (1..%d jobs)", GEO_MAX_JOBS);
+    OFX_REQUIRE(job_count_host && job_neighbours_host && job_coverage_host && job_flags_host, "ofx_compute_edges_geodesic: null job array");
     if (status_host) status_host[0] = status_host[1] = 0;
+    GeoArgs g{};
+    int M = 0, out = 0, any_only_valid = 0;
+    for (int j = 0; j < n_jobs; ++j) {
+        OFX_REQUIRE(job_count_host[j] >= 0 && job_neighbours_host[j] >= 1, "ofx_compute_edges_geodesic: bad job %d", j);
+        g.jobs[j] = GeoJob{M, job_count_host[j], job_neighbours_host[j], job_flags_host[j] & 1, (job_flags_host[j] >> 1) & 1,
+                           job_coverage_host[j], 2.f * job_coverage_host[j], out};                   // :173
+        any_only_valid |= job_flags_host[j] & 1;
+        M += job_count_host[j];
+        out += job_count_host[j] * job_neighbours_host[j];
+    }
     if (M == 0) return 0;
-    OFX_REQUIRE(verts && faces && node_idx && edges && distances && n_found && (!only_valid || valid) && V > 0,
+    OFX_REQUIRE(verts && faces && node_idx && edges && distances && n_found && (!any_only_valid || valid) && V > 0,
                 "ofx_compute_edges_geodesic: null pointer");
     cudaStream_t s = (cudaStream_t)stream;
-    const int E = max_neighbours;
-    const int grid = std::min(M, 2 * sm_count());
+    // distances + flags of a search in shared memory when the mesh fits (4.25 bytes per vertex), else in global scratch
+    const int n_words = (V + 15) / 16;
+    const size_t geo_smem = ((size_t)V + n_words) * sizeof(int);
+    const bool in_smem = geo_smem <= 200 * 1024;
+    const int per_sm = in_smem ? std::max(1, std::min(4, (int)((220 * 1024) / (geo_smem + 10 * 1024)))) : 2;
+    const int grid = std::min(M, per_sm * sm_count());
     // scratch: adjacency + per-CTA search state
     const size_t n_raw = (size_t)6 * F + 4;
     const int n_scan_sums = (V + 1 + SCAN_BLOCK * SCAN_ITEMS - 1) / (SCAN_BLOCK * SCAN_ITEMS) + 2;
     int *deg = nullptr, *off = nullptr, *cnt = nullptr, *raw = nullptr, *sums = nullptr, *vnode = nullptr, *small = nullptr;
     int *dist_bits = nullptr, *lists = nullptr, *todo = nullptr;
-    int *flags = nullptr;
+    unsigned *flags = nullptr;
     uint8_t *need = nullptr;
     if (graph_scratch_alloc((void **)&deg, ((size_t)V + 2) * sizeof(int), s)) return 1;
     if (graph_scratch_alloc((void **)&off, ((size_t)V + 2) * sizeof(int), s)) return 1;
     if (graph_scratch_alloc((void **)&cnt, ((size_t)V + 2) * sizeof(int), s)) return 1;
     if (graph_scratch_alloc((void **)&raw, n_raw * sizeof(int), s)) return 1;
     if (graph_scratch_alloc((void **)&sums, (size_t)n_scan_sums * sizeof(int), s)) return 1;
-    if (graph_scratch_alloc((void **)&vnode, (size_t)V * sizeof(int), s)) return 1;
+    if (graph_scratch_alloc((void **)&vnode, (size_t)n_jobs * V * sizeof(int), s)) return 1;
     if (graph_scratch_alloc((void **)&small, 8 * sizeof(int), s)) return 1;        // [0] error, [1] number of flagged nodes, [2] total degree
-    if (graph_scratch_alloc((void **)&dist_bits, (size_t)grid * V * sizeof(int), s)) return 1;
+    if (graph_scratch_alloc((void **)&dist_bits, in_smem ? 16 : (size_t)grid * V * sizeof(int), s)) return 1;
     if (graph_scratch_alloc((void **)&lists, (size_t)grid * 4 * V * sizeof(int), s)) return 1;
-    if (graph_scratch_alloc((void **)&flags, (size_t)grid * V * sizeof(int), s)) return 1;
+    if (graph_scratch_alloc((void **)&flags, in_smem ? 16 : (size_t)grid * n_words * sizeof(unsigned), s)) return 1;
     if (graph_scratch_alloc((void **)&need, (size_t)M + 4, s)) return 1;
     if (graph_scratch_alloc((void **)&todo, ((size_t)M + 1) * sizeof(int), s)) return 1;
     OFX_CUDA(cudaMemsetAsync(deg, 0, ((size_t)V + 2) * sizeof(int), s));
     OFX_CUDA(cudaMemsetAsync(small, 0, 8 * sizeof(int), s));
-    OFX_CUDA(cudaMemsetAsync(flags, 0, (size_t)grid * V * sizeof(int), s));
+    if (!in_smem) OFX_CUDA(cudaMemsetAsync(flags, 0, (size_t)grid * n_words * sizeof(unsigned), s));
     if (F > 0) adj_degree_kernel<<<(F + 255) / 256, 256, 0, s>>>(faces, F, V, deg, small);
     if (int rc = exclusive_scan(deg, V + 1, off, sums, small + 2, s)) return rc;
     OFX_CUDA(cudaMemsetAsync(cnt, 0, ((size_t)V + 2) * sizeof(int), s));
     if (F > 0) adj_fill_kernel<<<(F + 255) / 256, 256, 0, s>>>(faces, F, V, off, cnt, raw);
     adj_sort_unique_kernel<<<(V + 127) / 128, 128, 0, s>>>(V, off, raw, cnt);
-    fill_int_kernel<<<std::min((V + 255) / 256, 4 * sm_count()), 256, 0, s>>>(vnode, V, -1);
-    vertex_node_kernel<<<(M + 255) / 256, 256, 0, s>>>(node_idx, M, vnode);
-    fill_int_kernel<<<4 * sm_count(), 256, 0, s>>>(dist_bits, (int64_t)grid * V, INF_BITS);
+    fill_int_kernel<<<std::min((n_jobs * V + 255) / 256, 4 * sm_count()), 256, 0, s>>>(vnode, (int64_t)n_jobs * V, -1);
+    for (int j = 0; j < n_jobs; ++j)
+        if (g.jobs[j].count > 0)
+            vertex_node_kernel<<<(g.jobs[j].count + 255) / 256, 256, 0, s>>>(node_idx, g.jobs[j].first, g.jobs[j].count, vnode + (size_t)j * V);
+    if (!in_smem) fill_int_kernel<<<4 * sm_count(), 256, 0, s>>>(dist_bits, (int64_t)grid * V, INF_BITS);
     OFX_LAUNCH_CHECK();
 
-    GeoArgs g{};
     g.verts = verts; g.valid = valid; g.off = off; g.cnt = cnt; g.adj = raw; g.vertex_node = vnode; g.node_idx = node_idx;
-    g.V = V; g.M = M; g.E = E; g.coverage = node_coverage; g.max_influence = 2.f * node_coverage;   // :173
-    g.only_valid = only_valid; g.enforce_total = enforce_total;
+    g.V = V; g.M = M; g.n_jobs = n_jobs;
     g.edges = edges; g.dists = distances; g.n_found = n_found; g.need_exact = need; g.error = small;
     g.dist_bits = dist_bits; g.lists = lists; g.flags = flags;
-    geodesic_relax_kernel<<<grid, GEO_THREADS, 0, s>>>(g);
+    if (in_smem) {
+        OFX_CUDA(cudaFuncSetAttribute(geodesic_relax_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)geo_smem));
+        geodesic_relax_kernel<true><<<grid, GEO_THREADS, geo_smem, s>>>(g);
+    } else {
+        geodesic_relax_kernel<false><<<grid, GEO_THREADS, 0, s>>>(g);
+    }
     compact_flags_kernel<<<(M + 255) / 256, 256, 0, s>>>(need, M, todo, small + 1);
     OFX_LAUNCH_CHECK();
     int host[4] = {0, 0, 0, 0};
@@ -587,6 +653,17 @@ extern "C" int ofx_compute_edges_geodesic(const float *verts, const uint8_t *val
     else if (host[0] < 0)
         rc = fail("ofx_compute_edges_geodesic: a face index is out of range or the search heap overflowed (%d)", host[0]);
     return rc;
+}
+
+extern "C" int ofx_compute_edges_geodesic(const float *verts, const uint8_t *valid, int32_t V, const int32_t *faces, int32_t F,
+                                          const int32_t *node_idx, int32_t M, int32_t max_neighbours, float node_coverage,
+                                          int32_t *edges, float *distances, int32_t *n_found, int32_t only_valid,
+                                          int32_t enforce_total, int32_t *status_host, void *stream)
+{
+    OFX_REQUIRE(M >= 0 && max_neighbours >= 1, "ofx_compute_edges_geodesic: bad sizes");
+    const int32_t flags = (only_valid ? 1 : 0) | (enforce_total ? 2 : 0);
+    return ofx_compute_edges_geodesic_batch(verts, valid, V, faces, F, node_idx, 1, &M, &max_neighbours, &node_coverage, &flags, edges,
+                                            distances, n_found, status_host, stream);
 }
 
 // weights of the edges from their geodesic distances, normalised per node (graph_proc.cpp:150-152, 281-296): HOST arrays,

@@ -20,7 +20,7 @@ import numpy as np
 import torch
 
 from . import _capi
-from .graph_proc import (DeviceMesh, compute_clusters_d, compute_edges_geodesic_d, downsample_nodes_d,
+from .graph_proc import (DeviceMesh, compute_clusters_d, compute_edges_geodesic_batch_d, compute_edges_geodesic_d, downsample_nodes_d,
                          node_and_edge_clean_up_d)
 
 DEFAULT_GRAPH_PARAMETERS = {           # embedded_deformation_graph.py:62-73
@@ -197,6 +197,8 @@ class EDGraph:
         mesh = getattr(self, "_mesh", None)
         if mesh is None or mesh.V != self.vertices.shape[0] or mesh.F != np.shape(self.faces)[0]:
             mesh = self._mesh = DeviceMesh(self.vertices, self.faces, np.ones(self.vertices.shape[0], dtype=bool), self.device)
+        # the node sets of the three coarser levels first (pure geometry), then ONE launch for their geodesic edges
+        jobs = []
         for level in range(1, 4):
             node_coverage = node_coverage * 2
             down_sample_idx, up_sample_idx = downsample_nodes_d(old_nodes, node_coverage, self.device)   # :279-298, on the device
@@ -206,12 +208,13 @@ class EDGraph:
             graph_edges = -np.ones((n, E), dtype=np.int32)
             graph_edges_weights = np.zeros((n, E), dtype=np.float32)
             graph_edges_distances = np.zeros((n, E), dtype=np.float32)
-            compute_edges_geodesic_d(mesh, level_node_indices, E, node_coverage, graph_edges, graph_edges_weights,
-                                     graph_edges_distances, False, True)                      # :313-320
+            jobs.append((level_node_indices, E, node_coverage, graph_edges, graph_edges_weights, graph_edges_distances,
+                         False, True))                                                        # :313-320
             pyd["down_sample_idx" + str(level)] = down_sample_idx
             pyd["up_sample_idx" + str(level)] = up_sample_idx
             pyd["nn_index_l" + str(level)] = graph_edges
             old_nodes = old_nodes[down_sample_idx]
+        compute_edges_geodesic_batch_d(mesh, jobs)
         self.pyd = pyd
 
     def get_graph_pyramid(self):

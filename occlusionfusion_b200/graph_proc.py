@@ -110,42 +110,62 @@ class DeviceMesh:
         self.V, self.F = int(self.verts.shape[0]), int(self.faces.shape[0])
 
 
+def compute_edges_geodesic_batch_d(mesh, jobs):
+    """Several compute_edges_geodesic searches (graph_proc.cpp:155-300) over ONE mesh in one launch.  jobs: list of tuples
+    (node_indices, num_neighbours, node_coverage, graph_edges, graph_edges_weights, graph_edges_distances,
+    allow_only_valid_vertices, enforce_total_num_neighbors); each job's (M,E) arrays are filled in place for the neighbours
+    found (pre-filled by the caller, as in the reference).  Returns the number of nodes whose answer depended on equal
+    distances (replayed with the reference's heap)."""
+    import torch
+    nis, counts, Es, covs, flags = [], [], [], [], []
+    for ni, E, cov, e, w, d, only_valid, enforce in jobs:
+        ni = np.ascontiguousarray(ni, dtype=np.int32).reshape(-1)
+        M, E = len(ni), int(E)
+        _inplace(e, np.int32, "graph_edges"); _inplace(w, np.float32, "graph_edges_weights"); _inplace(d, np.float32, "graph_edges_distances")
+        assert e.shape == (M, E) and w.shape == (M, E) and d.shape == (M, E)
+        if ni.max(initial=-1) >= mesh.V:
+            raise _capi.OfxError(f"compute_edges_geodesic: node vertex {int(ni.max())} out of range")
+        if only_valid and mesh.valid is None:
+            raise _capi.OfxError("compute_edges_geodesic: allow_only_valid_vertices needs the vertex mask")
+        nis.append(ni); counts.append(M); Es.append(E); covs.append(float(cov))
+        flags.append((1 if only_valid else 0) | (2 if enforce else 0))
+    total = sum(counts)
+    if total == 0:
+        return 0
+    dev = mesh.device
+    n_jobs = len(jobs)
+    i32a = lambda v: (C.c_int32 * n_jobs)(*v)                                  # noqa: E731
+    with torch.cuda.device(dev):
+        ni_d = torch.from_numpy(np.concatenate(nis)).to(dev)
+        e_d = torch.from_numpy(np.concatenate([j[3].reshape(-1) for j in jobs])).to(dev)
+        d_d = torch.from_numpy(np.concatenate([j[5].reshape(-1) for j in jobs])).to(dev)
+        n_d = torch.zeros(total, dtype=torch.int32, device=dev)
+        status = (C.c_int32 * 2)()
+        _capi.check(_capi.load().ofx_compute_edges_geodesic_batch(
+            _capi.ptr(mesh.verts), _capi.ptr(mesh.valid), mesh.V, _capi.ptr(mesh.faces), mesh.F, _capi.ptr(ni_d), n_jobs, i32a(counts),
+            i32a(Es), (C.c_float * n_jobs)(*covs), i32a(flags), _capi.ptr(e_d), _capi.ptr(d_d), _capi.ptr(n_d), status,
+            _capi.stream_ptr(dev)))
+        e_all, d_all, found = e_d.cpu().numpy(), d_d.cpu().numpy(), n_d.cpu().numpy()
+    o = n0 = 0
+    lib = _capi.load()
+    for (ni, E, cov, e, w, d, _, _), M in zip(jobs, counts):
+        E = int(E)
+        e[...] = e_all[o:o + M * E].reshape(M, E)
+        d[...] = d_all[o:o + M * E].reshape(M, E)
+        if M:
+            _capi.check(lib.ofx_edge_weights_host(_p(d), _p(np.ascontiguousarray(found[n0:n0 + M])), M, E, C.c_float(cov), _p(w)))
+        o += M * E
+        n0 += M
+    return int(status[1])
+
+
 def compute_edges_geodesic_d(mesh, node_indices, num_neighbours, node_coverage, graph_edges, graph_edges_weights,
                              graph_edges_distances, allow_only_valid_vertices, enforce_total_num_neighbors):
     """compute_edges_geodesic (graph_proc.cpp:155-300) on the device: `mesh` is a DeviceMesh; graph_edges (M,E) i32 /
     weights / distances (M,E) f32 are filled in place for the neighbours found (pre-filled by the caller, as in the reference).
     Returns the number of nodes whose answer depended on equal distances (replayed with the reference's heap)."""
-    import torch
-    ni = np.ascontiguousarray(node_indices, dtype=np.int32).reshape(-1)
-    M, E = len(ni), int(num_neighbours)
-    e = _inplace(graph_edges, np.int32, "graph_edges")
-    w = _inplace(graph_edges_weights, np.float32, "graph_edges_weights")
-    d = _inplace(graph_edges_distances, np.float32, "graph_edges_distances")
-    assert e.shape == (M, E) and w.shape == (M, E) and d.shape == (M, E)
-    if M == 0:
-        return 0
-    if ni.max(initial=-1) >= mesh.V:
-        raise _capi.OfxError(f"compute_edges_geodesic: node vertex {int(ni.max())} out of range")
-    dev = mesh.device
-    with torch.cuda.device(dev):
-        ni_d = torch.from_numpy(ni).to(dev)
-        e_d = torch.from_numpy(e).to(dev)
-        d_d = torch.from_numpy(d).to(dev)
-        n_d = torch.zeros(M, dtype=torch.int32, device=dev)
-        status = (C.c_int32 * 2)()
-        only_valid = int(bool(allow_only_valid_vertices))
-        if only_valid and mesh.valid is None:
-            raise _capi.OfxError("compute_edges_geodesic: allow_only_valid_vertices needs the vertex mask")
-        _capi.check(_capi.load().ofx_compute_edges_geodesic(_capi.ptr(mesh.verts), _capi.ptr(mesh.valid), mesh.V, _capi.ptr(mesh.faces),
-                                                            mesh.F, _capi.ptr(ni_d), M, E, C.c_float(node_coverage), _capi.ptr(e_d),
-                                                            _capi.ptr(d_d), _capi.ptr(n_d), only_valid,
-                                                            int(bool(enforce_total_num_neighbors)), status,
-                                                            _capi.stream_ptr(dev)))
-        e[...] = e_d.cpu().numpy()
-        d[...] = d_d.cpu().numpy()
-        found = n_d.cpu().numpy()
-    _capi.check(_capi.load().ofx_edge_weights_host(_p(d), _p(found), M, E, C.c_float(node_coverage), _p(w)))
-    return int(status[1])
+    return compute_edges_geodesic_batch_d(mesh, [(node_indices, num_neighbours, node_coverage, graph_edges, graph_edges_weights,
+                                                  graph_edges_distances, allow_only_valid_vertices, enforce_total_num_neighbors)])
 
 
 def node_and_edge_clean_up_d(graph_edges, valid_nodes_mask, device=None):

@@ -258,6 +258,18 @@ class WarpField:
         order = np.argsort(dist[unreachable_verts])[::-1]
         return unreachable_verts[order]
 
+    def _nearest_rows(self, points, nodes):
+        """Index of the nearest row of `nodes` for every row of `points` (float32, ties -> lower index): ofx_nearest_node."""
+        pts = _capi.to_device(points, torch.float32, self.device).reshape(-1, 3)
+        nd = _capi.to_device(nodes, torch.float32, self.device).reshape(-1, 3)
+        idx = torch.empty(pts.shape[0], dtype=torch.int32, device=self.device)
+        if pts.shape[0] == 0:
+            return np.zeros(0, np.int64)
+        with torch.cuda.device(self.device):
+            _capi.check(self._lib.ofx_nearest_node(_capi.ptr(pts), pts.shape[0], _capi.ptr(nd), nd.shape[0], None, _capi.ptr(idx),
+                                                   _capi.stream_ptr(self.device)))
+        return idx.cpu().numpy().astype(np.int64)
+
     def update_graph(self, canonical_model=None):
         """Node insertion (warpfield.py:487-582): add nodes for canonical vertices the graph does
         not reach, re-skin the volume, initialise the new nodes' transforms.
@@ -289,7 +301,7 @@ class WarpField:
             if not kept:
                 # the edge rebuild dropped nodes with too few neighbours and renumbered the rest (edg.py:596): every node of
                 # the new table takes the transform of the nearest old node (an old node that survived finds itself)
-                nearest = np.argmin(np.linalg.norm(self.graph.nodes[:, None, :] - old_nodes[None, :, :], axis=2), axis=1)
+                nearest = self._nearest_rows(self.graph.nodes, old_nodes)
                 R_new, t_new = np.asarray(R_rel)[nearest], np.asarray(t_rel)[nearest]
                 deformed = self.graph.nodes + t_new
             elif getattr(self, "model", None) is not None and hasattr(self.graph, "get_reduced_graph"):
@@ -303,7 +315,7 @@ class WarpField:
                 R_new, t_new, deformed = est["node_rotations"], est["node_translations"], est["deformed_nodes_to_target"]
             else:
                 old, new = self.graph.nodes[:old_num_nodes], self.graph.nodes[old_num_nodes:]
-                nearest = np.argmin(np.linalg.norm(new[:, None, :] - old[None, :, :], axis=2), axis=1)
+                nearest = self._nearest_rows(new, old)
                 R_new = np.concatenate([R_rel, np.asarray(R_rel)[nearest]], axis=0)
                 t_new = np.concatenate([t_rel, np.asarray(t_rel)[nearest]], axis=0)
                 deformed = self.graph.nodes + t_new
