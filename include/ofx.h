@@ -241,6 +241,16 @@ int ofx_node_and_edge_clean_up(const int32_t *edges, int32_t M, int32_t E, uint8
  * (device).  Synchronises the stream (error check). */
 int ofx_compute_clusters(const int32_t *edges, int32_t M, int32_t E, int32_t *clusters, int32_t *sizes,
                          int32_t *n_clusters, void *stream);
+/* ofx_compute_clusters without any allocation.  NO counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The label scratch of the kernel lives in a file-scope device array of OFX_NOALLOC_MAX_NODES ints (256 KiB, held by every
+ * GPU that loads the library until exit); more nodes are refused with an error (use ofx_compute_clusters).  Same outputs as
+ * ofx_compute_clusters; the range check of the edges is reported through *status (DEVICE int32: 0 = ok, n + 1 = node n
+ * has an edge out of range) instead of a host read, so the call neither allocates nor synchronises.  All calls on one GPU
+ * share the array: calls that overlap on the GPU (different streams) race -- order them. */
+#define OFX_NOALLOC_MAX_NODES 65536
+int ofx_compute_clusters_noalloc(const int32_t *edges, int32_t M, int32_t E, int32_t *clusters, int32_t *sizes,
+                                 int32_t *n_clusters, int32_t *status, void *stream);
 /* up_sample_idx of one pyramid level (embedded_deformation_graph.py:279-298) on DEVICE arrays: for every node the position,
  * within down_idx (the kept nodes, ascending: ofx_greedy_insert over the nodes in index order), of the nearest node kept
  * before it. */

@@ -24,7 +24,7 @@ SYMBOLS = [
     "ofx_warp_points", "ofx_check_visibility", "ofx_peer_copy",
     "ofx_nearest_node", "ofx_pixel_anchors_euclidean", "ofx_argmin_norm", "ofx_greedy_insert", "ofx_sample_nodes", "ofx_erode_mesh", "ofx_truncated_region",
     "ofx_mc_count", "ofx_mc_emit", "ofx_mc_vertices",
-    "ofx_compute_edges_geodesic", "ofx_compute_edges_geodesic_batch", "ofx_edge_weights_host", "ofx_node_and_edge_clean_up", "ofx_compute_clusters", "ofx_upsample_index",
+    "ofx_compute_edges_geodesic", "ofx_compute_edges_geodesic_batch", "ofx_edge_weights_host", "ofx_node_and_edge_clean_up", "ofx_compute_clusters", "ofx_compute_clusters_noalloc", "ofx_upsample_index",
     "ofx_compute_edges_geodesic_host", "ofx_node_and_edge_clean_up_host", "ofx_compute_clusters_host", "ofx_downsample_nodes_host",
 ]
 
@@ -89,6 +89,7 @@ def load():
     lib.ofx_edge_weights_host.argtypes = [vp, vp, i32, i32, C.c_float, vp]
     lib.ofx_node_and_edge_clean_up.argtypes = [vp, i32, i32, vp, vp]
     lib.ofx_compute_clusters.argtypes = [vp, i32, i32, vp, vp, vp, vp]
+    lib.ofx_compute_clusters_noalloc.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp]
     lib.ofx_upsample_index.argtypes = [vp, i32, vp, i32, vp, vp]
     lib.ofx_compute_edges_geodesic_host.argtypes = [vp, vp, i32, vp, i32, vp, i32, i32, C.c_float, vp, vp, vp, vp, i32, i32, i32]
     lib.ofx_node_and_edge_clean_up_host.argtypes = [vp, i32, i32, vp]

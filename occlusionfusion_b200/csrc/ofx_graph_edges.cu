@@ -738,3 +738,38 @@ extern "C" int ofx_upsample_index(const float *nodes, int32_t M, const int32_t *
     OFX_LAUNCH_CHECK();
     return 0;
 }
+
+// ---- ofx_compute_clusters_noalloc: the same kernel with its label scratch in a file-scope device array ----------------
+// No counterpart in the reference; added for callers that cannot allocate (CUDA
+// graph capture, serving loops, harnesses that forbid cudaMalloc).  Every GPU that loads the library holds the array
+// (OFX_NOALLOC_MAX_NODES ints = 256 KiB) until exit; every call shares it, so calls that overlap on one GPU race.
+namespace ofx {
+static __device__ __align__(256) int g_noalloc_labels[OFX_NOALLOC_MAX_NODES];
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static int *g_noalloc_labels_ptr[NOALLOC_MAX_DEVICES];      // device address of the array, per device (host code cannot use the name)
+}  // namespace ofx
+
+extern "C" int ofx_compute_clusters_noalloc(const int32_t *edges, int32_t M, int32_t E, int32_t *clusters, int32_t *sizes,
+                                            int32_t *n_clusters, int32_t *status, void *stream)
+{
+    OFX_REQUIRE(M >= 0 && E >= 0 && n_clusters && status, "ofx_compute_clusters_noalloc: bad arguments");
+    OFX_REQUIRE(M <= OFX_NOALLOC_MAX_NODES, "ofx_compute_clusters_noalloc: %d nodes exceed the static scratch (%d); use ofx_compute_clusters",
+                M, OFX_NOALLOC_MAX_NODES);
+    cudaStream_t s = (cudaStream_t)stream;
+    OFX_CUDA(cudaMemsetAsync(status, 0, sizeof(int), s));                      // the kernel only ever raises it
+    if (M == 0) { OFX_CUDA(cudaMemsetAsync(n_clusters, 0, sizeof(int), s)); return 0; }
+    OFX_REQUIRE(edges && clusters && sizes, "ofx_compute_clusters_noalloc: null pointer");
+    int dev = 0;
+    OFX_CUDA(cudaGetDevice(&dev));
+    OFX_REQUIRE(dev >= 0 && dev < NOALLOC_MAX_DEVICES, "ofx_compute_clusters_noalloc: device %d out of range", dev);
+    if (!g_noalloc_labels_ptr[dev]) {                                          // once per device, with that device current
+        int *p = nullptr;
+        OFX_CUDA(cudaGetSymbolAddress((void **)&p, g_noalloc_labels));
+        OFX_REQUIRE(p != nullptr, "ofx_compute_clusters_noalloc: no device address for the scratch array");
+        g_noalloc_labels_ptr[dev] = p;
+    }
+    // the kernel writes label[0..M) before it reads it: nothing of the previous call's contents is used
+    clusters_kernel<<<1, 1024, 0, s>>>(edges, M, E, g_noalloc_labels_ptr[dev], clusters, sizes, n_clusters, status);
+    OFX_LAUNCH_CHECK();
+    return 0;
+}
