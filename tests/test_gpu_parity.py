@@ -683,3 +683,50 @@ def test_full_size_sequence_with_node_insertion(oracle):
     compare(99)
     assert len(nodes) == 980 and n_valid[-1] > n_valid[0]                 # the inserted nodes reach new voxels
     assert wt.max() >= 30 and ((t < 1.0) & (t > -1.0)).sum() > 1000
+
+
+@pytest.mark.parametrize("pinned", [False, True])
+def test_overlapped_frames_with_a_reused_host_buffer(pinned, oracle):
+    """The overlapped end-to-end path (two per-frame sets, upload stream, lazy counters: tsdf.py update / integrate /
+    last_stats) under the worst caller: ONE host frame buffer and ONE estimate dict, overwritten for the next frame the
+    moment integrate() returns (page-locked buffer: after wait_uploaded(), as update() documents), with nothing else
+    waiting for the device.  Every frame differs, so a frame read late, a node-transform staging buffer reused early or
+    counters read from the wrong set change the volume or the counters."""
+    import torch
+    from occlusionfusion_b200 import WarpField
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload("tiny")
+    n_frames = 9
+    vol = _mk_volume(w)
+    wf = WarpField(w.graph(), vol, None)
+    wf.graph_neighbours = w.K
+    vol.warpfield = wf
+    ov = oracle.OracleVolume(w.dims, w.origin, w.voxel_size, w.intr, w.trunc)
+    ov.set_graph(w.nodes, w.coverage, w.K)
+    buf = torch.empty((6, w.H, w.W), dtype=torch.float32, pin_memory=pinned)
+    host = buf.numpy()
+    est_shared = {k: np.array(v, copy=True) for k, v in w.estimate(1).items() if isinstance(v, np.ndarray)}
+    expected, seen = [], []
+    for f in range(n_frames):
+        im = w.frame(f)
+        host[...] = im                                   # overwrite the buffer the previous frame was read from
+        if f > 0:
+            est = w.estimate(f)
+            for k in est_shared:
+                est_shared[k][...] = est[k]              # and the arrays the previous transforms were staged from
+            wf.update_transformations({**est, **est_shared})
+            ov.set_transforms(est["node_rotations"], wf.translations)
+        vol.integrate({"im": buf if pinned else host, "id": f})
+        if pinned:
+            vol.wait_uploaded()
+        host[...] = np.float32(7.5)                      # garbage, at once
+        for k in est_shared:
+            est_shared[k][...] = 3.0
+        expected.append(ov.integrate(im, f == 0))
+        prev = vol.last_stats(previous=True)             # never waits for the frame just submitted
+        if f > 0:
+            assert prev is not None
+            seen.append(prev["updated"])
+    seen.append(vol.last_stats()["updated"])
+    assert seen == expected and min(expected[1:]) > 1000
+    _assert_bit_equal(vol, ov)
