@@ -837,7 +837,7 @@ def bench_graph_ops(args, device):
             "band_frac": float((t.abs() <= 0.9).float().mean()), "region_frac": float(want.mean()),
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
                          "peak_source": peak_src, "bytes_formula": "5*N (4 read + 1 written)"}}
-    # marching cubes inside the truncated region of the same real volume (count -> prefix sum -> emit -> unique -> vertices)
+    # marching cubes inside the truncated region of the same real volume (count -> device scans -> vertices -> faces, one library call)
     region = vol.get_truncated_region(1.2)
     mc = lambda: TSDFVolume.marching_cubes(vol._tsdf_vol, region, 0.0, vol._color_vol)      # noqa: E731
     ms = gpu_ms(mc, reps=3)
@@ -848,7 +848,7 @@ def bench_graph_ops(args, device):
     out["ops"]["marching_cubes_c2_source_frame_512"] = {
         "gpu_ms": ms, "cpu_ms": c_ms, "cpu_kind": "port", "cpu_cores": 1, "voxels": int(vol._tsdf_vol.numel()),
         "vertices": int(v_d.shape[0]), "triangles": int(f_d.shape[0]),
-        "note": "gpu_ms includes the prefix sum and the key sort (torch.cumsum / torch.unique) and one host read of the triangle count"}
+        "note": "one ofx_mc_mesh call (count, two device scans, vertices, faces: own kernels, no sort) + the one host read of the two counts"}
     out["parity"] = "every GPU result above was compared with its CPU baseline's result: identical"
     print(json.dumps(out), flush=True)
 

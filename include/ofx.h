@@ -189,22 +189,21 @@ int ofx_truncated_region(const float *tsdf, int32_t Dx, int32_t Dy, int32_t Dz, 
                          uint8_t *region, void *stream);
 
 /* ---- marching cubes (the scikit-image call at fusion_with_occlusion/tsdf.py:794 and the colour unpack at :797-807) ----
- * Classic form with the case table of csrc/ofx_mc_tables.h.  vol / mask / colour are whole (Dx,Dy,Dz) volumes, C order;
- * cube i = (x*Dy + y)*Dz + z is processed when mask == NULL or mask[i] != 0; corners with value < level are inside.
- *   1. ofx_mc_count:    row_count (Dx*Dy,) i32 = triangles of every z-row of cubes (row = x*Dy + y).
- *   2. the caller forms row_offset (Dx*Dy,) i32 = exclusive prefix sum of row_count, T = total.
- *   3. ofx_mc_emit:     keys (3T,) i64, three per triangle in cube order: a triangle corner is named by its grid edge,
- *                       key = 3 * (linear index of the edge's lower corner) + axis.
- *   4. the caller sorts the keys into unique vertices (faces = index of each key among the unique keys).
- *   5. ofx_mc_vertices: per unique key the vertex in voxel coordinates (lower corner + (level - v0)/(v1 - v0) along the
- *                       axis, float32), optionally the unit gradient normal (towards increasing values) and the colour of
- *                       the nearest voxel unpacked to r, g, b bytes (tsdf.py:797-807; rgb needs colour). */
-int ofx_mc_count(const float *vol, const uint8_t *mask, int32_t Dx, int32_t Dy, int32_t Dz, float level,
-                 int32_t *row_count, void *stream);
-int ofx_mc_emit(const float *vol, const uint8_t *mask, int32_t Dx, int32_t Dy, int32_t Dz, float level,
-                const int32_t *row_count, const int32_t *row_offset, int64_t *keys, void *stream);
-int ofx_mc_vertices(const float *vol, const float *colour, int32_t Dx, int32_t Dy, int32_t Dz, float level,
-                    const int64_t *keys, int64_t n, float *verts, float *normals, uint8_t *rgb, void *stream);
+ * Classic form with the case table of csrc/ofx_mc_tables.h, ONE call, no host read inside.  vol / mask / colour are whole
+ * (Dx,Dy,Dz) volumes, C order (mask, colour may be NULL); cube i = (x*Dy + y)*Dz + z is processed when mask == NULL or
+ * mask[i] != 0; corners with value < level are inside.  Outputs (DEVICE):
+ *   counts (2,) i32   [0] vertices, [1] triangles of the mesh -- always written;
+ *   verts (cap_verts,3) f32   one vertex per crossed grid edge of a processed cube, ascending by edge
+ *                     (3 * linear index of the edge's lower corner + axis), in voxel coordinates: lower corner +
+ *                     (level - v0)/(v1 - v0) along the axis, float32;
+ *   normals (cap_verts,3) f32 or NULL   unit gradient of vol at the vertex (towards increasing values);
+ *   rgb (cap_verts,3) u8 or NULL        colour of the nearest voxel unpacked to r, g, b (tsdf.py:797-807; needs colour);
+ *   faces (cap_tris,3) i32    vertex indices, triangles in cube order.
+ * When counts[0] > cap_verts or counts[1] > cap_tris nothing but counts is written: read counts, come back with room
+ * (cap 0 / NULL buffers = count only).  Dz <= 21845. */
+int ofx_mc_mesh(const float *vol, const uint8_t *mask, const float *colour, int32_t Dx, int32_t Dy, int32_t Dz,
+                float level, int32_t cap_verts, int32_t cap_tris, float *verts, float *normals, uint8_t *rgb,
+                int32_t *faces, int32_t *counts, void *stream);
 
 /* ---- the edge half of the graph builder on the device ---------------------------------------------------------
  * compute_edges_geodesic (csrc/cpu/graph_proc.cpp:155-300, binding csrc/main.cpp:30; callers

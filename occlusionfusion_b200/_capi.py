@@ -23,7 +23,7 @@ SYMBOLS = [
     "ofx_volume_world_points", "ofx_volume_skin", "ofx_volume_deform", "ofx_pack_frame", "ofx_skin",
     "ofx_warp_points", "ofx_check_visibility", "ofx_peer_copy",
     "ofx_nearest_node", "ofx_pixel_anchors_euclidean", "ofx_argmin_norm", "ofx_greedy_insert", "ofx_sample_nodes", "ofx_erode_mesh", "ofx_truncated_region",
-    "ofx_mc_count", "ofx_mc_emit", "ofx_mc_vertices",
+    "ofx_mc_mesh",
     "ofx_compute_edges_geodesic", "ofx_compute_edges_geodesic_batch", "ofx_edge_weights_host", "ofx_node_and_edge_clean_up", "ofx_compute_clusters", "ofx_compute_clusters_noalloc", "ofx_upsample_index",
     "ofx_compute_edges_geodesic_host", "ofx_node_and_edge_clean_up_host", "ofx_compute_clusters_host", "ofx_downsample_nodes_host",
 ]
@@ -81,9 +81,7 @@ def load():
     lib.ofx_sample_nodes.argtypes = [vp, i32, vp, C.c_float, i32, vp, vp, vp, vp]
     lib.ofx_erode_mesh.argtypes = [vp, i32, i32, i32, i32, vp, vp]
     lib.ofx_truncated_region.argtypes = [vp, i32, i32, i32, f64, vp, vp]
-    lib.ofx_mc_count.argtypes = [vp, vp, i32, i32, i32, C.c_float, vp, vp]
-    lib.ofx_mc_emit.argtypes = [vp, vp, i32, i32, i32, C.c_float, vp, vp, vp, vp]
-    lib.ofx_mc_vertices.argtypes = [vp, vp, i32, i32, i32, C.c_float, vp, i64, vp, vp, vp, vp]
+    lib.ofx_mc_mesh.argtypes = [vp, vp, vp, i32, i32, i32, C.c_float, i32, i32, vp, vp, vp, vp, vp, vp]
     lib.ofx_compute_edges_geodesic.argtypes = [vp, vp, i32, vp, i32, vp, i32, i32, C.c_float, vp, vp, vp, i32, i32, vp, vp]
     lib.ofx_compute_edges_geodesic_batch.argtypes = [vp, vp, i32, vp, i32, vp, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp]
     lib.ofx_edge_weights_host.argtypes = [vp, vp, i32, i32, C.c_float, vp]

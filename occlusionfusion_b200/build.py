@@ -16,7 +16,7 @@ CSRC = os.path.join(PKG, "csrc")
 LIB_DIR = os.path.join(PKG, "lib")
 LIB = os.path.join(LIB_DIR, "libofx.so")
 SOURCES = ["ofx_volume.cu", "ofx_points.cu", "ofx_skin_cache.cu", "ofx_integrate.cu", "ofx_graph.cu", "ofx_graph_edges.cu", "ofx_graph_host.cu", "ofx_mc.cu"]
-HEADERS = ["ofx_mc_tables.h", "ofx_math.cuh", "ofx_volume.cuh", "ofx_brick.cuh", "ofx_common.h", os.path.join("..", "..", "include", "ofx.h")]
+HEADERS = ["ofx_mc_tables.h", "ofx_math.cuh", "ofx_volume.cuh", "ofx_brick.cuh", "ofx_fused.cuh", "ofx_scan.cuh", "ofx_common.h", os.path.join("..", "..", "include", "ofx.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "--fmad=false", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off", "-Xptxas", "-v"]
 # -ffp-contract=off: the HOST code of the .cu files (ofx_graph_host.cu: geodesic path lengths and edge weights that must equal

@@ -19,6 +19,9 @@ import torch
 
 from . import _capi
 
+# output capacities of marching_cubes() remembered per (volume shape, device): (vertices, triangles)
+_MC_CAPACITY = {}
+
 
 class TSDFVolume:
     """Volumetric TSDF fusion of RGB-D frames under a non-rigid warp field (tsdf.py:37)."""
@@ -342,11 +345,12 @@ class TSDFVolume:
 
     @staticmethod
     def marching_cubes(tsdf_vol, mask=None, level=0.0, color_vol=None):
-        """Classic marching cubes on the device (ofx_mc_count / ofx_mc_emit / ofx_mc_vertices; the scikit-image call of
-        tsdf.py:794 -- Lewiner's variant there, see DESIGN.md for what differs).  tsdf_vol / mask / color_vol: (Dx,Dy,Dz)
-        numpy arrays or CUDA tensors.  Returns CUDA tensors: verts (n,3) f32 in voxel coordinates (array axis order), faces
-        (T,3) i64, normals (n,3) f32 (unit gradient, towards increasing values), rgb (n,3) u8 or None.  Vertices are unique
-        per grid edge and sorted by edge; faces come in cube order."""
+        """Classic marching cubes on the device (ofx_mc_mesh: one library call; the scikit-image call of tsdf.py:794 --
+        Lewiner's variant there, see DESIGN.md for what differs).  tsdf_vol / mask / color_vol: (Dx,Dy,Dz) numpy arrays or
+        CUDA tensors.  Returns CUDA tensors: verts (n,3) f32 in voxel coordinates (array axis order), faces (T,3) i32,
+        normals (n,3) f32 (unit gradient, towards increasing values), rgb (n,3) u8 or None.  Vertices are unique per grid
+        edge and sorted by edge; faces come in cube order.  One host read (the two counts) after the kernels; the output
+        buffers are sized from the previous call on a volume of the same shape (retried with room when they were short)."""
         _capi.require_cuda()
         lib = _capi.load()
         dev = tsdf_vol.device if isinstance(tsdf_vol, torch.Tensor) and tsdf_vol.is_cuda \
@@ -361,27 +365,25 @@ class TSDFVolume:
         else:
             m = _capi.to_device(np.asarray(mask).astype(np.uint8), torch.uint8, dev)
         c = None if color_vol is None else _capi.to_device(color_vol, torch.float32, dev)
-        lvl = C.c_float(level)
+        key = (Dx, Dy, Dz, dev.index)
+        cap_v, cap_t = _MC_CAPACITY.get(key, (1 << 14, 1 << 15))
         with torch.cuda.device(dev):
             S = _capi.stream_ptr(dev)
-            count = torch.zeros(max(Dx * Dy, 1), dtype=torch.int32, device=dev)
-            _capi.check(lib.ofx_mc_count(_capi.ptr(t), _capi.ptr(m), Dx, Dy, Dz, lvl, _capi.ptr(count), S))
-            incl = torch.cumsum(count, 0, dtype=torch.int32)                  # plumbing: prefix sum over the Dx*Dy rows
-            T = int(incl[-1].item())
-            offset = (incl - count).contiguous()
-            keys = torch.empty(3 * T, dtype=torch.int64, device=dev)
-            if T:
-                _capi.check(lib.ofx_mc_emit(_capi.ptr(t), _capi.ptr(m), Dx, Dy, Dz, lvl, _capi.ptr(count), _capi.ptr(offset),
-                                            _capi.ptr(keys), S))
-            ukeys, inverse = torch.unique(keys, sorted=True, return_inverse=True)    # plumbing: vertices = unique grid edges
-            n = int(ukeys.numel())
-            verts = torch.empty((n, 3), dtype=torch.float32, device=dev)
-            normals = torch.empty((n, 3), dtype=torch.float32, device=dev)
-            rgb = torch.empty((n, 3), dtype=torch.uint8, device=dev) if c is not None else None
-            if n:
-                _capi.check(lib.ofx_mc_vertices(_capi.ptr(t), _capi.ptr(c), Dx, Dy, Dz, lvl, _capi.ptr(ukeys.contiguous()), n,
-                                                _capi.ptr(verts), _capi.ptr(normals), _capi.ptr(rgb), S))
-        return verts, inverse.reshape(-1, 3), normals, rgb
+            counts = torch.empty(2, dtype=torch.int32, device=dev)
+            while True:
+                verts = torch.empty((cap_v, 3), dtype=torch.float32, device=dev)
+                normals = torch.empty((cap_v, 3), dtype=torch.float32, device=dev)
+                rgb = torch.empty((cap_v, 3), dtype=torch.uint8, device=dev) if c is not None else None
+                faces = torch.empty((cap_t, 3), dtype=torch.int32, device=dev)
+                _capi.check(lib.ofx_mc_mesh(_capi.ptr(t), _capi.ptr(m), _capi.ptr(c), Dx, Dy, Dz, C.c_float(level), cap_v, cap_t,
+                                            _capi.ptr(verts), _capi.ptr(normals), _capi.ptr(rgb), _capi.ptr(faces),
+                                            _capi.ptr(counts), S))
+                n, T = (int(x) for x in counts.tolist())                         # the one host read
+                if n <= cap_v and T <= cap_t:
+                    break
+                cap_v, cap_t = max(cap_v, n + n // 4 + 64), max(cap_t, T + T // 4 + 64)
+            _MC_CAPACITY[key] = (max(cap_v, n + n // 4 + 64), max(cap_t, T + T // 4 + 64))
+        return verts[:n], faces[:T], normals[:n], (rgb[:n] if rgb is not None else None)
 
     def get_mesh(self):
         """(verts, faces, norms, colors) of the zero level set inside the truncated region (tsdf.py:779-809): verts in world
@@ -390,7 +392,7 @@ class TSDFVolume:
         region = self.get_truncated_region(1.2)                                # tsdf.py:791
         verts, faces, norms, rgb = self.marching_cubes(self._tsdf_vol, region, 0.0, self._color_vol)
         verts = verts.cpu().numpy() * np.float32(self._voxel_size) + np.asarray(self._vol_origin, dtype=np.float32)   # :798
-        return verts, faces.cpu().numpy().astype(np.int32), norms.cpu().numpy(), rgb.cpu().numpy()
+        return verts, faces.cpu().numpy(), norms.cpu().numpy(), rgb.cpu().numpy()
 
     def get_canonical_model(self):                                            # tsdf.py:811-821
         if hasattr(self, "canonical_model"):

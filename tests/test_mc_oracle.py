@@ -27,6 +27,28 @@ def test_table_is_what_the_generator_derives(tmp_path):
     assert open(tmp_path / "t.h").read() == committed
 
 
+def test_table_uses_exactly_the_crossed_edges_of_every_case():
+    """What csrc/ofx_mc.cu's vertex ownership rests on: the triangles of a case touch every grid edge of the cube whose
+    end points lie on different sides of the level, and no other edge."""
+    import re
+    s = open(os.path.join(ROOT, "occlusionfusion_b200", "csrc", "ofx_mc_tables.h")).read()
+    tris = [int(x) for x in re.findall(r"-?\d+", re.search(r"OFX_MC_TRIS\[256\]\s*=\s*\{(.*?)\};", s, re.S).group(1))]
+    rows = re.findall(r"\{([^{}]*)\}", re.search(r"OFX_MC_EDGES\[256\]\[\d+\]\s*=\s*\{(.*)\};", s, re.S).group(1))
+    edges = [[int(x) for x in re.findall(r"-?\d+", r)] for r in rows]
+    assert len(tris) == 256 and len(edges) == 256
+    for c in range(256):
+        crossed = set()
+        for e in range(12):
+            axis, r = e >> 2, e & 3
+            off = [0, 0, 0]
+            off[1 if axis == 0 else 0] = r & 1
+            off[1 if axis == 2 else 2] = r >> 1
+            k0 = off[0] + 2 * off[1] + 4 * off[2]
+            if ((c >> k0) & 1) != ((c >> (k0 + (1 << axis))) & 1):
+                crossed.add(e)
+        assert set(edges[c][:3 * tris[c]]) == crossed, c
+
+
 def test_closed_surface_is_a_closed_oriented_manifold(oracle):
     n = 36
     x, y, z = np.meshgrid(*(np.arange(n),) * 3, indexing="ij")
