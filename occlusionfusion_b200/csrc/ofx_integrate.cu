@@ -23,6 +23,7 @@
 namespace ofx {
 
 int sm_count();
+int graph_scratch_alloc(void **p, size_t bytes, cudaStream_t s);   // ofx_graph.cu: the stream-ordered scratch pool
 
 // ---- generic one-CTA-per-brick kernel (identity warp, deform materialisation) --------------------
 // dynamic shared memory (non-identity modes): [skin-cache slot | node transforms]
@@ -452,6 +453,7 @@ extern "C" int ofx_prepare_frame(ofx_volume *v, const float *rotations, const fl
 {
     OFX_REQUIRE(v && rotations && translations && intr_host && H > 0 && W > 0, "ofx_prepare_frame: bad arguments");
     OFX_REQUIRE(v->graph_ready, "ofx_prepare_frame: call ofx_set_graph first");
+    if (int rc = graph_finish(v)) return rc;
     cudaStream_t s = (cudaStream_t)stream;
     const int set = 1 - v->cur_set;
     v->prepared = false;
@@ -479,6 +481,7 @@ extern "C" int ofx_integrate(ofx_volume *v, const float *depth, const float *col
         return launch_brick<4, MODE_IDENTITY>(v, v->n_bricks, ga, fa, st, nullptr, nullptr, s);
     }
     OFX_REQUIRE(v->graph_ready, "ofx_integrate: warped frame before ofx_set_graph");
+    if (int rc = graph_finish(v)) return rc;
     const bool culled = v->prepared;
     if (culled) {
         // ofx_prepare_frame has staged this frame in the other set: switch to it
@@ -505,6 +508,7 @@ extern "C" int ofx_integrate_warped(ofx_volume *v, const float *rotations, const
     OFX_REQUIRE(v && rotations && translations && depth && colour_packed && intr_host && H > 0 && W > 0,
                 "ofx_integrate_warped: bad arguments");
     OFX_REQUIRE(v->graph_ready, "ofx_integrate_warped: warped frame before ofx_set_graph");
+    if (int rc = graph_finish(v)) return rc;
     cudaStream_t s = (cudaStream_t)stream;
     unsigned long long *st = reinterpret_cast<unsigned long long *>(stats ? stats : v->stats_scratch);
     const FrameArgs fa = make_frame_args(depth, colour_packed, intr_host, H, W, v->desc.trunc_margin, obs_weight);
@@ -527,6 +531,7 @@ extern "C" int ofx_volume_deform(ofx_volume *v, float *out_pts, uint8_t *valid, 
 {
     OFX_REQUIRE(v, "ofx_volume_deform: null handle");
     OFX_REQUIRE(v->graph_ready, "ofx_volume_deform: call ofx_set_graph first");
+    if (int rc = graph_finish(v)) return rc;
     FrameArgs fa{};
     const GraphArgs ga = graph_args(v);
     cudaStream_t s = (cudaStream_t)stream;
@@ -546,23 +551,20 @@ extern "C" int ofx_volume_skin(ofx_volume *v, int32_t *anchors, float *weights, 
 {
     OFX_REQUIRE(v && anchors && weights && valid, "ofx_volume_skin: null argument");
     OFX_REQUIRE(v->graph_ready, "ofx_volume_skin: call ofx_set_graph first");
+    if (int rc = graph_finish(v)) return rc;
     // Full (n,K) arrays as WarpField.skin returns them, including partially-anchored voxels:
     // exact brute force over all nodes; on request only, never on the per-frame path.
     cudaStream_t s = (cudaStream_t)stream;
-    float *pts = nullptr, *nodes = nullptr;
-    OFX_CUDA(cudaMalloc(&pts, (size_t)v->n_voxels * 3 * sizeof(float)));
-    if (cudaMalloc(&nodes, (size_t)v->M * 3 * sizeof(float)) != cudaSuccess) {
-        cudaFree(pts);
-        return fail("ofx_volume_skin: out of device memory");
-    }
+    float *pts = nullptr, *nodes = nullptr;                       // stream-ordered pool: no device-wide synchronisation
+    if (graph_scratch_alloc((void **)&pts, (size_t)v->n_voxels * 3 * sizeof(float), s)) return 1;
+    if (graph_scratch_alloc((void **)&nodes, (size_t)v->M * 3 * sizeof(float), s)) { cudaFreeAsync(pts, s); return 1; }
     int rc = ofx_volume_world_points(v, pts, stream);
     if (!rc) {
         cudaMemcpy2DAsync(nodes, 3 * sizeof(float), v->node_rec, NODE_REC_FLOATS * sizeof(float), 3 * sizeof(float),
                           v->M, cudaMemcpyDeviceToDevice, s);
         rc = ofx_skin(pts, v->n_voxels, nodes, v->M, v->coverage, v->K, anchors, weights, valid, stream);
     }
-    cudaStreamSynchronize(s);
-    cudaFree(pts);
-    cudaFree(nodes);
+    cudaFreeAsync(pts, s);
+    cudaFreeAsync(nodes, s);
     return rc;
 }

@@ -123,56 +123,84 @@ __global__ void __launch_bounds__(128) brick_bound_kernel(VolumeGeom g, int n_br
     if (live && !fill) cnt[b] = count;
 }
 
-// Single-CTA exclusive scan of n ints (n up to a few million; runs only when the graph changes).
-// flag_mode: scan (in[i] > 0) instead of in[i] and scatter i into `compact` at its rank.
-__global__ void __launch_bounds__(1024) scan_kernel(const int *__restrict__ in, int n, int *__restrict__ out,
-                                                    int *__restrict__ compact, int *__restrict__ total_max)
+// Exclusive scans over the bricks, two levels, every block busy (the single-CTA scan of round 1 walked 131 k bricks of a
+// 512^3 volume in 128 serial rounds, three times per ofx_set_graph).  One pass handles both sequences the set-up needs:
+// the candidate counts themselves (-> list offsets) and the flags count > 0 (-> ranks: cache slots, or the compact list).
+//   brick_scan_local_kernel   per block of 1024 bricks: local exclusive prefixes, block sums, running maximum
+//   brick_scan_apply_kernel   per block: base = sum of the block sums before it (re-reduced by every block: at most 1024
+//                             entries), prefixes + base -> outputs, compaction, totals by the last block
+constexpr int BSCAN = 1024;
+
+__device__ __forceinline__ int2 block_scan2(int a, int b, int2 *s_warp, int2 *total)
 {
-    __shared__ int s_warp[32];
-    __shared__ int s_carry;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    if (threadIdx.x == 0) s_carry = 0;
-    int vmax = 0;
-    __syncthreads();
-    for (int base = 0; base < n; base += 1024) {
-        const int i = base + threadIdx.x;
-        int x = i < n ? in[i] : 0;
-        vmax = max(vmax, x);
-        if (compact) x = x > 0 ? 1 : 0;
-        int incl = x;
-        for (int o = 1; o < 32; o <<= 1) {
-            const int y = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += y;
-        }
-        if (lane == 31) s_warp[wid] = incl;
-        __syncthreads();
-        if (wid == 0) {
-            int t = s_warp[lane];
-            for (int o = 1; o < 32; o <<= 1) {
-                const int y = __shfl_up_sync(0xffffffffu, t, o);
-                if (lane >= o) t += y;
-            }
-            s_warp[lane] = t;
-        }
-        __syncthreads();
-        const int excl = s_carry + (wid ? s_warp[wid - 1] : 0) + incl - x;
-        if (i < n) {
-            if (out) out[i] = excl;
-            if (compact && x) compact[excl] = i;
-        }
-        __syncthreads();
-        if (threadIdx.x == 1023) s_carry = excl + x;
-        __syncthreads();
+    int ia = a, ib = b;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int ya = __shfl_up_sync(0xffffffffu, ia, o), yb = __shfl_up_sync(0xffffffffu, ib, o);
+        if (lane >= o) { ia += ya; ib += yb; }
     }
-    // block max
-    for (int o = 16; o > 0; o >>= 1) vmax = max(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
-    if (lane == 0) s_warp[wid] = vmax;
     __syncthreads();
-    if (threadIdx.x == 0) {
-        int m = 0;
-        for (int k = 0; k < 32; ++k) m = max(m, s_warp[k]);
-        total_max[0] = s_carry;
-        total_max[1] = m;
+    if (lane == 31) s_warp[wid] = make_int2(ia, ib);
+    __syncthreads();
+    if (wid == 0) {
+        int2 t = s_warp[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int ya = __shfl_up_sync(0xffffffffu, t.x, o), yb = __shfl_up_sync(0xffffffffu, t.y, o);
+            if (lane >= o) { t.x += ya; t.y += yb; }
+        }
+        s_warp[lane] = t;
+    }
+    __syncthreads();
+    const int2 before = wid ? s_warp[wid - 1] : make_int2(0, 0);
+    *total = s_warp[31];
+    return make_int2(before.x + ia - a, before.y + ib - b);
+}
+
+__global__ void __launch_bounds__(BSCAN) brick_scan_local_kernel(const int *__restrict__ cnt, int n, int *__restrict__ off_out,
+                                                                 int *__restrict__ rank_out, int2 *__restrict__ block_sums,
+                                                                 int *__restrict__ max_out)
+{
+    __shared__ int2 s_warp[32];
+    const int i = blockIdx.x * BSCAN + threadIdx.x;
+    const int x = i < n ? cnt[i] : 0;
+    int2 total;
+    const int2 ex = block_scan2(x, x > 0 ? 1 : 0, s_warp, &total);
+    if (i < n) {
+        if (off_out) off_out[i] = ex.x;
+        rank_out[i] = ex.y;
+    }
+    if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
+    if (max_out) {
+        int m = x;
+        for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if ((threadIdx.x & 31) == 0 && m > 0) atomicMax(max_out, m);
+    }
+}
+
+// totals[0] = sum of the counts, totals[1] = number of bricks with count > 0
+__global__ void __launch_bounds__(BSCAN) brick_scan_apply_kernel(const int *__restrict__ cnt, int n, int *__restrict__ off_out,
+                                                                 int *__restrict__ rank_out, int *__restrict__ compact,
+                                                                 const int2 *__restrict__ block_sums, int *__restrict__ total_cnt,
+                                                                 int *__restrict__ total_flags)
+{
+    __shared__ int2 s_warp[32];
+    int a = 0, b = 0;
+    for (int k = threadIdx.x; k < (int)blockIdx.x; k += BSCAN) { const int2 t = block_sums[k]; a += t.x; b += t.y; }
+    int2 base;
+    block_scan2(a, b, s_warp, &base);
+    const int i = blockIdx.x * BSCAN + threadIdx.x;
+    if (i < n) {
+        if (off_out) off_out[i] += base.x;
+        const int r = rank_out[i] + base.y;
+        rank_out[i] = r;
+        if (compact && cnt[i] > 0) compact[r] = i;
+    }
+    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) {
+        const int2 mine = block_sums[blockIdx.x];
+        if (total_cnt) *total_cnt = base.x + mine.x;
+        if (total_flags) *total_flags = base.y + mine.y;
     }
 }
 
@@ -324,12 +352,13 @@ __global__ void __launch_bounds__(BRICK_THREADS) skin_brick_kernel(VolumeGeom g,
 
 // One record per active brick with everything the per-frame cull needs, contiguous in the order of the
 // active list: {lx0, iy0, iz0, n_used | list offset, cache slot, brick, 0 | centre + bounding radius | half extents}.
-__global__ void active_desc_kernel(VolumeGeom g, const int *__restrict__ active, int n_active, const int *__restrict__ cnt,
+__global__ void active_desc_kernel(VolumeGeom g, const int *__restrict__ active, const int *__restrict__ n_active_dev,
+                                   const int *__restrict__ cnt,
                                    const int *__restrict__ off, const int *__restrict__ brick_slot,
                                    const float4 *__restrict__ brick_box, int4 *__restrict__ desc)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_active) return;
+    if (i >= *n_active_dev) return;                  // the grid covers every brick: the host does not know the count yet
     const int b = active[i];
     const BrickCoord bc = brick_coord(g, b);
     const float4 box = brick_box[2 * b], ext = brick_box[2 * b + 1];
@@ -373,16 +402,18 @@ extern "C" int ofx_set_graph(ofx_volume *v, const float *nodes, int32_t M, doubl
 
     v->cache_kp = K <= 4 ? 4 : 8;
 
-    const int nb = v->n_bricks;
+    const int nb = v->n_bricks, nblk = (nb + BSCAN - 1) / BSCAN;
+    v->graph_pending = false;
     OFX_CUDA(cudaMemsetAsync(v->scratch, 0, 16 * sizeof(int), s));
     brick_bound_kernel<<<(nb + 127) / 128, 128, 0, s>>>(v->geom, nb, v->node_rec, M, K, v->cutoff, v->brick_radius,
                                                         v->brick_cnt, nullptr, nullptr, v->brick_box);
     OFX_LAUNCH_CHECK();
-    scan_kernel<<<1, 1024, 0, s>>>(v->brick_cnt, nb, v->brick_off, nullptr, v->scratch);
+    // list offsets (scan of the counts) and cache slots (rank among the bricks that have candidates) in one pass
+    brick_scan_local_kernel<<<nblk, BSCAN, 0, s>>>(v->brick_cnt, nb, v->brick_off, v->brick_slot, v->scan_sums, v->scratch + 1);
+    brick_scan_apply_kernel<<<nblk, BSCAN, 0, s>>>(v->brick_cnt, nb, v->brick_off, v->brick_slot, nullptr, v->scan_sums,
+                                                   v->scratch + 0, v->scratch + 6);
     OFX_LAUNCH_CHECK();
-    // cache slots: rank of the brick among the bricks that have candidates (v->live is free scratch here)
-    scan_kernel<<<1, 1024, 0, s>>>(v->brick_cnt, nb, v->brick_slot, v->live, v->scratch + 6);
-    OFX_LAUNCH_CHECK();
+    // the one wait of the set-up: the sizes of the cache and of the node lists are needed on the host to provide the memory
     int tm[8] = {0};
     OFX_CUDA(cudaMemcpyAsync(tm, v->scratch, sizeof(tm), cudaMemcpyDeviceToHost, s));
     OFX_CUDA(cudaStreamSynchronize(s));
@@ -422,20 +453,37 @@ extern "C" int ofx_set_graph(ofx_volume *v, const float *nodes, int32_t M, doubl
     default: rc = launch_skin_brick<8>(v, max_cnt, s); break;
     }
     if (rc) return rc;
-    scan_kernel<<<1, 1024, 0, s>>>(v->brick_cnt, nb, nullptr, v->active, v->scratch + 4);
+    // active list = the bricks that kept a skin-valid voxel (v->live is free scratch here: the ranks)
+    brick_scan_local_kernel<<<nblk, BSCAN, 0, s>>>(v->brick_cnt, nb, nullptr, v->live, v->scan_sums, nullptr);
+    brick_scan_apply_kernel<<<nblk, BSCAN, 0, s>>>(v->brick_cnt, nb, nullptr, v->live, v->active, v->scan_sums, nullptr,
+                                                   v->scratch + 4);
+    active_desc_kernel<<<(nb + 255) / 256, 256, 0, s>>>(v->geom, v->active, v->scratch + 4, v->brick_cnt, v->brick_off,
+                                                        v->brick_slot, v->brick_box, v->active_desc);
     OFX_LAUNCH_CHECK();
-    int res[6] = {0};
-    OFX_CUDA(cudaMemcpyAsync(res, v->scratch, sizeof(res), cudaMemcpyDeviceToHost, s));
-    OFX_CUDA(cudaStreamSynchronize(s));
-    OFX_REQUIRE(res[2] == 0, "ofx_set_graph: a brick of %dx%dx%d voxels uses %d distinct anchor nodes (limit %d); "
-                "nodes are far denser than the voxel grid", BX, BY, BZ, res[2], MAX_BRICK_NODES);
-    v->n_active = res[4];
-    if (v->n_active > 0) {
-        active_desc_kernel<<<(v->n_active + 255) / 256, 256, 0, s>>>(v->geom, v->active, v->n_active, v->brick_cnt, v->brick_off,
-                                                                   v->brick_slot, v->brick_box, v->active_desc);
-        OFX_LAUNCH_CHECK();
-    }
+    // the results (error flag, number of active bricks) travel to page-locked host memory behind the kernels; nobody waits
+    // here -- graph_finish() reads them when the next call needs them
+    OFX_CUDA(cudaMemcpyAsync(v->host_res, v->scratch, 8 * sizeof(int), cudaMemcpyDeviceToHost, s));
+    OFX_CUDA(cudaEventRecord(v->graph_event, s));
+    v->graph_pending = true;
+    v->n_active = 0;
     v->counters_dirty[0] = v->counters_dirty[1] = false;       // scratch was cleared above
     v->graph_ready = true;
+    return 0;
+}
+
+// The tail of ofx_set_graph, run by the first call that needs its results: waits for the set-up kernels (long done in a
+// frame loop), reports the brick-node overflow, publishes the number of active bricks.
+int ofx::graph_finish(ofx_volume *v)
+{
+    if (!v->graph_pending) return 0;
+    v->graph_pending = false;
+    OFX_CUDA(cudaEventSynchronize(v->graph_event));
+    const int *res = v->host_res;
+    if (res[2] != 0) {
+        v->graph_ready = false;
+        return fail("ofx_set_graph: a brick of %dx%dx%d voxels uses %d distinct anchor nodes (limit %d); "
+                    "nodes are far denser than the voxel grid", BX, BY, BZ, res[2], MAX_BRICK_NODES);
+    }
+    v->n_active = res[4];
     return 0;
 }

@@ -131,6 +131,9 @@ extern "C" int ofx_volume_create(ofx_volume **out, const ofx_volume_desc *d)
     OFX_CUDA(cudaMalloc(&v->scratch, 16 * sizeof(int)));      // [0..7] set_graph results, [8 + 4*set ..] n_live, brick work counter, retired CTAs
     OFX_CUDA(cudaMemset(v->scratch, 0, 16 * sizeof(int)));
     OFX_CUDA(cudaMalloc(&v->stats_scratch, OFX_N_STATS * sizeof(uint64_t)));
+    OFX_CUDA(cudaMalloc(&v->scan_sums, ((nb + 1023) / 1024 + 1) * sizeof(int2)));
+    OFX_CUDA(cudaHostAlloc(&v->host_res, 8 * sizeof(int), cudaHostAllocDefault));
+    OFX_CUDA(cudaEventCreateWithFlags(&v->graph_event, cudaEventDisableTiming));
     *out = v;
     return 0;
 }
@@ -142,6 +145,9 @@ extern "C" int ofx_volume_destroy(ofx_volume *v)
     cudaFree(v->brick_off); cudaFree(v->brick_radius); cudaFree(v->cand); cudaFree(v->brick_nodes);
     cudaFree(v->active); cudaFree(v->scratch); cudaFree(v->stats_scratch);
     cudaFree(v->live_set[0]); cudaFree(v->live_set[1]); cudaFree(v->stats_acc); cudaFree(v->active_desc); cudaFree(v->brick_box); cudaFree(v->depth_tiles); cudaFree(v->frame_dc);
+    cudaFree(v->scan_sums);
+    if (v->host_res) cudaFreeHost(v->host_res);
+    if (v->graph_event) cudaEventDestroy(v->graph_event);
     delete v;
     return 0;
 }
@@ -204,6 +210,7 @@ extern "C" int ofx_set_transforms(ofx_volume *v, const float *rotations, const f
 {
     OFX_REQUIRE(v && rotations && translations, "ofx_set_transforms: null argument");
     OFX_REQUIRE(v->graph_ready, "ofx_set_transforms: call ofx_set_graph first");
+    if (int rc = graph_finish(v)) return rc;
     if (int rc = ofx_write_transforms(v, v->node_rec, rotations, translations, (cudaStream_t)stream)) return rc;
     v->transforms_ready = true;
     return 0;

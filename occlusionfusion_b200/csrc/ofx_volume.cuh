@@ -95,5 +95,15 @@ struct ofx_volume {
     int *scratch;                // small device scratch: [0]=total [1]=max [2]=error [8 + 4*set ..]: n_live, work counter, retired CTAs (all zero between launches)
     uint64_t *stats_scratch;     // OFX_N_STATS counters when the caller passes NULL
     bool graph_ready, transforms_ready;
+    // ofx_set_graph does not wait for its last kernels: their results land in host_res behind graph_event and are read
+    // by graph_finish(), which every call that needs them runs first
+    int2 *scan_sums;              // ceil(n_bricks / 1024) block sums of the brick scans
+    int *host_res;                // page-locked copy of scratch[0..8)
+    cudaEvent_t graph_event;
+    bool graph_pending;
     bool counters_dirty[2];       // a launch failed between the cull and the fused kernel: the launch counters need a reset
 };
+
+namespace ofx {
+int graph_finish(ofx_volume *v);   // ofx_skin_cache.cu
+}
