@@ -116,6 +116,14 @@ int ofx_integrate_warped(ofx_volume *v, const float *rotations, const float *tra
  * ofx_set_transforms + ofx_integrate. */
 int ofx_prepare_frame(ofx_volume *v, const float *rotations, const float *translations, int32_t H,
                       int32_t W, const float *intr_host, void *stream);
+/* No reference counterpart (the reference integrates one frame at a time on one device).  EVERYTHING of the next warped
+ * frame except the fused kernel -- interleaved frame image, depth tiles, node transforms, brick cull with the depth-range
+ * test -- into the frame set that is not in use, on `stream`, while the current frame integrates on another stream; the
+ * caller orders the call after the frame BEFORE the current one (whose set it overwrites).  The next ofx_integrate must be
+ * given the same depth / colour_packed pointers and camera; it launches the fused kernel only, on a grid that leaves one
+ * CTA slot per SM free for the staging launches of the frame after it. */
+int ofx_stage_frame(ofx_volume *v, const float *rotations, const float *translations, const float *depth,
+                    const float *colour_packed, int32_t H, int32_t W, const float *intr_host, void *stream);
 
 /* Materialise what the reference keeps on the host, on request only (vis / tests):
  *   world_pts (n,3)                                   tsdf.py:307

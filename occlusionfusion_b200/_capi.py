@@ -19,7 +19,7 @@ STAT_UPDATED, STAT_SKIN_VALID, STAT_BRICKS, STAT_WEIGHT_SUM = range(4)
 # every symbol include/ofx.h declares (tests check the .so exports all of them)
 SYMBOLS = [
     "ofx_abi_version", "ofx_last_error", "ofx_volume_create", "ofx_volume_destroy", "ofx_volume_reset",
-    "ofx_volume_num_voxels", "ofx_set_graph", "ofx_set_transforms", "ofx_integrate", "ofx_integrate_warped", "ofx_prepare_frame",
+    "ofx_volume_num_voxels", "ofx_set_graph", "ofx_set_transforms", "ofx_integrate", "ofx_integrate_warped", "ofx_prepare_frame", "ofx_stage_frame",
     "ofx_volume_world_points", "ofx_volume_skin", "ofx_volume_deform", "ofx_pack_frame", "ofx_skin",
     "ofx_warp_points", "ofx_check_visibility", "ofx_peer_copy",
     "ofx_nearest_node", "ofx_pixel_anchors_euclidean", "ofx_argmin_norm", "ofx_greedy_insert", "ofx_sample_nodes", "ofx_erode_mesh", "ofx_truncated_region",
@@ -64,6 +64,7 @@ def load():
     lib.ofx_set_graph.argtypes = [vp, vp, i32, f64, i32, vp]
     lib.ofx_set_transforms.argtypes = [vp, vp, vp, vp]
     lib.ofx_prepare_frame.argtypes = [vp, vp, vp, i32, i32, C.POINTER(C.c_float), vp]
+    lib.ofx_stage_frame.argtypes = [vp, vp, vp, vp, vp, i32, i32, C.POINTER(C.c_float), vp]
     lib.ofx_integrate.argtypes = [vp, vp, vp, i32, i32, C.POINTER(C.c_float), f64, i32, vp, vp]
     lib.ofx_integrate_warped.argtypes = [vp, vp, vp, vp, vp, i32, i32, C.POINTER(C.c_float), f64, vp, vp]
     lib.ofx_volume_world_points.argtypes = [vp, vp, vp]

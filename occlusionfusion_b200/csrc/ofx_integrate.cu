@@ -308,6 +308,9 @@ static int launch_brick(ofx_volume *v, int grid, const GraphArgs &ga, const Fram
 #ifndef OFX_PDL
 #define OFX_PDL 1
 #endif
+#ifndef OFX_STAGE_RESERVE
+#define OFX_STAGE_RESERVE 0      // CTA slots per SM the fused kernel leaves to the staging launches of the next frame (measured: 1 costs the fused kernel 15-20 %, more than the staging hides; tools/shard_probe.py)
+#endif
 #ifndef OFX_PDL_SHARDS
 #define OFX_PDL_SHARDS 1      // shards of a multi-GPU volume too: 0.0903 vs 0.0915 ms/frame on 8 B200 (round 2; in round 1, with a
 #endif                        // separate node-transform kernel in front, it was slower: DESIGN.md section 6)
@@ -327,29 +330,33 @@ struct PdlLaunch {
     PdlLaunch(const PdlLaunch &) = delete;
 };
 
-// the handle's interleaved frame image + depth tiles (grown on demand; the first frame of a size allocates)
+// the handle's interleaved frame images + depth tiles, one per frame set (grown on demand; the first frame of a size
+// allocates): set k at offset k * capacity
 static int ensure_frame_buffers(ofx_volume *v, int H, int W)
 {
     const int64_t npix = (int64_t)H * W;
     if (npix <= v->frame_capacity) return 0;
     if (v->frame_dc) OFX_CUDA(cudaFree(v->frame_dc));
     if (v->depth_tiles) OFX_CUDA(cudaFree(v->depth_tiles));
-    v->frame_dc = nullptr; v->depth_tiles = nullptr; v->frame_capacity = 0;
-    OFX_CUDA(cudaMalloc(&v->frame_dc, (size_t)npix * sizeof(float2)));
+    v->frame_dc = nullptr; v->depth_tiles = nullptr; v->frame_capacity = 0; v->tile_capacity = 0;
+    OFX_CUDA(cudaMalloc(&v->frame_dc, (size_t)2 * npix * sizeof(float2)));
     const int64_t nt = (int64_t)((W + DEPTH_TILE - 1) / DEPTH_TILE) * ((H + DEPTH_TILE - 1) / DEPTH_TILE);
-    OFX_CUDA(cudaMalloc(&v->depth_tiles, (size_t)nt * sizeof(float)));
-    v->frame_capacity = npix;
+    OFX_CUDA(cudaMalloc(&v->depth_tiles, (size_t)2 * nt * sizeof(float)));
+    v->frame_capacity = npix; v->tile_capacity = nt;
+    v->prepared = 0;             // a staged frame lived in the old buffers
     return 0;
 }
+static inline float2 *frame_dc_of(const ofx_volume *v, int set) { return v->frame_dc + (size_t)set * v->frame_capacity; }
+static inline float *tiles_of(const ofx_volume *v, int set) { return v->depth_tiles + (size_t)set * v->tile_capacity; }
 
 // frame_prep_kernel: interleaved image + depth tiles (+ node transforms into `table` when rotations != nullptr)
-static int launch_prep(ofx_volume *v, const float *depth, const float *colour, int H, int W, const float *rotations,
+static int launch_prep(ofx_volume *v, int set, const float *depth, const float *colour, int H, int W, const float *rotations,
                        const float *translations, float *table, cudaStream_t s)
 {
     if (int rc = ensure_frame_buffers(v, H, W)) return rc;
     const int bpr = (W + PREP_BW - 1) / PREP_BW, n_img = bpr * ((H + PREP_BH - 1) / PREP_BH);
     const int n_xf = rotations ? (v->M * 12 + PREP_BW * PREP_BH - 1) / (PREP_BW * PREP_BH) : 0;
-    frame_prep_kernel<<<n_img + n_xf, PREP_BW * PREP_BH, 0, s>>>(depth, colour, H, W, v->frame_dc, v->depth_tiles,
+    frame_prep_kernel<<<n_img + n_xf, PREP_BW * PREP_BH, 0, s>>>(depth, colour, H, W, frame_dc_of(v, set), tiles_of(v, set),
                                                                  (W + DEPTH_TILE - 1) / DEPTH_TILE, bpr, n_img, rotations,
                                                                  translations, v->M, table);
     OFX_LAUNCH_CHECK();
@@ -384,14 +391,18 @@ static int launch_cull(ofx_volume *v, int set, const Camera &cam, const float *t
 }
 
 template <int K, bool OBS1>
-static int launch_persistent_t(ofx_volume *v, const FrameArgs &fa, unsigned long long *stats, cudaStream_t s)
+static int launch_persistent_t(ofx_volume *v, const FrameArgs &fa, unsigned long long *stats, int staged, cudaStream_t s)
 {
     using C = PersistCfg<K>;
     // (function attributes are per device: set on every launch, nothing cached per process)
     OFX_CUDA(cudaFuncSetAttribute(fused_warped_persistent<K, OBS1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
     const int set = v->cur_set;
     const GraphArgs ga = graph_args(v);
-    const int cap = v->sm_count * C::MIN_CTAS;        // persistent grid: a multiple of the SM count
+    // persistent grid: a multiple of the SM count.  A frame that arrived through ofx_stage_frame belongs to a caller that
+    // stages the NEXT frame on another stream while this kernel runs: OFX_STAGE_RESERVE CTA slots per SM stay free for
+    // those launches (a persistent grid that owns every slot would hold them back until its tail)
+    const int per_sm = staged == 2 && C::MIN_CTAS > OFX_STAGE_RESERVE ? C::MIN_CTAS - OFX_STAGE_RESERVE : C::MIN_CTAS;
+    const int cap = v->sm_count * per_sm;
     const int want = (v->n_active + C::GROUPS - 1) / C::GROUPS;
     const int grid = want < cap ? want : cap;         // CTAs beyond the live count retire at once
     PdlLaunch L(v, grid, C::THREADS, C::SMEM, s);
@@ -403,7 +414,7 @@ static int launch_persistent_t(ofx_volume *v, const FrameArgs &fa, unsigned long
 
 template <int K>
 static int launch_warped(ofx_volume *v, FrameArgs fa, unsigned long long *stats, const float *rotations,
-                         const float *translations, bool culled, cudaStream_t s)
+                         const float *translations, int staged, cudaStream_t s)
 {
     const float obsf = fa.fu.obsf;
     const bool fast = volume_vec_ok(v) && fa.fu.obs_is_f32 && obsf >= 1e-18f && obsf <= 1e18f;
@@ -421,28 +432,30 @@ static int launch_warped(ofx_volume *v, FrameArgs fa, unsigned long long *stats,
         OFX_CUDA(cudaMemsetAsync(stats, 0, OFX_N_STATS * sizeof(uint64_t), s));
         return 0;
     }
-    if (int rc = launch_prep(v, fa.depth, fa.colour_im, fa.cam.H, fa.cam.W, rotations, translations, v->node_rec, s)) return rc;
-    fa.dc = v->frame_dc;
-    if (!culled)
-        if (int rc = launch_cull(v, v->cur_set, fa.cam, v->depth_tiles, s)) return rc;
+    // staged: 0 nothing, 1 node transforms + frustum cull (ofx_prepare_frame), 2 everything but the fused kernel (ofx_stage_frame)
+    if (staged < 2)
+        if (int rc = launch_prep(v, v->cur_set, fa.depth, fa.colour_im, fa.cam.H, fa.cam.W, rotations, translations, v->node_rec, s)) return rc;
+    fa.dc = frame_dc_of(v, v->cur_set);
+    if (staged == 0)
+        if (int rc = launch_cull(v, v->cur_set, fa.cam, tiles_of(v, v->cur_set), s)) return rc;
 #ifdef OFX_CULL_ONLY     // timing builds only: preparation + cull alone
     return 0;
 #endif
-    return obsf == 1.0f ? launch_persistent_t<K, true>(v, fa, stats, s) : launch_persistent_t<K, false>(v, fa, stats, s);
+    return obsf == 1.0f ? launch_persistent_t<K, true>(v, fa, stats, staged, s) : launch_persistent_t<K, false>(v, fa, stats, staged, s);
 }
 
 static int dispatch_warped(ofx_volume *v, const FrameArgs &fa, unsigned long long *st, const float *rotations,
-                           const float *translations, bool culled, cudaStream_t s)
+                           const float *translations, int staged, cudaStream_t s)
 {
     switch (v->K) {
-    case 1: return launch_warped<1>(v, fa, st, rotations, translations, culled, s);
-    case 2: return launch_warped<2>(v, fa, st, rotations, translations, culled, s);
-    case 3: return launch_warped<3>(v, fa, st, rotations, translations, culled, s);
-    case 4: return launch_warped<4>(v, fa, st, rotations, translations, culled, s);
-    case 5: return launch_warped<5>(v, fa, st, rotations, translations, culled, s);
-    case 6: return launch_warped<6>(v, fa, st, rotations, translations, culled, s);
-    case 7: return launch_warped<7>(v, fa, st, rotations, translations, culled, s);
-    default: return launch_warped<8>(v, fa, st, rotations, translations, culled, s);
+    case 1: return launch_warped<1>(v, fa, st, rotations, translations, staged, s);
+    case 2: return launch_warped<2>(v, fa, st, rotations, translations, staged, s);
+    case 3: return launch_warped<3>(v, fa, st, rotations, translations, staged, s);
+    case 4: return launch_warped<4>(v, fa, st, rotations, translations, staged, s);
+    case 5: return launch_warped<5>(v, fa, st, rotations, translations, staged, s);
+    case 6: return launch_warped<6>(v, fa, st, rotations, translations, staged, s);
+    case 7: return launch_warped<7>(v, fa, st, rotations, translations, staged, s);
+    default: return launch_warped<8>(v, fa, st, rotations, translations, staged, s);
     }
 }
 
@@ -456,14 +469,46 @@ extern "C" int ofx_prepare_frame(ofx_volume *v, const float *rotations, const fl
     if (int rc = graph_finish(v)) return rc;
     cudaStream_t s = (cudaStream_t)stream;
     const int set = 1 - v->cur_set;
-    v->prepared = false;
+    v->prepared = 0;
     if (int rc = ofx_write_transforms(v, v->node_rec_set[set], rotations, translations, s)) return rc;
     const Camera cam{intr_host[0], intr_host[1], intr_host[2], intr_host[3], H, W};
     if (v->n_active > 0)
         if (int rc = launch_cull(v, set, cam, nullptr, s)) return rc;
     for (int i = 0; i < 4; ++i) v->prepared_intr[i] = intr_host[i];
     v->prepared_hw[0] = H; v->prepared_hw[1] = W;
-    v->prepared = true;
+    v->prepared = 1;
+    return 0;
+}
+
+// Everything of the next warped frame except the fused kernel -- interleaved image, depth tiles, node transforms, brick cull
+// with the depth-range test -- into the frame set that is NOT in use: runs on another stream while the current frame
+// integrates (the caller orders it after the frame BEFORE the current one, whose set it overwrites).  The next
+// ofx_integrate with the same images and camera launches the fused kernel only.
+extern "C" int ofx_stage_frame(ofx_volume *v, const float *rotations, const float *translations, const float *depth,
+                               const float *colour_packed, int32_t H, int32_t W, const float *intr_host, void *stream)
+{
+    OFX_REQUIRE(v && rotations && translations && depth && colour_packed && intr_host && H > 0 && W > 0, "ofx_stage_frame: bad arguments");
+    OFX_REQUIRE(v->graph_ready, "ofx_stage_frame: call ofx_set_graph first");
+    if (int rc = graph_finish(v)) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int set = 1 - v->cur_set;
+    v->prepared = 0;
+    if (v->n_active <= 0 || !volume_vec_ok(v)) {          // nothing to cull / generic kernel: transforms only
+        if (int rc = ofx_write_transforms(v, v->node_rec_set[set], rotations, translations, s)) return rc;
+        if (v->n_active > 0) {
+            const Camera cam0{intr_host[0], intr_host[1], intr_host[2], intr_host[3], H, W};
+            if (int rc = launch_cull(v, set, cam0, nullptr, s)) return rc;
+        }
+        v->prepared = 1;
+    } else {
+        if (int rc = launch_prep(v, set, depth, colour_packed, H, W, rotations, translations, v->node_rec_set[set], s)) return rc;
+        const Camera cam{intr_host[0], intr_host[1], intr_host[2], intr_host[3], H, W};
+        if (int rc = launch_cull(v, set, cam, tiles_of(v, set), s)) return rc;
+        v->prepared = 2;
+        v->staged_depth = depth; v->staged_colour = colour_packed;
+    }
+    for (int i = 0; i < 4; ++i) v->prepared_intr[i] = intr_host[i];
+    v->prepared_hw[0] = H; v->prepared_hw[1] = W;
     return 0;
 }
 
@@ -482,8 +527,8 @@ extern "C" int ofx_integrate(ofx_volume *v, const float *depth, const float *col
     }
     OFX_REQUIRE(v->graph_ready, "ofx_integrate: warped frame before ofx_set_graph");
     if (int rc = graph_finish(v)) return rc;
-    const bool culled = v->prepared;
-    if (culled) {
+    int staged = v->prepared;
+    if (staged) {
         // ofx_prepare_frame has staged this frame in the other set: switch to it
         const float *pi = v->prepared_intr;
         OFX_REQUIRE(pi[0] == intr_host[0] && pi[1] == intr_host[1] && pi[2] == intr_host[2] && pi[3] == intr_host[3] &&
@@ -492,11 +537,18 @@ extern "C" int ofx_integrate(ofx_volume *v, const float *depth, const float *col
         v->cur_set ^= 1;
         v->node_rec = v->node_rec_set[v->cur_set];
         v->live = v->live_set[v->cur_set];
-        v->prepared = false;
+        v->prepared = 0;
         v->transforms_ready = true;
+        if (staged == 2) {
+            OFX_REQUIRE(v->staged_depth == depth && v->staged_colour == colour_packed,
+                        "ofx_integrate: images differ from the ones given to ofx_stage_frame");
+            // a frame weight outside the float32 fast path takes the generic kernel, which reads the plain images
+            const FuseArgs &fu = fa.fu;
+            if (!(fu.obs_is_f32 && fu.obsf >= 1e-18f && fu.obsf <= 1e18f)) staged = 1;
+        }
     }
     OFX_REQUIRE(v->transforms_ready, "ofx_integrate: warped frame before ofx_set_transforms");
-    return dispatch_warped(v, fa, st, nullptr, nullptr, culled, s);
+    return dispatch_warped(v, fa, st, nullptr, nullptr, staged, s);
 }
 
 // ofx_set_transforms + ofx_integrate of a warped frame as ONE call: the node transforms ride in the frame
@@ -512,8 +564,8 @@ extern "C" int ofx_integrate_warped(ofx_volume *v, const float *rotations, const
     cudaStream_t s = (cudaStream_t)stream;
     unsigned long long *st = reinterpret_cast<unsigned long long *>(stats ? stats : v->stats_scratch);
     const FrameArgs fa = make_frame_args(depth, colour_packed, intr_host, H, W, v->desc.trunc_margin, obs_weight);
-    v->prepared = false;         // a staged look-ahead frame is superseded by the transforms given here
-    const int rc = dispatch_warped(v, fa, st, rotations, translations, false, s);
+    v->prepared = 0;             // a staged look-ahead frame is superseded by the transforms given here
+    const int rc = dispatch_warped(v, fa, st, rotations, translations, 0, s);
     if (!rc) v->transforms_ready = true;
     return rc;
 }

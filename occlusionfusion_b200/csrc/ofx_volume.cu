@@ -188,7 +188,7 @@ int ofx_upload_nodes(ofx_volume *v, const float *nodes, int M, cudaStream_t s)
         v->node_rec_capacity = cap;
     }
     v->cur_set = 0;
-    v->prepared = false;
+    v->prepared = 0;
     v->node_rec = v->node_rec_set[0];
     v->live = v->live_set[0];
     for (int k = 0; k < 2; ++k) {

@@ -86,11 +86,12 @@ struct ofx_volume {
     int cur_set;                 // per-frame set (node transforms, live list, launch counters, counter accumulators) in use
     float prepared_intr[4];      // the camera ofx_prepare_frame culled against
     int prepared_hw[2];
-    bool prepared;               // the other set holds the next frame's transforms + live list (ofx_prepare_frame)
+    int prepared;                // the other set holds the next frame: 1 = transforms + frustum-culled live list (ofx_prepare_frame), 2 = everything but the fused kernel (ofx_stage_frame)
+    const float *staged_depth, *staged_colour;   // the images ofx_stage_frame was given
     unsigned long long *stats_acc;   // 2 x OFX_N_STATS: per-set accumulators of the persistent kernel
-    float2 *frame_dc;            // per frame: the frame interleaved {depth, packed colour} (frame_prep_kernel)
-    float *depth_tiles;          // per frame: max valid depth of each DEPTH_TILE x DEPTH_TILE pixel tile (0 = none)
-    int64_t frame_capacity;      // pixels allocated for frame_dc / depth_tiles
+    float2 *frame_dc;            // per frame set: the frame interleaved {depth, packed colour} (frame_prep_kernel); set k at k * frame_capacity
+    float *depth_tiles;          // per frame set: max valid depth of each DEPTH_TILE x DEPTH_TILE pixel tile (0 = none); set k at k * tile_capacity
+    int64_t frame_capacity, tile_capacity;   // pixels / tiles allocated per set
     int sm_count;                // of the handle's device
     int *scratch;                // small device scratch: [0]=total [1]=max [2]=error [8 + 4*set ..]: n_live, work counter, retired CTAs (all zero between launches)
     uint64_t *stats_scratch;     // OFX_N_STATS counters when the caller passes NULL

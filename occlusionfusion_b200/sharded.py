@@ -198,11 +198,15 @@ class ShardedFusion:
         self._ev_bcast = [torch.cuda.Event() for _ in range(2)]
         self._ev_done = [torch.cuda.Event() for _ in range(2)]
         self._HW = (H, W)
-        # OFX_LOOKAHEAD=1: stage frame t+1's node transforms and frustum cull (ofx_prepare_frame) on the communication
-        # stream while frame t integrates.  Off by default: measured slower on 2/4/8 B200 (0.335 vs 0.327, 0.191 vs
-        # 0.176, 0.132 vs 0.101 ms/frame) -- the cull's CTAs queue behind the persistent kernel, which owns every SM
-        # slot until its tail, and the next frame then waits for them across streams.
-        self._lookahead = hasattr(self.be, "prepare") and bool(os.environ.get("OFX_LOOKAHEAD"))
+        # Look-ahead on the communication stream while frame t integrates (OFX_LOOKAHEAD): 1 = frame t+1's node transforms
+        # and frustum cull (ofx_prepare_frame), 2 = everything of frame t+1 but the fused kernel (ofx_stage_frame: frame
+        # image, depth tiles, node transforms, cull with the depth-range test).  The staging kernels only get SM slots
+        # in the tail of the persistent kernel (it owns every slot; leaving one slot per SM free costs it 15-20 %,
+        # tools/shard_probe.py), so what is hidden is their launch latency and part of their run time.
+        la = os.environ.get("OFX_LOOKAHEAD", "")
+        self._lookahead = int(la) if la.isdigit() and hasattr(self.be, "prepare") else 0
+        if self._lookahead == 2 and not hasattr(self.be, "stage"):
+            self._lookahead = 1
 
     def pipeline_begin(self, H, W, first_packet=None):
         self.pipeline_setup(H, W)
@@ -254,7 +258,10 @@ class ShardedFusion:
                 # frame t's node-transform table and frustum cull, still on the communication stream: they
                 # overlap the kernel of frame t-1 (their CTAs fill the SM slots its tail frees)
                 v = self._pviews[j]
-                self.be.prepare(v["R"], v["T"], self._HW[0], self._HW[1])
+                if self._lookahead == 2:
+                    self.be.stage(v["R"], v["T"], v["depth"], v["colour"])
+                else:
+                    self.be.prepare(v["R"], v["T"], self._HW[0], self._HW[1])
             self._ev_bcast[j].record(self._comm)
         return self._pgath[pj].view(self.world, N_STATS)
 
@@ -377,6 +384,14 @@ class CudaShard:
         stream (ofx_prepare_frame); the next integrate() then launches only the fused kernel."""
         c = self._capi
         c.check(self.lib.ofx_prepare_frame(self.vol._h, c.ptr(R), c.ptr(T), int(H), int(W), self.vol._intr4, self._s()))
+
+    def stage(self, R, T, depth, colour):
+        """Look-ahead, full: everything of the next frame except the fused kernel (ofx_stage_frame) into the other frame
+        set, on the current stream; the next integrate() on the same images launches the fused kernel only."""
+        c = self._capi
+        H, W = depth.shape
+        c.check(self.lib.ofx_stage_frame(self.vol._h, c.ptr(R), c.ptr(T), c.ptr(depth), c.ptr(colour), int(H), int(W),
+                                         self.vol._intr4, self._s()))
 
     def pack_frame(self, im):
         self.vol.update(im, getattr(self.vol, "frame_id", -self.vol.fopt.skip_rate) + self.vol.fopt.skip_rate)

@@ -355,13 +355,14 @@ def test_sharded_equals_whole(x_block, oracle):
         _assert_bit_equal(vol, ov, gx)
 
 
-@pytest.mark.parametrize("lookahead", [False, True])
+@pytest.mark.parametrize("lookahead", [0, 1, 2])
 def test_pipelined_driver_equals_sequential(lookahead, oracle, monkeypatch):
-    """sharded.ShardedFusion.pipeline_* (two packets, two streams: the N > 1 bench path) on one shard, without and
-    with the ofx_prepare_frame look-ahead: same volume and the same per-frame counters as the sequential step(),
+    """sharded.ShardedFusion.pipeline_* (two packets, two streams: the N > 1 bench path) on one shard, without the
+    look-ahead, with ofx_prepare_frame (1) and with ofx_stage_frame (2: everything of the next frame but the fused
+    kernel staged on the communication stream): same volume and the same per-frame counters as the sequential step(),
     and as the oracle."""
     if lookahead:
-        monkeypatch.setenv("OFX_LOOKAHEAD", "1")
+        monkeypatch.setenv("OFX_LOOKAHEAD", str(lookahead))
     else:
         monkeypatch.delenv("OFX_LOOKAHEAD", raising=False)
     import torch
@@ -404,7 +405,7 @@ def test_pipelined_driver_equals_sequential(lookahead, oracle, monkeypatch):
         assert np.array_equal(a, b)
     # (the look-ahead cull runs before the depth image exists, so it keeps the bricks behind the surface: more bricks
     # and skin-valid voxels VISITED, the same voxels updated)
-    cols = [0, 3] if lookahead else [0, 1, 2, 3]
+    cols = [0, 3] if lookahead == 1 else [0, 1, 2, 3]
     assert np.array_equal(counters[0][-1][:, cols], counters[1][-1][:, cols])
     assert np.array_equal(counters[0][-2][:, cols], counters[1][-2][:, cols])
     ov = oracle.OracleVolume(w.dims, w.origin, w.voxel_size, w.intr, w.trunc)

@@ -1,44 +1,49 @@
-"""Investigation only: where an end-to-end frame (public classes, host buffers) spends its time.  tools/e2e_probe.py"""
-import os, sys, time
+"""Investigation only: host time per call of the N > 1 end-to-end loop (bench.py bench_e2e on host frames), per rank.
+    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tools/e2e_probe.py \
+        --gpus 2 --workload c1 --also '' --no-cpu-baseline --no-parity
+Wraps the pipeline's host functions with wall-clock accumulators (no device synchronisation) and prints mean microseconds per
+call to stderr when the process ends."""
+import atexit
+import os
+import sys
+import time
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-import numpy as np
-import torch
-from occlusionfusion_b200 import TSDFVolume, WarpField
-from occlusionfusion_b200.synthetic import Workload
+import torch.distributed as dist                                           # noqa: E402
+from occlusionfusion_b200 import sharded, warpfield                        # noqa: E402
 
-w = Workload(os.environ.get("WORKLOAD", "c2-dense"))
-dev = torch.device("cuda:0")
-vol = TSDFVolume(w.bbox, w.max_depth, w.intr, w.fopt, None, device=dev)
-wf = WarpField(w.graph(), vol, None)
-vol.warpfield = wf
-frames = [torch.from_numpy(w.frame(i)).pin_memory().numpy() for i in range(5)]
-ests = [w.estimate(i) for i in range(1, 5)]
-vol.integrate({"im": frames[0], "id": 0})
-acc = {}
-def lap(name, t0, sync=False):
-    if sync:
-        torch.cuda.synchronize()
-    t = time.perf_counter()
-    acc.setdefault(name, []).append((t - t0) * 1e6)
-    return t
-for mode in ("async", "sync-each"):
-    acc.clear()
-    sy = mode == "sync-each"
-    for s in range(1, 40):
-        est = dict(ests[s % 4]); est["target_frame_id"] = vol.frame_id + 1
-        wf.frame_id = vol.frame_id
-        torch.cuda.synchronize()
-        t0 = ta = time.perf_counter()
-        wf.update_transformations(est); t0 = lap("update_transformations (host numpy)", t0, sy)
-        vol.update(frames[1 + s % 4], vol.frame_id + 1); t0 = lap("update: H2D RGB+Z, pack kernel", t0, sy)
-        wf._sync_device(); t0 = lap("H2D R|T + node-transform kernel", t0, sy)
-        H, W = vol._depth_im_dev.shape
-        from occlusionfusion_b200 import _capi
-        _capi.check(vol._lib.ofx_integrate(vol._h, _capi.ptr(vol._depth_im_dev), _capi.ptr(vol._color_im_dev), H, W, vol._intr4, 1.0, 0,
-                                           _capi.ptr(vol._stats), _capi.stream_ptr(dev))); t0 = lap("ofx_integrate (cull + fused)", t0, sy)
-        vol.last_stats(); t0 = lap("last_stats (D2H + sync)", t0)
-        acc.setdefault("TOTAL", []).append((t0 - ta) * 1e6)
-    print(mode)
-    for k, v in acc.items():
-        print(f"   {k:42s} {np.median(v[5:]):8.1f} us")
+T = {}
+
+
+def wrap(obj, name, label=None):
+    fn = getattr(obj, name)
+    label = label or name
+
+    def inner(*a, **k):
+        t0 = time.perf_counter()
+        r = fn(*a, **k)
+        e = T.setdefault(label, [0, 0.0])
+        e[0] += 1
+        e[1] += time.perf_counter() - t0
+        return r
+    setattr(obj, name, inner)
+
+
+for n in ("_stage_host", "_exchange", "pipeline_step", "counters_host", "_integrate", "pipeline_begin", "pipeline_end"):
+    wrap(sharded.ShardedFusion, n)
+wrap(warpfield.WarpField, "update_transformations")
+wrap(dist, "all_gather_into_tensor")
+
+
+def report():
+    rank = int(os.environ.get("RANK", "0"))
+    if rank > 1:
+        return
+    lines = [f"[e2e_probe rank {rank}]"] + [f"  {k:28s} n={v[0]:6d}  mean {1e6 * v[1] / max(1, v[0]):9.1f} us" for k, v in T.items()]
+    print("\n".join(lines), file=sys.stderr, flush=True)
+
+
+atexit.register(report)
+import bench                                                               # noqa: E402
+sys.exit(bench.main())

@@ -43,6 +43,64 @@ for s in range(24):
     if s >= 4:
         ti.append(ev[0].elapsed_time(ev[1]))
 print(f"shard 0 of {N} ({w.name}): prep+cull+fused {np.median(ti) * 1e3:.1f} us (min {np.min(ti) * 1e3:.1f}), stats {st.tolist()}")
+# ---- K frames back to back: one stream (prep + cull + fused per frame) against the staged loop (ofx_stage_frame of frame
+# t+1 on a second stream while frame t's fused kernel runs)
+K = int(os.environ.get("LOOP", "200"))
+lib = _capi.load()
+def reset():
+    _capi.check(lib.ofx_volume_reset(vol._h, _capi.stream_ptr(dev)))
+    torch.cuda.synchronize()
+def loop_plain():
+    out = []
+    for t in range(K):
+        R, T, depth, colour = frames[t % 4]
+        st = torch.zeros(4, dtype=torch.int64, device=dev)
+        be.integrate_warped(R, T, depth, colour, 1.0, stats=st)
+        out.append(st)
+    return out
+sB = torch.cuda.Stream(device=dev, priority=-1)
+def loop_staged():
+    sA = torch.cuda.current_stream(dev)
+    ev_done = [torch.cuda.Event() for _ in range(2)]
+    ev_staged = [torch.cuda.Event() for _ in range(2)]
+    sB.wait_stream(sA)
+    with torch.cuda.stream(sB):
+        be.stage(*frames[0])
+        ev_staged[0].record(sB)
+    out = []
+    for t in range(K):
+        R, T, depth, colour = frames[t % 4]
+        sA.wait_event(ev_staged[t % 2])
+        st = torch.zeros(4, dtype=torch.int64, device=dev)
+        be.integrate(depth, colour, False, 1.0, stats=st)
+        ev_done[t % 2].record(sA)
+        out.append(st)
+        if t + 1 < K:
+            with torch.cuda.stream(sB):
+                if t >= 1:
+                    sB.wait_event(ev_done[(t - 1) % 2])
+                be.stage(*frames[(t + 1) % 4])
+                ev_staged[(t + 1) % 2].record(sB)
+    sA.wait_stream(sB)
+    return out
+res = {}
+for name, fn in (("plain", loop_plain), ("staged", loop_staged), ("plain", loop_plain), ("staged", loop_staged)):
+    reset()
+    fn()                                        # warm
+    reset()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    sts = fn()
+    e1.record()
+    torch.cuda.synchronize()
+    tot = torch.stack(sts).cpu().numpy()
+    vols = [a.copy() for a in vol.get_volume()]
+    res.setdefault(name, []).append((e0.elapsed_time(e1) * 1e3 / K, tot, vols))
+    print(f"  loop {name:7s}: {e0.elapsed_time(e1) * 1e3 / K:7.2f} us/frame over {K} frames")
+a, b = res["plain"][0], res["staged"][0]
+same = np.array_equal(a[1][:, [0, 3]], b[1][:, [0, 3]]) and all(np.array_equal(x, y) for x, y in zip(a[2], b[2]))
+print("  staged loop == plain loop (updated / weight-sum counters of every frame, whole volume):", same)
 if timing:
     L = _capi.load()
     buf = (ctypes.c_ulonglong * (2048 * 8))()
