@@ -94,10 +94,14 @@ __device__ __forceinline__ void warp_voxel(const uint32_t (&ids)[2], const float
 // ({B_x, B_y} and {R_02, R_12} sit in aligned register pairs after the loads: the x and y components of
 // fma(R_2, p_z, B) are ONE packed fma.rn.f32x2, FFMA2 in SASS.)
 // Bricks with more than ROW_TAB_CAP nodes take the record path (warp_voxel).
-constexpr int ROW_TAB_CAP = 32;
-constexpr int ROW_TAB_BYTES = 4 * ROW_TAB_CAP * 16 + ROW_TAB_CAP * 8;      // per warp
+// (ROW_TAB_CAP = 32: ofx_volume.cuh)
+constexpr int ROW_TAB_BYTES = 4 * ROW_TAB_CAP * 16 + ROW_TAB_CAP * 8;      // per warp, at the largest capacity
+// The persistent kernel sizes its tables per LAUNCH (tab_cap <= ROW_TAB_CAP entries per row, chosen per graph: see
+// choose_tab_cap in ofx_skin_cache.cu): every KB of shared memory a CTA does not ask for goes to the L1 cache.
+__host__ __device__ constexpr int row_tab_bytes(int cap) { return 4 * cap * 16 + cap * 8; }
 
-__device__ __forceinline__ void build_row_table(uint32_t rec_base, int n_used, float px, float py, uint32_t tab_base, int lane)
+__device__ __forceinline__ void build_row_table(uint32_t rec_base, int n_used, float px, float py, uint32_t tab_base, int lane,
+                                                int cap = ROW_TAB_CAP)
 {
     const int r = lane >> 3;
     for (int n = lane & 7; n < n_used; n += 8) {
@@ -109,10 +113,10 @@ __device__ __forceinline__ void build_row_table(uint32_t rec_base, int n_used, f
         const float bx = __fmaf_rn(a[1], py, __fmaf_rn(a[0], px, a[9]));
         const float by = __fmaf_rn(a[4], py, __fmaf_rn(a[3], px, a[10]));
         const float bz = __fmaf_rn(a[7], py, __fmaf_rn(a[6], px, a[11]));
-        const uint32_t ent = tab_base + (uint32_t)(r * ROW_TAB_CAP + n) * 16u;
+        const uint32_t ent = tab_base + (uint32_t)(r * cap + n) * 16u;
         asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(ent), "f"(bx), "f"(by), "f"(bz), "f"(a[8]) : "memory");
         if (r == 0)
-            asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(tab_base + 4u * ROW_TAB_CAP * 16u + (uint32_t)n * 8u), "f"(a[2]),
+            asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(tab_base + 4u * (uint32_t)cap * 16u + (uint32_t)n * 8u), "f"(a[2]),
                          "f"(a[5])
                          : "memory");
     }

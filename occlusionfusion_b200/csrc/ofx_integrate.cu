@@ -405,9 +405,11 @@ static int launch_persistent_t(ofx_volume *v, const FrameArgs &fa, unsigned long
     const int cap = v->sm_count * per_sm;
     const int want = (v->n_active + C::GROUPS - 1) / C::GROUPS;
     const int grid = want < cap ? want : cap;         // CTAs beyond the live count retire at once
-    PdlLaunch L(v, grid, C::THREADS, C::SMEM, s);
+    // row tables sized for this graph (graph_finish): shared memory the CTAs do not ask for is L1 cache for the gathers
+    const int tab_cap = v->tab_cap > 0 && v->tab_cap <= ROW_TAB_CAP ? v->tab_cap : ROW_TAB_CAP;
+    PdlLaunch L(v, grid, C::THREADS, C::smem(tab_cap), s);
     OFX_CUDA(cudaLaunchKernelEx(&L.cfg, fused_warped_persistent<K, OBS1>, v->geom, v->desc.tsdf, v->desc.weight, v->desc.colour,
-                                ga, fa, (const int *)v->live, v->scratch + 8 + 4 * set, v->stats_acc + set * OFX_N_STATS, stats));
+                                ga, fa, (const int *)v->live, v->scratch + 8 + 4 * set, v->stats_acc + set * OFX_N_STATS, stats, tab_cap));
     v->counters_dirty[set] = false;
     return 0;
 }

@@ -133,6 +133,8 @@ extern "C" int ofx_volume_create(ofx_volume **out, const ofx_volume_desc *d)
     OFX_CUDA(cudaMalloc(&v->stats_scratch, OFX_N_STATS * sizeof(uint64_t)));
     OFX_CUDA(cudaMalloc(&v->scan_sums, ((nb + 1023) / 1024 + 1) * sizeof(int2)));
     OFX_CUDA(cudaHostAlloc(&v->host_res, 8 * sizeof(int), cudaHostAllocDefault));
+    OFX_CUDA(cudaMalloc(&v->node_hist, 64 * sizeof(int)));
+    OFX_CUDA(cudaHostAlloc(&v->host_hist, 64 * sizeof(int), cudaHostAllocDefault));
     OFX_CUDA(cudaEventCreateWithFlags(&v->graph_event, cudaEventDisableTiming));
     *out = v;
     return 0;
@@ -145,7 +147,8 @@ extern "C" int ofx_volume_destroy(ofx_volume *v)
     cudaFree(v->brick_off); cudaFree(v->brick_radius); cudaFree(v->cand); cudaFree(v->brick_nodes);
     cudaFree(v->active); cudaFree(v->scratch); cudaFree(v->stats_scratch);
     cudaFree(v->live_set[0]); cudaFree(v->live_set[1]); cudaFree(v->stats_acc); cudaFree(v->active_desc); cudaFree(v->brick_box); cudaFree(v->depth_tiles); cudaFree(v->frame_dc);
-    cudaFree(v->scan_sums);
+    cudaFree(v->scan_sums); cudaFree(v->node_hist);
+    if (v->host_hist) cudaFreeHost(v->host_hist);
     if (v->host_res) cudaFreeHost(v->host_res);
     if (v->graph_event) cudaEventDestroy(v->graph_event);
     delete v;

@@ -20,6 +20,10 @@ constexpr int LIVE_DESC_INTS = 8;      // live-brick descriptor: {lx0, iy0, iz0,
 constexpr int NODE_XFORM_OFFSET = 4;  // the 48-byte {R, T} tail is what the fused kernels stage (one TMA bulk copy)
 constexpr int NODE_XFORM_FLOATS = 12;
 __host__ __device__ constexpr int slot_bytes_of(int kp) { return BRICK_VOXELS * 5 * kp; }
+#ifndef OFX_ROW_TAB_CAP
+#define OFX_ROW_TAB_CAP 32
+#endif
+constexpr int ROW_TAB_CAP = OFX_ROW_TAB_CAP;   // largest per-warp row table of the fused kernels (ofx_brick.cuh)
 constexpr int MAX_BRICK_NODES = 255;  // local anchor ids are bytes, 0xFF = "no anchor"
 
 struct VolumeGeom {
@@ -102,6 +106,9 @@ struct ofx_volume {
     int *host_res;                // page-locked copy of scratch[0..8)
     cudaEvent_t graph_event;
     bool graph_pending;
+    int *node_hist;               // device: histogram of the used-node counts of the active bricks (bins 0..ROW_TAB_CAP, last = more)
+    int *host_hist;               // page-locked copy
+    int tab_cap;                  // row-table capacity of the persistent kernel for this graph (graph_finish)
     bool counters_dirty[2];       // a launch failed between the cull and the fused kernel: the launch counters need a reset
 };
 
