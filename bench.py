@@ -806,9 +806,25 @@ def bench_graph_ops(args, device):
             ref_graph.compute_edges_geodesic(verts, np.ones((V, 1), bool), faces, nidx, 8, cov, re_, rw, rd, n2v, True, True)
             c_geo = (time.perf_counter() - t0) * 1e3
             assert np.array_equal(ge, re_) and np.array_equal(gw, rw) and np.array_equal(gd, rd)
+        # the same on the device (csrc/ofx_graph_edges.cu): mesh uploaded once, one CTA per node search; wall clock of the
+        # whole call (it returns host arrays), compared with the host builder's result
+        from occlusionfusion_b200.graph_proc import DeviceMesh, compute_edges_geodesic_d
+        mesh_d = DeviceMesh(verts, faces, np.ones(V, bool), device)
+        de, dw, dd = -np.ones((M, 8), np.int32), np.zeros((M, 8), np.float32), np.zeros((M, 8), np.float32)
+        compute_edges_geodesic_d(mesh_d, nidx, 8, cov, de, dw, dd, True, True)          # warm (pool allocations)
+        t_geo_dev = []
+        for _ in range(3):
+            de[:] = -1; dw[:] = 0; dd[:] = 0
+            torch.cuda.synchronize(device)
+            t0 = time.perf_counter()
+            replayed = compute_edges_geodesic_d(mesh_d, nidx, 8, cov, de, dw, dd, True, True)
+            t_geo_dev.append((time.perf_counter() - t0) * 1e3)
+        assert np.array_equal(de, ge) and np.array_equal(dw, gw) and np.array_equal(dd, gd)
         out["ops"][f"mesh_{n}x{n}"] = {
             "edges_geodesic_host": {"ms": t_geo, "host_threads": os.cpu_count(), "cpu_ms": c_geo, "cpu_kind": "reference",
                                     "cpu_cores": 1, "where": "host C++ in libofx (the reference's is host C++ too)"},
+            "edges_geodesic_device": {"gpu_ms": float(np.median(t_geo_dev)), "nodes_replayed_for_ties": int(replayed),
+                                      "timing": "host wall clock of the whole call (results back on the host), mesh already uploaded"},
             "V": V, "F": F, "nodes_sampled": M, "graph_nodes": int(nodes.shape[0]), "candidates": int(len(cand)), "inserted": k,
             "erode_mesh_3_rounds": {"gpu_ms": t_erode, "cpu_ms": c_erode, "cpu_kind": kind, "cpu_cores": 1},
             "sample_nodes": {"gpu_ms": t_sample, "cpu_ms": c_sample, "cpu_kind": kind, "cpu_cores": 1},

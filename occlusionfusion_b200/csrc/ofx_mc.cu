@@ -10,6 +10,8 @@
 //   vertex exactly when its end points lie on different sides of the level and one of the (up to four) cubes around it is
 //   processed -- the case table uses every crossed edge of a cube (tests/test_mc_oracle.py checks the table for that).  So
 //   the vertices of a z-row (row = x*Dy + y) can be counted and numbered from the volume alone, in key order:
+//     mc_row_flags_kernel per row: does the mask hold a cube at all (the truncated region is sparse: the count pass then
+//                         reads the volume only around flagged rows)
 //     mc_count_kernel     per row: triangles of its cubes, vertices of the edges whose lower corner lies in the row
 //     exclusive_scan x 2  row offsets of triangles and vertices; the totals stay on the device (counts[2])
 //     mc_vertices_kernel  per row: position, gradient normal, colour of every owned vertex at row offset + rank, and its
@@ -93,16 +95,50 @@ __device__ __forceinline__ int block_exclusive_scan(int v, int *s_warp, int *tot
     return before + incl - v;
 }
 
+// pass 0 (only with a mask): row_flag[r] = the z-row r holds a processed cube.  The mask is sparse (the truncated region
+// is a fraction of a percent of a fusion volume): the count pass then touches the volume only around flagged rows.
+__global__ void __launch_bounds__(256) mc_row_flags_kernel(const uint8_t *__restrict__ mask, int rows, int D, uint8_t *__restrict__ row_flag)
+{
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    const int n_warps = (gridDim.x * blockDim.x) >> 5;
+    for (int r = warp; r < rows; r += n_warps) {
+        const uint8_t *m = mask + (int64_t)r * D;
+        int any = 0;
+        if ((D & 15) == 0 && (reinterpret_cast<uintptr_t>(m) & 15) == 0) {
+            for (int q = lane; q < (D >> 4); q += 32) {
+                const uint4 w = __ldg(reinterpret_cast<const uint4 *>(m) + q);
+                any |= (w.x | w.y | w.z | w.w) != 0u;
+            }
+        } else {
+            for (int z = lane; z < D; z += 32) any |= __ldg(m + z) != 0;
+        }
+        any = __any_sync(0xffffffffu, any);
+        if (lane == 0) row_flag[r] = (uint8_t)any;
+    }
+}
+
 // pass 1: triangles and owned vertices per z-row.  Nothing per voxel is stored: the later passes recompute.
-__global__ void __launch_bounds__(256) mc_count_kernel(McGrid g, int32_t *__restrict__ row_tris, int32_t *__restrict__ row_verts)
+// row_flag == nullptr (no mask): every row counts.
+__global__ void __launch_bounds__(256) mc_count_kernel(McGrid g, const uint8_t *__restrict__ row_flag, int32_t *__restrict__ row_tris,
+                                                       int32_t *__restrict__ row_verts)
 {
     __shared__ int s_warp[8];
     for (int r = blockIdx.x; r < g.W * g.H; r += gridDim.x) {
         const int x = r / g.H, y = r - x * g.H;
+        // cubes of this row make triangles; cubes of the rows (x-1..x, y-1..y) touch the edges that start in this row
+        bool f_t = true, f_v = true;
+        if (row_flag) {
+            f_t = row_flag[r] != 0;
+            f_v = f_t || (x > 0 && row_flag[r - g.H]) || (y > 0 && row_flag[r - 1]) || (x > 0 && y > 0 && row_flag[r - g.H - 1]);
+        }
+        if (!f_v) {                                                    // uniform across the block
+            if (threadIdx.x == 0) { row_tris[r] = 0; row_verts[r] = 0; }
+            continue;
+        }
         int tris = 0, verts = 0;
         for (int z = threadIdx.x; z < g.D; z += blockDim.x) {
             const int64_t i = (int64_t)r * g.D + z;
-            tris += OFX_MC_TRIS[mc_case(g, i, x, y, z)];
+            if (f_t) tris += OFX_MC_TRIS[mc_case(g, i, x, y, z)];
             verts += __popc(owned_edges(g, i, x, y, z));
         }
         int total_t, total_v;
@@ -243,14 +279,16 @@ extern "C" int ofx_mc_mesh(const float *vol, const uint8_t *mask, const float *c
     // scratch (stream-ordered pool): four row arrays, the scan's block sums, one 16-bit code per vertex
     int32_t *rowbuf = nullptr;
     uint16_t *vcode = nullptr;
-    const size_t n_row_ints = (size_t)4 * rows + 2 + n_sums;
+    const size_t n_row_ints = (size_t)4 * rows + 2 + n_sums + (mask ? (rows + 3) / 4 + 1 : 0);      // + one flag byte per row
     if (graph_scratch_alloc((void **)&rowbuf, n_row_ints * sizeof(int32_t), s)) return 1;
     if (graph_scratch_alloc((void **)&vcode, ((size_t)cap_verts + 8) * sizeof(uint16_t), s)) { cudaFreeAsync(rowbuf, s); return 1; }
     int32_t *row_tris = rowbuf, *row_verts = rowbuf + rows, *tri_off = rowbuf + 2 * rows, *vert_off = rowbuf + 3 * rows + 1;
     int32_t *sums = rowbuf + 4 * rows + 2;                                // tri_off and vert_off have rows + 1 entries
+    uint8_t *row_flag = mask ? reinterpret_cast<uint8_t *>(rowbuf + 4 * rows + 2 + n_sums) : nullptr;
     const McGrid g{vol, mask, Dx, Dy, Dz, level};
     int rc = 0;
-    mc_count_kernel<<<grid, 256, 0, s>>>(g, row_tris, row_verts);
+    if (mask) mc_row_flags_kernel<<<sm_count() * 8, 256, 0, s>>>(mask, rows, Dz, row_flag);
+    mc_count_kernel<<<grid, 256, 0, s>>>(g, row_flag, row_tris, row_verts);
     if (!rc) rc = exclusive_scan(row_verts, rows, vert_off, sums, counts + 0, s);
     if (!rc) rc = exclusive_scan(row_tris, rows, tri_off, sums, counts + 1, s);
     if (!rc && cudaMemcpyAsync(vert_off + rows, counts, sizeof(int32_t), cudaMemcpyDeviceToDevice, s) != cudaSuccess) rc = 1;
