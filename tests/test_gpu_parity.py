@@ -731,3 +731,18 @@ def test_overlapped_frames_with_a_reused_host_buffer(pinned, oracle):
     seen.append(vol.last_stats()["updated"])
     assert seen == expected and min(expected[1:]) > 1000
     _assert_bit_equal(vol, ov)
+
+
+@pytest.mark.parametrize("cap", ["1", "6", "32"])
+def test_row_table_capacity_does_not_change_results(cap, oracle, monkeypatch):
+    """The persistent kernel sizes its per-warp row tables per graph (choose_tab_cap, csrc/ofx_skin_cache.cu); bricks with
+    more nodes than the capacity blend straight from the staged node transforms.  Forced capacities (the library's
+    investigation hook OFX_TAB_CAP): 1 = every brick takes the staged-transform path, 6 = a mix, 32 = every brick the
+    tables -- all bit-identical to the oracle."""
+    from occlusionfusion_b200.synthetic import Workload
+    monkeypatch.setenv("OFX_TAB_CAP", cap)
+    w = Workload("tiny")
+    vol, ov, wf, stats = _run_pair(w, oracle, n_frames=4)
+    _assert_bit_equal(vol, ov)
+    for st, n in stats:
+        assert st["updated"] == n
