@@ -308,6 +308,9 @@ static int launch_brick(ofx_volume *v, int grid, const GraphArgs &ga, const Fram
 #ifndef OFX_PDL
 #define OFX_PDL 1
 #endif
+#ifndef OFX_SMALL_REC
+#define OFX_SMALL_REC 1
+#endif
 #ifndef OFX_STAGE_RESERVE
 #define OFX_STAGE_RESERVE 0      // CTA slots per SM the fused kernel leaves to the staging launches of the next frame (measured: 1 costs the fused kernel 15-20 %, more than the staging hides; tools/shard_probe.py)
 #endif
@@ -390,12 +393,12 @@ static int launch_cull(ofx_volume *v, int set, const Camera &cam, const float *t
     return 0;
 }
 
-template <int K, bool OBS1>
+template <int K, bool OBS1, bool SMALL>
 static int launch_persistent_t(ofx_volume *v, const FrameArgs &fa, unsigned long long *stats, int staged, cudaStream_t s)
 {
-    using C = PersistCfg<K>;
+    using C = PersistCfg<K, SMALL>;
     // (function attributes are per device: set on every launch, nothing cached per process)
-    OFX_CUDA(cudaFuncSetAttribute(fused_warped_persistent<K, OBS1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
+    OFX_CUDA(cudaFuncSetAttribute(fused_warped_persistent<K, OBS1, SMALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
     const int set = v->cur_set;
     const GraphArgs ga = graph_args(v);
     // persistent grid: a multiple of the SM count.  A frame that arrived through ofx_stage_frame belongs to a caller that
@@ -408,7 +411,7 @@ static int launch_persistent_t(ofx_volume *v, const FrameArgs &fa, unsigned long
     // row tables sized for this graph (graph_finish): shared memory the CTAs do not ask for is L1 cache for the gathers
     const int tab_cap = v->tab_cap > 0 && v->tab_cap <= ROW_TAB_CAP ? v->tab_cap : ROW_TAB_CAP;
     PdlLaunch L(v, grid, C::THREADS, C::smem(tab_cap), s);
-    OFX_CUDA(cudaLaunchKernelEx(&L.cfg, fused_warped_persistent<K, OBS1>, v->geom, v->desc.tsdf, v->desc.weight, v->desc.colour,
+    OFX_CUDA(cudaLaunchKernelEx(&L.cfg, fused_warped_persistent<K, OBS1, SMALL>, v->geom, v->desc.tsdf, v->desc.weight, v->desc.colour,
                                 ga, fa, (const int *)v->live, v->scratch + 8 + 4 * set, v->stats_acc + set * OFX_N_STATS, stats, tab_cap));
     v->counters_dirty[set] = false;
     return 0;
@@ -443,7 +446,10 @@ static int launch_warped(ofx_volume *v, FrameArgs fa, unsigned long long *stats,
 #ifdef OFX_CULL_ONLY     // timing builds only: preparation + cull alone
     return 0;
 #endif
-    return obsf == 1.0f ? launch_persistent_t<K, true>(v, fa, stats, staged, s) : launch_persistent_t<K, false>(v, fa, stats, staged, s);
+    // graphs whose bricks use at most 32 nodes each run the variant with the small node-transform area (more L1)
+    if (OFX_SMALL_REC && v->max_used > 0 && v->max_used <= 32)
+        return obsf == 1.0f ? launch_persistent_t<K, true, true>(v, fa, stats, staged, s) : launch_persistent_t<K, false, true>(v, fa, stats, staged, s);
+    return obsf == 1.0f ? launch_persistent_t<K, true, false>(v, fa, stats, staged, s) : launch_persistent_t<K, false, false>(v, fa, stats, staged, s);
 }
 
 static int dispatch_warped(ofx_volume *v, const FrameArgs &fa, unsigned long long *st, const float *rotations,

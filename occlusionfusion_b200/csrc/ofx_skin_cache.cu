@@ -531,6 +531,7 @@ int ofx::graph_finish(ofx_volume *v)
     int max_used = v->host_hist[ROW_TAB_CAP + 2];
     for (int c = ROW_TAB_CAP; c > 0 && max_used == 0; --c)
         if (v->host_hist[c]) max_used = c;
+    v->max_used = max_used;
     if (const char *e = getenv("OFX_TAB_CAP")) v->tab_cap = std::min(ROW_TAB_CAP, std::max(1, atoi(e)));
     if (getenv("OFX_DEBUG"))
         fprintf(stderr, "[ofx] graph: %d active bricks, largest brick node count %d -> row tables of %d entries\n", v->n_active, max_used, v->tab_cap);

@@ -109,6 +109,7 @@ struct ofx_volume {
     int *node_hist;               // device: histogram of the used-node counts of the active bricks (bins 0..ROW_TAB_CAP, last = more)
     int *host_hist;               // page-locked copy
     int tab_cap;                  // row-table capacity of the persistent kernel for this graph (graph_finish)
+    int max_used;                 // largest brick node count of the graph (graph_finish)
     bool counters_dirty[2];       // a launch failed between the cull and the fused kernel: the launch counters need a reset
 };
 
