@@ -191,6 +191,7 @@ class ShardedFusion:
         self._ev_gath = [torch.cuda.Event() for _ in range(2)] if dev.type == "cuda" else [None, None]
         # host-frame staging on the rank that receives the camera frames (pipeline_step(next_packet=(im, R, T)))
         self._hraw = [None, None]
+        self._hviews = [None, None]
         self._hRT = [None, None]
         self._hfr = [None, None]
         self._ev_staged = [None, None]
@@ -218,7 +219,7 @@ class ShardedFusion:
         self._comm.wait_stream(torch.cuda.current_stream(dev))
         self._exchange(0, first_packet, prev=None)
 
-    def _exchange(self, t, packet, prev, publish=True):
+    def _exchange(self, t, packet, prev, publish=True, comp=None):
         """Communication-stream work of one step: publish packet t and gather the counters of frame
         `prev` (None: nothing to gather yet).  ONE collective does both jobs: the all-gather of the
         counters is also the hand-shake of the packet transport --
@@ -229,7 +230,12 @@ class ShardedFusion:
         The pull is a copy-engine transfer from rank 0's mapped buffer: the persistent fused kernel holds
         every SM slot, an SM copy kernel (ofx_peer_copy, OFX_PULL_KERNEL=1) would queue behind it."""
         j = t % 2
-        with torch.cuda.stream(self._comm):
+        # (set_stream both ways instead of the `with torch.cuda.stream` context: it looks the current stream up twice, ~20 us
+        # of Python per frame on the rank that paces the end-to-end loop)
+        if comp is None:
+            comp = torch.cuda.current_stream(self.device)
+        torch.cuda.set_stream(self._comm)
+        try:
             if prev is not None:
                 self._comm.wait_event(self._ev_done[prev % 2])
             if publish and self.rank == 0 and isinstance(packet, (tuple, list)):
@@ -263,6 +269,8 @@ class ShardedFusion:
                 else:
                     self.be.prepare(v["R"], v["T"], self._HW[0], self._HW[1])
             self._ev_bcast[j].record(self._comm)
+        finally:
+            torch.cuda.set_stream(comp)
         return self._pgath[pj].view(self.world, N_STATS)
 
     def _stage_host(self, j, im, R, T):
@@ -277,6 +285,8 @@ class ShardedFusion:
         if self._hraw[j] is None:
             self._hraw[j] = torch.empty((4, H, W), dtype=torch.float32, device=dev)
             self._hRT[j] = torch.empty(12 * M, dtype=torch.float32).pin_memory()
+            # views made once: this function runs per frame on the rank that paces the end-to-end loop
+            self._hviews[j] = (self._hraw[j][:3], self._hraw[j][3], self._hRT[j].numpy(), self._pbuf[j][:12 * M])
         elif self._ev_staged[j] is not None:
             self._ev_staged[j].synchronize()                     # the staging of two frames ago has left the pinned buffers
         src = im if isinstance(im, torch.Tensor) else torch.from_numpy(np.asarray(im, dtype=np.float32))
@@ -287,15 +297,15 @@ class ShardedFusion:
             self._hfr[j][3].copy_(src[-1])
             self._hraw[j].copy_(self._hfr[j], non_blocking=True)
         else:
-            self._hraw[j][:3].copy_(src[:3], non_blocking=True)
-            self._hraw[j][3].copy_(src[-1], non_blocking=True)
+            self._hviews[j][0].copy_(src[:3], non_blocking=True)
+            self._hviews[j][1].copy_(src[-1], non_blocking=True)
         v = self._pviews[j]
         _capi.check(_capi.load().ofx_pack_frame(_capi.ptr(self._hraw[j]), 4, H, W, _capi.ptr(v["colour"]), _capi.ptr(v["depth"]),
                                                 _capi.stream_ptr(dev)))
-        h = self._hRT[j].numpy()
+        h = self._hviews[j][2]
         h[:9 * M] = np.asarray(R, dtype=np.float32).reshape(-1)
         h[9 * M:] = np.asarray(T, dtype=np.float32).reshape(-1)
-        self._pbuf[j][:12 * M].copy_(self._hRT[j], non_blocking=True)      # R at word 0, T at word 9 M (FramePacket)
+        self._hviews[j][3].copy_(self._hRT[j], non_blocking=True)          # R at word 0, T at word 9 M (FramePacket)
         if self._ev_staged[j] is None:
             self._ev_staged[j] = torch.cuda.Event()
         self._ev_staged[j].record(self._comm)
@@ -323,7 +333,7 @@ class ShardedFusion:
             self._integrate(v, False, obs_weight, stats=self._pstats[j])
         self._ev_done[j].record(comp)
         # issued after integrate(t): the look-ahead stages frame t+1 in the frame set integrate(t) is not using
-        out = self._exchange(t + 1, next_packet, prev=t - 1 if t > 0 else None, publish=not last)
+        out = self._exchange(t + 1, next_packet, prev=t - 1 if t > 0 else None, publish=not last, comp=comp)
         self._pipe_t += 1
         return out
 

@@ -84,6 +84,8 @@ class TSDFVolume:
         # the host->device copy of frame t+1 runs on the upload stream while the kernels of frame t run on the
         # caller's stream; nothing in integrate() waits for the device (counters are read lazily, last_stats()).
         self._set = 0
+        self._fd_views = [None, None]
+        self._comp = None            # the compute stream of the integrate() call in progress (update() reuses it)
         self._frame_host = [None, None]     # pinned staging for frames that arrive in pageable memory
         self._frame_dev = [None, None]
         self._color_ims = [None, None]
@@ -178,7 +180,8 @@ class TSDFVolume:
             self._color_ims[j] = torch.empty((H, W), dtype=torch.float32, device=self.device)
             self._depth_ims[j] = torch.empty((H, W), dtype=torch.float32, device=self.device)
             self._frame_host[j] = None
-        comp = torch.cuda.current_stream(self.device)
+            self._fd_views[j] = (self._frame_dev[j][:3], self._frame_dev[j][3])
+        comp = self._comp if self._comp is not None else torch.cuda.current_stream(self.device)
         fd = self._frame_dev[j]
         if im_t is not None and im_t.is_cuda:
             fd[:3].copy_(im_t[:3])
@@ -198,13 +201,19 @@ class TSDFVolume:
             cs = self._copy_stream
             if self._set_used[j]:
                 cs.wait_event(self._set_done[j])          # the kernels of two frames ago are done with this set
-            with torch.cuda.stream(cs):
+            # (set_stream both ways instead of `with torch.cuda.stream(cs)`: the context manager looks the current stream
+            # up twice, ~20 us of Python per frame; `comp` is the current stream, known here)
+            torch.cuda.set_stream(cs)
+            try:
                 if src4 is not None:
                     fd.copy_(src4, non_blocking=True)
                 else:
-                    fd[:3].copy_(src[:3], non_blocking=True)
-                    fd[3].copy_(src[-1], non_blocking=True)
+                    fd3, fdz = self._fd_views[j]
+                    fd3.copy_(src[:3], non_blocking=True)
+                    fdz.copy_(src[-1], non_blocking=True)
                 self._h2d_done[j].record(cs)
+            finally:
+                torch.cuda.set_stream(comp)
             comp.wait_event(self._h2d_done[j])
         self.h2d_bytes_last_frame = fd.numel() * 4
         self._color_im_dev, self._depth_im_dev, self._stats = self._color_ims[j], self._depth_ims[j], self._stats_sets[j]
@@ -235,7 +244,11 @@ class TSDFVolume:
         (tsdf.py:395-398); any other frame is warped by self.warpfield (tsdf.py:401).
         Returns once the work is enqueued; last_stats() (or any read of the volume) waits for it."""
         with torch.cuda.device(self.device):
-            self.update(image_data["im"], image_data["id"])
+            comp = self._comp = torch.cuda.current_stream(self.device)      # looked up once per frame (8 us of Python a call)
+            try:
+                self.update(image_data["im"], image_data["id"])
+            finally:
+                self._comp = None
             identity = self.frame_id == self.fopt.source_frame
             H, W = self._depth_im_dev.shape
             S = _capi.stream_ptr(self.device)
@@ -259,7 +272,6 @@ class TSDFVolume:
                                                     _capi.ptr(self._stats), S))
             # the frame's counters go to page-locked host memory behind the kernels; nobody waits here
             j = self._set
-            comp = torch.cuda.current_stream(self.device)
             self._stats_host[j].copy_(self._stats, non_blocking=True)
             self._set_done[j].record(comp)
             self._set_used[j] = True

@@ -85,24 +85,30 @@ class WarpField:
         T = np.asarray(self.translations)
         assert R.shape[0] == M == T.shape[0], \
             f"Nodes mismatch between transformation data:{self.rotations.shape} and graph nodes:{nodes.shape}"
-        with torch.cuda.device(self.device):
-            if self._RT_host is None or self._RT_host.shape[1] != 12 * M:
-                # two staging buffers used in turn: the upload of frame t+1 may be staged while frame t's is in flight
+        if self._RT_host is None or self._RT_host.shape[1] != 12 * M:
+            # two staging buffers used in turn: the upload of frame t+1 may be staged while frame t's is in flight
+            with torch.cuda.device(self.device):
                 self._RT_host = torch.empty((2, 12 * M), dtype=torch.float32, pin_memory=True)
                 self._RT_dev = torch.empty((2, 12 * M), dtype=torch.float32, device=self.device)
                 self._RT_done = [torch.cuda.Event(), torch.cuda.Event()]
-                self._RT_used = [False, False]
-                self._RT_i = 0
-            i = self._RT_i = 1 - self._RT_i
-            if self._RT_used[i]:
-                self._RT_done[i].synchronize()   # the upload before last has left this staging buffer
-            h = self._RT_host[i].numpy()
-            h[:9 * M] = R.reshape(-1)            # casts to float32 like the reference's device upload
-            h[9 * M:] = T.reshape(-1)
-            self._RT_dev[i].copy_(self._RT_host[i], non_blocking=True)
-            self._RT_done[i].record(torch.cuda.current_stream(self.device))
-            self._RT_used[i] = True
-        self._R_dev, self._T_dev = self._RT_dev[i, :9 * M], self._RT_dev[i, 9 * M:]
+            self._RT_used = [False, False]
+            self._RT_i = 0
+            # views made once (the frame loop is host-paced on small volumes: every Python object per frame counts)
+            self._RT_np = [self._RT_host[k].numpy() for k in range(2)]
+            self._RT_views = [(self._RT_dev[k, :9 * M], self._RT_dev[k, 9 * M:]) for k in range(2)]
+        i = self._RT_i = 1 - self._RT_i
+        if self._RT_used[i]:
+            self._RT_done[i].synchronize()       # the upload before last has left this staging buffer
+        h = self._RT_np[i]
+        h[:9 * M] = R.reshape(-1)                # casts to float32 like the reference's device upload
+        h[9 * M:] = T.reshape(-1)
+        comp = getattr(self.tsdf, "_comp", None)          # inside TSDFVolume.integrate: the stream it looked up
+        if comp is None:
+            comp = torch.cuda.current_stream(self.device)
+        self._RT_dev[i].copy_(self._RT_host[i], non_blocking=True)      # H2D: runs on the destination device's current stream
+        self._RT_done[i].record(comp)
+        self._RT_used[i] = True
+        self._R_dev, self._T_dev = self._RT_views[i]
         return self._R_dev, self._T_dev
 
     def _sync_device(self):
