@@ -919,8 +919,18 @@ def main():
         return e
 
     names = [n for n in args.also.split(",") if n and n != args.workload] if args.also else []
+    def settle():
+        """Between workloads (never inside a timed region): the previous workload's volume, warp field and graph reference one
+        another, so only the cyclic collector frees them -- at a moment of its choosing, e.g. in the middle of the next
+        workload's update_graph, where the cudaFree of gigabytes of volume and skin cache showed up as single 20-70 ms
+        updates.  Collect now."""
+        import gc
+        gc.collect()
+        torch.cuda.synchronize(device)
+
     if world == 1:
         for name in names:
+            settle()
             if name == "c3":
                 also["c3"] = bench_c3(args, device)
             else:

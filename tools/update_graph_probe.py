@@ -48,3 +48,6 @@ verts, faces = vol.get_canonical_model()[:2]
 print(f"mesh {len(verts)} vertices {len(faces)} faces, {wf.graph.nodes.shape[0]} nodes")
 for k, v in T.items():
     print(f"  {k:45s} n={len(v):3d} median {np.median(v):8.3f} ms  total/update_graph {sum(v) / max(1, len(T['update_graph'])):8.3f} ms")
+if os.environ.get("PROBE_LISTS"):      # every call, in order: the first calls carry one-off costs
+    for k, v in T.items():
+        print(f"  {k:45s} " + " ".join(f"{x:.2f}" for x in v))
