@@ -276,7 +276,7 @@ class ShardedFusion:
     def _stage_host(self, j, im, R, T):
         """Rank 0, on the communication stream: a HOST frame (6,H,W) float32 (RGB in [0,1] + XYZ, tsdf.py:545-572) and the
         node transforms R (M,3,3), T (M,3) into packet j -- RGB + Z are DMA'd (straight from the caller's buffer when it is
-        page-locked: do not overwrite it before the next pipeline_step returns), folded into the packet's colour / depth
+        page-locked: do not overwrite it before wait_staged() of that packet returns), folded into the packet's colour / depth
         images on the device (ofx_pack_frame), R | T go through a pinned staging buffer.  Nothing waits for the device."""
         from . import _capi
         H, W = self._HW
@@ -309,6 +309,14 @@ class ShardedFusion:
         if self._ev_staged[j] is None:
             self._ev_staged[j] = torch.cuda.Event()
         self._ev_staged[j].record(self._comm)
+
+    def wait_staged(self, t):
+        """Blocks until the HOST frame and node transforms handed over for frame t (pipeline_begin: t = 0; pipeline_step
+        number i: t = i + 1) have been read: a page-locked frame buffer may be overwritten afterwards (a pageable one is
+        copied before pipeline_step returns and may be reused at once)."""
+        ev = self._ev_staged[t % 2]
+        if ev is not None:
+            ev.synchronize()
 
     def counters_host(self, t):
         """The gathered (world, N_STATS) counters of frame t as a host array; waits only for that frame's exchange

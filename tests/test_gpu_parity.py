@@ -746,3 +746,54 @@ def test_row_table_capacity_does_not_change_results(cap, oracle, monkeypatch):
     _assert_bit_equal(vol, ov)
     for st, n in stats:
         assert st["updated"] == n
+
+
+@pytest.mark.parametrize("pinned", [False, True])
+def test_pipelined_driver_on_host_frames(pinned, oracle):
+    """The end-to-end form of the pipelined driver (what bench.py's e2e leg runs at N > 1): pipeline_step is handed HOST
+    frames + node transforms as (im, R, T) tuples, stages them on the communication stream (sharded.py _stage_host: DMA of
+    RGB + Z, pack kernel, R|T through pinned memory) and reads the counters one exchange late from pinned memory.  One
+    shard, bit-identical to the oracle; the host buffers are overwritten as soon as the documented rule allows."""
+    import torch
+    from occlusionfusion_b200 import WarpField
+    from occlusionfusion_b200.sharded import CudaShard, ShardedFusion
+    from occlusionfusion_b200.synthetic import Workload
+    w = Workload("tiny")
+    dev = torch.device("cuda", 0)
+    vol = _mk_volume(w)
+    wf = WarpField(w.graph(), vol, None)
+    vol.warpfield = wf
+    sf = ShardedFusion(CudaShard(vol), w.dims, 0, 1, w.dims[0], dev)
+    sf.set_graph(w.nodes, w.coverage, w.K)
+    ov = oracle.OracleVolume(w.dims, w.origin, w.voxel_size, w.intr, w.trunc)
+    ov.set_graph(w.nodes, w.coverage, w.K)
+    sf.fill_packet(w.frame(0), np.tile(np.eye(3, dtype=np.float32), (w.M, 1, 1)), np.zeros((w.M, 3), np.float32))
+    sf.step(w.H, w.W, identity_warp=True)
+    ov.integrate(w.frame(0), True)
+    n = 7
+    bufs = [torch.empty((6, w.H, w.W), dtype=torch.float32, pin_memory=pinned) for _ in range(2)]   # two in flight at most
+
+    def host_packet(i):
+        f = i + 1
+        est = w.estimate(f)
+        T = (-np.einsum("nij,nj->ni", est["node_rotations"], w.nodes) + w.nodes + est["node_translations"]).astype(np.float32)
+        b = bufs[i % 2]
+        b.numpy()[...] = w.frame(f)
+        return (b.numpy(), est["node_rotations"], T)
+
+    expected = []
+    for i in range(n):
+        f = i + 1
+        est = w.estimate(f)
+        T = (-np.einsum("nij,nj->ni", est["node_rotations"], w.nodes) + w.nodes + est["node_translations"]).astype(np.float32)
+        ov.set_transforms(est["node_rotations"], T)
+        expected.append(ov.integrate(w.frame(f), False))
+    sf.pipeline_begin(w.H, w.W, host_packet(0))
+    for i in range(n):
+        if pinned and i >= 1:
+            sf.wait_staged(i - 1)            # the buffer packet i+1 is about to be written into was packet i-1's
+        sf.pipeline_step(host_packet(i + 1) if i + 1 < n else None, last=(i + 1 == n))
+    sf.pipeline_end()
+    got = [int(sf.counters_host(t)[:, 0].sum()) for t in range(n - 2, n)]
+    assert got == expected[-2:] and min(expected) > 1000
+    _assert_bit_equal(vol, ov)
