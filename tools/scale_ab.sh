@@ -8,7 +8,7 @@ import json, sys
 n, tag = sys.argv[1:3]
 try:
     d = json.loads(open(f"gpurun_out/bench_{tag}_n{n}.json").read().strip().splitlines()[-1])
-    print(f"n{n} {tag:12s} value {d['value']:.4g} ms/step {d['ms_per_step']:.4f} kernel {d['roofline']['kernel_ms']:.4f} e2e {d['e2e']['ms_per_step']:.3f}")
+    print(f"n{n} {tag:12s} value {d['value']:.4g} ms/step {d['ms_per_step']:.4f} kernel {d['roofline']['kernel_ms']:.4f} e2e {(d.get('e2e') or {}).get('ms_per_step', float('nan')):.3f}")
 except Exception as e:
     print(n, tag, "FAILED", e, open(f"gpurun_out/bench_{tag}_n{n}.err").read()[-600:])
 PY
