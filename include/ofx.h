@@ -300,6 +300,11 @@ int ofx_downsample_nodes_host(const float *nodes_host, int32_t M, double coverag
  * [R | T | colour | depth] from the rank that received the camera frame.  New in this library (the
  * reference has no multi-device path); replaces the NCCL broadcast on the per-frame path. */
 int ofx_peer_copy(void *dst, const void *src, int64_t bytes, int32_t ctas, void *stream);
+/* The frame packet pushed ONCE through an NVSwitch multicast mapping (no reference counterpart: the reference is single-device):
+ * copies `bytes` (multiple of 16) from `src` (local device memory) to `mc_dst`, a multicast address that the switch
+ * replicates into the same offset of every participating GPU's buffer (torch symmetric memory: handle.multicast_ptr), with
+ * multimem.st.  Completion on the peers is the caller's hand-shake (a barrier after this launch in stream order). */
+int ofx_multicast_copy(void *mc_dst, const void *src, int64_t bytes, int32_t ctas, void *stream);
 
 #ifdef __cplusplus
 }

@@ -21,7 +21,7 @@ SYMBOLS = [
     "ofx_abi_version", "ofx_last_error", "ofx_volume_create", "ofx_volume_destroy", "ofx_volume_reset",
     "ofx_volume_num_voxels", "ofx_set_graph", "ofx_set_transforms", "ofx_integrate", "ofx_integrate_warped", "ofx_prepare_frame", "ofx_stage_frame",
     "ofx_volume_world_points", "ofx_volume_skin", "ofx_volume_deform", "ofx_pack_frame", "ofx_skin",
-    "ofx_warp_points", "ofx_check_visibility", "ofx_peer_copy",
+    "ofx_warp_points", "ofx_check_visibility", "ofx_peer_copy", "ofx_multicast_copy",
     "ofx_nearest_node", "ofx_pixel_anchors_euclidean", "ofx_argmin_norm", "ofx_greedy_insert", "ofx_sample_nodes", "ofx_erode_mesh", "ofx_truncated_region",
     "ofx_mc_mesh",
     "ofx_compute_edges_geodesic", "ofx_compute_edges_geodesic_batch", "ofx_edge_weights_host", "ofx_node_and_edge_clean_up", "ofx_compute_clusters", "ofx_compute_clusters_noalloc", "ofx_upsample_index",
@@ -74,6 +74,7 @@ def load():
     lib.ofx_skin.argtypes = [vp, i64, vp, i32, f64, i32, vp, vp, vp, vp]
     lib.ofx_warp_points.argtypes = [vp, i64, vp, vp, vp, i32, vp, vp, vp, vp]
     lib.ofx_peer_copy.argtypes = [vp, vp, i64, i32, vp]
+    lib.ofx_multicast_copy.argtypes = [vp, vp, i64, i32, vp]
     lib.ofx_check_visibility.argtypes = [vp, i64, vp, i32, i32, C.POINTER(C.c_float), f64, vp, vp, vp]
     lib.ofx_nearest_node.argtypes = [vp, i64, vp, i32, vp, vp, vp]
     lib.ofx_pixel_anchors_euclidean.argtypes = [vp, i32, vp, i32, i32, C.c_float, vp, vp, vp]

@@ -221,7 +221,28 @@ __global__ void __launch_bounds__(256) peer_copy_kernel(uint4 *__restrict__ dst,
     }
     for (; i < n16; i += stride) dst[i] = src[i];
 }
+// One store per 16 bytes to a MULTICAST address (the NVSwitch replicates it into every mapped GPU's buffer): the frame packet
+// leaves the sending GPU once instead of once per peer.
+__global__ void __launch_bounds__(256) multicast_copy_kernel(float4 *__restrict__ mc_dst, const float4 *__restrict__ src, int64_t n16)
+{
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n16; i += (int64_t)gridDim.x * blockDim.x) {
+        const float4 v = __ldg(src + i);
+        asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_dst + i), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+                     : "memory");
+    }
+}
 }  // namespace ofx
+
+extern "C" int ofx_multicast_copy(void *mc_dst, const void *src, int64_t bytes, int32_t ctas, void *stream)
+{
+    OFX_REQUIRE(mc_dst && src && bytes >= 0 && bytes % 16 == 0, "ofx_multicast_copy: bad arguments");
+    OFX_REQUIRE((((uintptr_t)mc_dst | (uintptr_t)src) & 15) == 0, "ofx_multicast_copy: pointers must be 16-byte aligned");
+    if (bytes == 0) return 0;
+    if (ctas < 1) ctas = 64;
+    ofx::multicast_copy_kernel<<<ctas, 256, 0, (cudaStream_t)stream>>>((float4 *)mc_dst, (const float4 *)src, bytes / 16);
+    OFX_LAUNCH_CHECK();
+    return 0;
+}
 
 extern "C" int ofx_peer_copy(void *dst, const void *src, int64_t bytes, int32_t ctas, void *stream)
 {

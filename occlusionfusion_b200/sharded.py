@@ -180,9 +180,27 @@ class ShardedFusion:
                 import sys
                 print(f"[sharded] symmetric memory unavailable ({type(e).__name__}: {e}); using dist.broadcast", file=sys.stderr)
                 self._peer_src = None
+        # Large packets (BASELINE config 5: 7.6 MB) are PUSHED once through the NVSwitch multicast mapping of the symmetric
+        # buffers instead of being pulled seven times out of rank 0 (its NVLink egress is the bound there): rank 0 stages the
+        # packet in a local buffer, and after the per-frame all-gather (= every rank is done with the frame that used this
+        # packet buffer) copies it to the multicast address (ofx_multicast_copy); a barrier on the symmetric-memory signal
+        # pads tells the peers it has landed.  OFX_MULTICAST=1 / 0 forces it on / off; default: packets of 4 MB and more.
+        self._mc = None
+        if self._peer_src is not None:
+            mc = [int(getattr(h, "multicast_ptr", 0) or 0) for h in self._symm[1]]
+            want = os.environ.get("OFX_MULTICAST")
+            if all(mc) and (want == "1" or (want is None and self.packet.nbytes >= (4 << 20))):
+                self._mc = mc
+                if self.rank == 0 and os.environ.get("OFX_DEBUG"):
+                    import sys
+                    print(f"[sharded] packets of {self.packet.nbytes} bytes go out through the NVSwitch multicast mapping", file=sys.stderr)
+                self._pstage = [self.packet.alloc(dev) if self.rank == 0 else None for _ in range(2)]
         if self._peer_src is None:
             self._pbuf = [self.buf, self.packet.alloc(dev)]
         self._pviews = [self.packet.views(b) for b in self._pbuf]
+        # where rank 0 stages a packet before it is published: the packet buffer itself, or the local buffer of the multicast push
+        self._sbuf = self._pstage if (self._mc and self.rank == 0) else self._pbuf
+        self._sviews = [self.packet.views(b) for b in self._sbuf] if (self._mc and self.rank == 0) else self._pviews
         self._pstats = [torch.zeros(N_STATS, dtype=torch.int64, device=dev) for _ in range(2)]
         self._pgath = [torch.zeros(self.world * N_STATS, dtype=torch.int64, device=dev) for _ in range(2)]
         # gathered counters also land in page-locked host memory behind each exchange: read lazily (counters_host)
@@ -240,8 +258,8 @@ class ShardedFusion:
                 self._comm.wait_event(self._ev_done[prev % 2])
             if publish and self.rank == 0 and isinstance(packet, (tuple, list)):
                 self._stage_host(j, *packet)                     # HOST frame + node transforms -> packet j (asynchronous)
-            elif publish and self.rank == 0 and packet is not None and packet.data_ptr() != self._pbuf[j].data_ptr():
-                self._pbuf[j].copy_(packet, non_blocking=True)
+            elif publish and self.rank == 0 and packet is not None and packet.data_ptr() != self._sbuf[j].data_ptr():
+                self._sbuf[j].copy_(packet, non_blocking=True)
             pj = 0 if prev is None else prev % 2
             if self.world > 1:
                 dist.all_gather_into_tensor(self._pgath[pj], self._pstats[pj], group=self.group)
@@ -250,7 +268,13 @@ class ShardedFusion:
             if prev is not None and self._ev_gath[pj] is not None:
                 self._pgath_host[pj].copy_(self._pgath[pj], non_blocking=True)
                 self._ev_gath[pj].record(self._comm)
-            if self.world > 1 and publish:
+            if self.world > 1 and publish and self._mc:
+                from . import _capi
+                if self.rank == 0:
+                    _capi.check(_capi.load().ofx_multicast_copy(self._mc[j], _capi.ptr(self._sbuf[j]), self.packet.nbytes, 64,
+                                                                _capi.stream_ptr(self.device)))
+                self._symm[1][j].barrier(0, 10000)          # the push has landed everywhere (10 s time-out: no silent hang)
+            elif self.world > 1 and publish:
                 if self._peer_src is None:
                     dist.broadcast(self._pbuf[j], src=0, group=self.group)
                 elif self.rank != 0:
@@ -286,7 +310,7 @@ class ShardedFusion:
             self._hraw[j] = torch.empty((4, H, W), dtype=torch.float32, device=dev)
             self._hRT[j] = torch.empty(12 * M, dtype=torch.float32).pin_memory()
             # views made once: this function runs per frame on the rank that paces the end-to-end loop
-            self._hviews[j] = (self._hraw[j][:3], self._hraw[j][3], self._hRT[j].numpy(), self._pbuf[j][:12 * M])
+            self._hviews[j] = (self._hraw[j][:3], self._hraw[j][3], self._hRT[j].numpy(), self._sbuf[j][:12 * M])
         elif self._ev_staged[j] is not None:
             self._ev_staged[j].synchronize()                     # the staging of two frames ago has left the pinned buffers
         src = im if isinstance(im, torch.Tensor) else torch.from_numpy(np.asarray(im, dtype=np.float32))
@@ -299,7 +323,7 @@ class ShardedFusion:
         else:
             self._hviews[j][0].copy_(src[:3], non_blocking=True)
             self._hviews[j][1].copy_(src[-1], non_blocking=True)
-        v = self._pviews[j]
+        v = self._sviews[j]
         _capi.check(_capi.load().ofx_pack_frame(_capi.ptr(self._hraw[j]), 4, H, W, _capi.ptr(v["colour"]), _capi.ptr(v["depth"]),
                                                 _capi.stream_ptr(dev)))
         h = self._hviews[j][2]
