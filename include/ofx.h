@@ -81,7 +81,10 @@ int64_t ofx_volume_num_voxels(const ofx_volume *v); /* local voxels: nx_local*Dy
 /* Graph nodes (canonical positions g, EDGraph.nodes) -- call again after node insertion
  * (WarpField.update_graph, warpfield.py:487-582 -> :532-533 rebuild tree + re-skin).
  * Rebuilds the per-voxel skin cache (anchor ids + normalised weights; the device form of WarpField.skin_tsdf's cache,
- * warpfield.py:131-141).  K = graph_neighbours (warpfield.py:60), 1..OFX_MAX_K, K <= M. */
+ * warpfield.py:131-141).  K = graph_neighbours (warpfield.py:60), 1..OFX_MAX_K, K <= M.
+ * Waits on `stream` once in the middle (the sizes of the cache it has to provide); the results of its last kernels -- the
+ * number of active bricks, the brick-node overflow error, the statistics the per-frame launch configuration is chosen
+ * from -- are read by the next call on the handle that needs them, which reports the overflow if there was one. */
 int ofx_set_graph(ofx_volume *v, const float *nodes, int32_t M, double node_coverage, int32_t K,
                   void *stream);
 /* Node transforms in origin form: rotations (M,3,3) row-major, translations T = -R g + g + t
@@ -120,8 +123,8 @@ int ofx_prepare_frame(ofx_volume *v, const float *rotations, const float *transl
  * frame except the fused kernel -- interleaved frame image, depth tiles, node transforms, brick cull with the depth-range
  * test -- into the frame set that is not in use, on `stream`, while the current frame integrates on another stream; the
  * caller orders the call after the frame BEFORE the current one (whose set it overwrites).  The next ofx_integrate must be
- * given the same depth / colour_packed pointers and camera; it launches the fused kernel only, on a grid that leaves one
- * CTA slot per SM free for the staging launches of the frame after it. */
+ * given the same depth / colour_packed pointers and camera; it launches the fused kernel only (on the full persistent grid:
+ * leaving a CTA slot per SM free for the staging launches was measured and costs more than it hides). */
 int ofx_stage_frame(ofx_volume *v, const float *rotations, const float *translations, const float *depth,
                     const float *colour_packed, int32_t H, int32_t W, const float *intr_host, void *stream);
 
